@@ -1,0 +1,195 @@
+/* pt_b200.h — C ABI of the B200-native wavefront path tracer.
+ *
+ * This is the drop-in boundary for the hot path of flomonster/path-tracer
+ * (reference = /root/reference, Rust, CPU only).  The reference has no FFI; its hot
+ * path sits behind in-process Rust calls.  Every entry point below cites the
+ * reference interface it replaces (file:line relative to the reference root).
+ * A Rust host binds these with an `extern "C"` block.
+ *
+ * Conventions: every function returns PT_OK (0) or a negative pt_status; it never
+ * throws or aborts across the ABI.  pt_last_error() returns a thread-local message.
+ * Handles are opaque and caller-owned.  There is NO CPU fallback: a call that needs
+ * the GPU fails with PT_ERR_CUDA when no device is usable.
+ */
+#ifndef PT_B200_H
+#define PT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  PT_OK = 0,
+  PT_ERR_INVALID = -1, /* bad argument / malformed scene              */
+  PT_ERR_IO = -2,      /* file missing / unreadable (reference: exit 2) */
+  PT_ERR_PARSE = -3,   /* JSON / YAML / PNG syntax (reference: exit 2)  */
+  PT_ERR_CUDA = -4,    /* CUDA runtime error or no device               */
+  PT_ERR_NOMEM = -5
+} pt_status;
+
+/* ---- flat scene description (what scene/isf.rs:5-142 deserialises into) ---- */
+
+enum { PT_MODEL_MESH = 0, PT_MODEL_SPHERE = 1 };   /* scene/isf.rs:31-43 */
+enum { PT_LIGHT_POINT = 0, PT_LIGHT_DIRECTIONAL = 1 }; /* scene/isf.rs:58-75 */
+enum { PT_TONEMAP_REINHARD = 0, PT_TONEMAP_FILMIC = 1, PT_TONEMAP_ACES = 2 }; /* renderer/tonemap.rs:4-13 */
+enum { PT_BRDF_COOK_TORRANCE = 0 };                /* renderer/brdf/mod.rs:50-55 */
+
+/* One material per model (scene/internal/model.rs:10-21, material.rs:10-25).
+ * Texture slots index pt_scene_desc.textures; -1 = no texture. */
+typedef struct {
+  float albedo[3];
+  float emissive[3];
+  float opacity;
+  float metalness;
+  float roughness;
+  float ior;
+  int32_t albedo_tex;    /* 3-channel, sRGB (material.rs:132-146) */
+  int32_t emissive_tex;  /* 3-channel (material.rs:189-201)        */
+  int32_t opacity_tex;   /* 1-channel (material.rs:207-214)        */
+  int32_t metalness_tex; /* 1-channel (material.rs:152-159)        */
+  int32_t roughness_tex; /* 1-channel (material.rs:165-172)        */
+  int32_t normal_tex;    /* 3-channel (material.rs:178-187)        */
+} pt_material;
+
+/* Model i owns material i.  Mesh: triangles [first_tri, first_tri+n_tris) of the
+ * tri_* arrays, in file order.  Sphere: center/radius (model.rs:26-64). */
+typedef struct {
+  int32_t type;
+  uint32_t first_tri;
+  uint32_t n_tris;
+  float center[3];
+  float radius;
+} pt_model;
+
+typedef struct {
+  int32_t type;
+  float vec[3]; /* Point: position; Directional: direction (light.rs:6-17) */
+  float color[3];
+  float size;   /* unused by the reference (renderer/mod.rs:304)          */
+} pt_light;
+
+/* 8-bit texture, row-major, channels = 3 (into_rgb8) or 1 (into_luma8)
+ * (scene/internal/texture_bank.rs:21-51). */
+typedef struct {
+  uint32_t width, height, channels;
+  const uint8_t *data;
+} pt_texture;
+
+typedef struct {
+  uint32_t n_models;
+  const pt_model *models;
+  const pt_material *materials; /* n_models entries */
+  uint64_t n_tris;
+  const float *tri_pos; /* n_tris*9: v0.xyz v1.xyz v2.xyz            */
+  const float *tri_nrm; /* n_tris*9                                   */
+  const float *tri_uv;  /* n_tris*6                                   */
+  uint32_t n_textures;
+  const pt_texture *textures;
+  uint32_t n_lights;
+  const pt_light *lights;
+  float camera[16];     /* column-major transform[c][r] (camera.rs:26) */
+  float fov;            /* vertical, radians (camera.rs:12)            */
+  float background[3];
+} pt_scene_desc;
+
+/* Profile (config/profile.rs:10-40, config/resolution.rs:4-16). */
+typedef struct {
+  uint32_t width, height; /* default 1920x1080 */
+  uint32_t bounces;       /* default 4         */
+  uint32_t samples;       /* default 64        */
+  int32_t brdf;           /* PT_BRDF_*         */
+  int32_t tonemap;        /* PT_TONEMAP_*, default FILMIC */
+} pt_profile;
+
+/* Closest hit record.  prim_id is the global primitive id: models in file order, a
+ * mesh's triangles contiguous in file order, a sphere takes two ids (entry, exit) —
+ * the order in which renderer/utils.rs:11-21 pushes hits before its stable sort.
+ * prim_id = -1 on a miss.  t is Hit::get_dist (hit.rs:39-45). */
+typedef struct {
+  int32_t prim_id;
+  float t, u, v;
+} pt_hit;
+
+/* Counters of one render (reference-equivalent ray_cast invocations). */
+typedef struct {
+  uint64_t samples;       /* W*H*spp rendered by this call                    */
+  uint64_t extend_rays;   /* one per path segment (renderer/mod.rs:182)       */
+  uint64_t shadow_rays;   /* one per light per shaded hit (mod.rs:291,319), skipped-as-zero excluded */
+  uint64_t alpha_recasts; /* continuation re-casts (implementation artefact) */
+  uint64_t kernel_launches;
+  float ms_total;         /* raygen -> accumulation resident, CUDA events     */
+  float ms_extend, ms_shade, ms_shadow, ms_other;
+  uint64_t extend_launches, shade_launches, shadow_launches;
+} pt_stats;
+
+typedef struct pt_scene pt_scene; /* immutable device-resident scene */
+
+/* ---- error reporting ---- */
+const char *pt_last_error(void);
+/* Number of usable CUDA devices (0 if none); never fails. */
+int pt_device_count(void);
+
+/* ---- profile: Profile::load / Default (config/profile.rs:27-40) ---- */
+void pt_profile_default(pt_profile *out);
+int pt_profile_load_yaml(const char *path, pt_profile *out);
+
+/* ---- scene: load_internal (scene/mod.rs:16-22) + Scene::load (internal/mod.rs:35-51) ---- */
+/* Parses scene.isf (JSON), decodes PNG textures relative to its directory, flattens,
+ * builds the acceleration structure and uploads everything to `device`. */
+int pt_scene_load_isf(const char *path, int device, pt_scene **out);
+/* Same, from caller-provided flat arrays (copied; caller keeps ownership). */
+int pt_scene_create(const pt_scene_desc *desc, int device, pt_scene **out);
+/* Procedural scenes for the large configs: recipe in {"console","foliage","city","soup"},
+ * n_tris is a target triangle count. */
+int pt_scene_synthetic(const char *recipe, uint64_t n_tris, uint64_t seed, int device, pt_scene **out);
+void pt_scene_destroy(pt_scene *scene);
+/* Introspection (host copies; pointers valid until pt_scene_destroy). */
+int pt_scene_get_desc(const pt_scene *scene, pt_scene_desc *out);
+int pt_scene_info(const pt_scene *scene, uint64_t *n_tris, uint64_t *n_prims, uint64_t *n_nodes,
+                  uint64_t *device_bytes);
+
+/* ---- ray_cast (renderer/utils.rs:11-21): first element of the sorted hit list ---- */
+/* rays: n*6 host floats (origin xyz, direction xyz); out: n host pt_hit. */
+int pt_trace_closest(const pt_scene *scene, const float *rays, size_t n, pt_hit *out);
+/* Same on device pointers (rays_dev, out_dev on the scene's device), on `stream`
+ * (a cudaStream_t passed as void*; NULL = default stream). */
+int pt_trace_closest_device(const pt_scene *scene, const float *rays_dev, size_t n, pt_hit *out_dev,
+                            void *stream);
+/* Directional-light shadow semantics of get_light_info (renderer/mod.rs:291-297):
+ * product over every hit of (1 - opacity(hit uv)); out: n floats. */
+int pt_trace_transmittance(const pt_scene *scene, const float *rays, size_t n, float *out);
+
+/* ---- Renderer::render (renderer/mod.rs:76-169) ---- */
+/* Renders samples {sample_begin + k*sample_stride | k in [0,n_samples)} of every pixel
+ * and ADDS their radiance into accum_dev (device, W*H*3 floats, row-major i=x+y*W,
+ * caller-zeroed).  Multi-GPU drivers give each rank a disjoint sample subset and then
+ * sum the buffers (one NCCL reduce).  Asynchronous on `stream` until stats are read:
+ * if stats_out != NULL the call synchronises and fills it. */
+int pt_render_accum_device(const pt_scene *scene, const pt_profile *profile, uint32_t sample_begin,
+                           uint32_t sample_stride, uint32_t n_samples, uint64_t seed, float *accum_dev,
+                           void *stream, pt_stats *stats_out);
+/* post_processing (renderer/mod.rs:150-162,335-353): mean = accum/total_samples,
+ * tonemap, gamma 1/2.2, saturating u8.  accum_dev: W*H*3 floats, rgb8_dev: W*H*3 bytes. */
+int pt_tonemap_device(const float *accum_dev, uint32_t width, uint32_t height, uint32_t total_samples,
+                      int32_t tonemap, uint8_t *rgb8_dev, int device, void *stream);
+/* Whole call a user makes: render all profile->samples on the scene's device, tonemap,
+ * copy back.  rgb8_out: W*H*3 host bytes (row-major RGB); accum_out optional W*H*3
+ * host floats (un-normalised sums); stats_out optional. */
+int pt_render(const pt_scene *scene, const pt_profile *profile, uint64_t seed, uint8_t *rgb8_out,
+              float *accum_out, pt_stats *stats_out);
+
+/* ---- image output: RgbImage::save (main.rs:50) ---- */
+int pt_write_png(const char *path, const uint8_t *rgb8, uint32_t width, uint32_t height);
+/* 8-bit PNG decode used by the texture bank (texture_bank.rs:33,49); channels_out in {1,3}.
+ * *data_out is malloc'ed; free with pt_free. */
+int pt_read_png(const char *path, uint32_t channels_out, uint32_t *width, uint32_t *height,
+                uint8_t **data_out);
+void pt_free(void *p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PT_B200_H */

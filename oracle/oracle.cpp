@@ -1,0 +1,335 @@
+// oracle/oracle.cpp — TEST INFRASTRUCTURE: CPU restatement of the reference's hot path.
+// Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+// load this library; the product (path-tracer_b200/) never links or calls it.
+//
+// Parity pinning: Möller–Trumbore is pinned by the reference's 3012 hit + 3012 miss vectors
+// (tests/moller_trumbore/*.yml, tolerance of triangle.rs:213-216); the whole integrator is
+// checked against the seven SHA-1 image hashes of src/main.rs:100-165 through the ChaCha12
+// (rand 0.8 StdRng) emulation — see tests/test_oracle_kat.py for which of them reproduce.
+//
+// Restates: Renderer::render renderer/mod.rs:76-169, render_pixel :172-228,
+// compute_radiance :230-278, get_light_info :281-333, post_processing :335-353.
+#include <atomic>
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <thread>
+
+#include "shading.hpp"
+
+using namespace orc;
+
+namespace {
+
+const float NORMAL_BIAS = 0.00001f;  // renderer/mod.rs:59
+
+struct Counters {
+  uint64_t extend = 0, shadow = 0;
+};
+
+// get_light_info, renderer/mod.rs:281-333
+void light_info(const Scene &s, const pt_light &light, const Hit &hit, bool brute, std::vector<Hit> &tmp, V3 &radiance,
+                V3 &direction, Counters &cnt) {
+  V3 lc = v3(light.color[0], light.color[1], light.color[2]);
+  V3 ori = hit.position + hit.normal * NORMAL_BIAS;
+  if (light.type == PT_LIGHT_DIRECTIONAL) {
+    V3 dir = v3(light.vec[0], light.vec[1], light.vec[2]);
+    V3 sdir = -1.0f * dir;
+    V3 color = lc;
+    ray_cast(s, ori, sdir, tmp, brute);
+    ++cnt.shadow;
+    for (const Hit &sh : tmp) {
+      MaterialSample ms = hit_material_sample(s, sh, sh.model);
+      color = color * (1.0f - ms.opacity);
+      if (sum(color) == 0.0f) break;
+    }
+    radiance = color;
+    direction = dir;
+    return;
+  }
+  V3 lp = v3(light.vec[0], light.vec[1], light.vec[2]);
+  V3 dir = hit.position - lp;
+  float dist = magnitude(dir);
+  dir = normalize(dir);
+  V3 sdir = -1.0f * dir;
+  float dissipation = 4.0f * PI_F * dist * dist;
+  V3 ld = lc / dissipation;
+  ray_cast(s, ori, sdir, tmp, brute);
+  ++cnt.shadow;
+  for (const Hit &sh : tmp) {
+    if (magnitude(sh.position - hit.position) > dist) break;
+    // quirk (mod.rs:324): the PRIMARY hit's variant/uv with the occluder's material
+    MaterialSample ms = hit_material_sample(s, hit, sh.model);
+    ld = ld * (1.0f - ms.opacity);
+    if (sum(ld) == 0.0f) break;
+  }
+  radiance = ld;
+  direction = dir;
+}
+
+// render_pixel, renderer/mod.rs:172-228 (+ compute_radiance :230-278 inlined)
+V3 render_pixel(const Scene &s, const pt_profile &prof, V3 ro, V3 rd, PathRng &rng, bool brute, std::vector<Hit> &hits,
+                std::vector<Hit> &tmp, Counters &cnt) {
+  V3 color = v3(0, 0, 0), thr = v3(1, 1, 1);
+  for (uint32_t bounce = 0; bounce < prof.bounces + 1; ++bounce) {
+    ray_cast(s, ro, rd, hits, brute);
+    ++cnt.extend;
+    if (hits.empty()) return color + mul_el(thr, s.background);
+    const Hit *hit = nullptr;
+    MaterialSample mat{};
+    V3 normal{};
+    uint32_t j = 0;
+    for (const Hit &h : hits) {
+      mat = hit_material_sample(s, h, h.model);
+      normal = hit_shading_normal(s, h, h.model);
+      hit = &h;
+      float op = mat.opacity;
+      if (op >= 1.0f) break;
+      if (op > 0.001f) {
+        if (rng.alpha(bounce, j++) < op) break;
+      }
+    }
+    V3 view = -1.0f * rd;
+    CookTorrance brdf(mat);
+    color = color + mul_el(thr, mat.emissive);
+    for (const pt_light &light : s.lights) {
+      V3 lr, ldir;
+      light_info(s, light, *hit, brute, tmp, lr, ldir, cnt);
+      if (lr.x == 0.0f && lr.y == 0.0f && lr.z == 0.0f) continue;
+      V3 rl = -1.0f * ldir;
+      color = color + mul_el(mul_el(thr, brdf.eval_direct(normal, view, rl)), lr);
+    }
+    if (bounce < prof.bounces) {
+      V3 no = hit->position + hit->normal * NORMAL_BIAS;
+      float r1 = rng.bsdf(bounce, 0);
+      float r2 = rng.bsdf(bounce, 1);
+      V3 nd = brdf.sample(normal, view, r1, r2);
+      V3 w = brdf.eval_indirect(normal, view, nd) / 1.0f;
+      thr = mul_el(thr, w);
+      ro = no;
+      rd = nd;
+    } else {
+      ro = v3(0, 0, 0);
+      rd = v3(0, 0, 0);
+    }
+    if (dot(thr, thr) < 0.00001f) return color;
+    if (bounce > 3) {  // russian_roulette, utils.rs:23-31
+      float p = rmax(rmax(thr.x, thr.y), thr.z);
+      thr = thr * (1.0f / p);
+      if (rng.rr(bounce) > p) return color;
+    }
+  }
+  return color;
+}
+
+// raygen, renderer/mod.rs:107-124 + camera.rs:36-48
+void raygen(const Scene &s, const pt_profile &prof, uint32_t x, uint32_t y, PathRng &rng, V3 &o, V3 &d) {
+  float wf = (float)prof.width, hf = (float)prof.height;
+  float ratio = wf / hf;
+  float sx = (float)x + rng.jitter(0);
+  sx = sx / wf * 2.0f - 1.0f;
+  sx *= std::tan(s.fov / 2.0f) * ratio;
+  float sy = (float)y + rng.jitter(1);
+  sy = 1.0f - sy / hf * 2.0f;
+  sy *= std::tan(s.fov / 2.0f);
+  V3 dir = normalize(v3(sx, sy, -1.0f));
+  const float *m = s.camera;  // column-major: column c at m[c*4..]
+  V3 c0 = v3(m[0], m[1], m[2]), c1 = v3(m[4], m[5], m[6]), c2 = v3(m[8], m[9], m[10]), c3 = v3(m[12], m[13], m[14]);
+  d = ((c0 * dir.x + c1 * dir.y) + c2 * dir.z) + c3 * 0.0f;
+  o = c3;
+}
+
+}  // namespace
+
+extern "C" {
+
+// triangle.rs:37-82 on one (ray, triangle) pair.  out4 = t,u,v,det.  Returns 1 on hit.
+int oracle_moller_trumbore(const float *ray6, const float *tri9, float *out4) {
+  float t = 0, u = 0, v = 0, det = 0;
+  bool hit = moller_trumbore(v3(ray6[0], ray6[1], ray6[2]), v3(ray6[3], ray6[4], ray6[5]), v3(tri9[0], tri9[1], tri9[2]),
+                             v3(tri9[3], tri9[4], tri9[5]), v3(tri9[6], tri9[7], tri9[8]), t, u, v, det);
+  out4[0] = t; out4[1] = u; out4[2] = v; out4[3] = det;
+  return hit ? 1 : 0;
+}
+
+void *oracle_scene_create(const pt_scene_desc *d) {
+  Scene *s = new Scene();
+  s->models.assign(d->models, d->models + d->n_models);
+  s->materials.assign(d->materials, d->materials + d->n_models);
+  s->pos.assign(d->tri_pos, d->tri_pos + d->n_tris * 9);
+  s->nrm.assign(d->tri_nrm, d->tri_nrm + d->n_tris * 9);
+  s->uv.assign(d->tri_uv, d->tri_uv + d->n_tris * 6);
+  s->texdata.resize(d->n_textures);
+  for (uint32_t i = 0; i < d->n_textures; ++i) {
+    const pt_texture &t = d->textures[i];
+    s->texdata[i].assign(t.data, t.data + (size_t)t.width * t.height * t.channels);
+    pt_texture c = t;
+    c.data = s->texdata[i].data();
+    s->textures.push_back(c);
+  }
+  s->lights.assign(d->lights, d->lights + d->n_lights);
+  std::memcpy(s->camera, d->camera, sizeof s->camera);
+  s->fov = d->fov;
+  s->background = v3(d->background[0], d->background[1], d->background[2]);
+  s->tri_model.resize(d->n_tris);
+  int32_t id = 0;
+  for (uint32_t m = 0; m < d->n_models; ++m) {
+    s->prim_base.push_back(id);
+    if (s->models[m].type == PT_MODEL_SPHERE) id += 2;
+    else {
+      for (uint32_t t = 0; t < s->models[m].n_tris; ++t) s->tri_model[s->models[m].first_tri + t] = (int32_t)m;
+      id += (int32_t)s->models[m].n_tris;
+    }
+  }
+  s->n_prims = id;
+  build_bvh(*s);
+  return s;
+}
+
+void oracle_scene_destroy(void *p) { delete (Scene *)p; }
+
+// ray_cast(...).first(): closest hit of each ray.  brute != 0 bypasses the BVH filter.
+int oracle_trace_closest(const void *sp, const float *rays, size_t n, pt_hit *out, int brute, int threads) {
+  const Scene &s = *(const Scene *)sp;
+  if (threads < 1) threads = 1;
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; ++t)
+    pool.emplace_back([&, t]() {
+      std::vector<Hit> hits;
+      for (size_t i = t; i < n; i += threads) {
+        const float *r = rays + i * 6;
+        ray_cast(s, v3(r[0], r[1], r[2]), v3(r[3], r[4], r[5]), hits, brute != 0);
+        if (hits.empty()) out[i] = pt_hit{-1, 0, 0, 0};
+        else out[i] = pt_hit{hits[0].prim_id, hits[0].dist, hits[0].u, hits[0].v};
+      }
+    });
+  for (auto &t : pool) t.join();
+  return 0;
+}
+
+// Full sorted hit list of ONE ray (debug / tie analysis).  Returns the number of hits.
+int oracle_trace_all(const void *sp, const float *ray6, pt_hit *out, int max_out, int brute) {
+  const Scene &s = *(const Scene *)sp;
+  std::vector<Hit> hits;
+  ray_cast(s, v3(ray6[0], ray6[1], ray6[2]), v3(ray6[3], ray6[4], ray6[5]), hits, brute != 0);
+  for (int i = 0; i < (int)hits.size() && i < max_out; ++i) out[i] = pt_hit{hits[i].prim_id, hits[i].dist, hits[i].u, hits[i].v};
+  return (int)hits.size();
+}
+
+// Directional shadow transmittance (renderer/mod.rs:291-297) with unit light colour.
+int oracle_trace_transmittance(const void *sp, const float *rays, size_t n, float *out, int brute) {
+  const Scene &s = *(const Scene *)sp;
+  std::vector<Hit> hits;
+  for (size_t i = 0; i < n; ++i) {
+    const float *r = rays + i * 6;
+    ray_cast(s, v3(r[0], r[1], r[2]), v3(r[3], r[4], r[5]), hits, brute != 0);
+    float tr = 1.0f;
+    for (const Hit &h : hits) {
+      tr *= 1.0f - hit_material_sample(s, h, h.model).opacity;
+      if (tr == 0.0f) break;
+    }
+    out[i] = tr;
+  }
+  return 0;
+}
+
+// Renderer::render.  Adds samples {sample_begin + k*sample_stride, k<n_samples} (0-based sample
+// index s; the reference's current_sample is s+1) into accum (W*H*3, caller-zeroed).
+// rng_mode 0 = ChaCha12 seeded (s+1) + i*profile.samples (mod.rs:110-112), 1 = Philox.
+// counters_out (optional): [extend_rays, shadow_rays].  Returns elapsed milliseconds.
+double oracle_render_accum(const void *sp, const pt_profile *prof, int rng_mode, uint64_t seed, uint32_t sample_begin,
+                           uint32_t sample_stride, uint32_t n_samples, int threads, int brute, float *accum,
+                           uint64_t *counters_out) {
+  const Scene &s = *(const Scene *)sp;
+  if (threads < 1) threads = 1;
+  const uint32_t W = prof->width, H = prof->height;
+  const uint64_t npix = (uint64_t)W * H;
+  std::vector<Counters> cnts(threads);
+  auto t0 = std::chrono::steady_clock::now();
+  for (uint32_t k = 0; k < n_samples; ++k) {  // one fork-join per sample pass, like mod.rs:105-106
+    const uint32_t sidx = sample_begin + k * sample_stride;
+    std::atomic<uint64_t> next{0};
+    std::vector<std::thread> pool;
+    for (int t = 0; t < threads; ++t)
+      pool.emplace_back([&, t]() {
+        std::vector<Hit> hits, tmp;
+        PathRng rng;
+        const uint64_t CH = 1024;
+        for (;;) {
+          uint64_t b = next.fetch_add(CH);
+          if (b >= npix) break;
+          uint64_t e = std::min(npix, b + CH);
+          for (uint64_t i = b; i < e; ++i) {
+            uint32_t x = (uint32_t)(i % W), y = (uint32_t)(i / W);
+            if (rng_mode == RNG_CHACHA) rng.init_chacha((uint64_t)(sidx + 1) + i * (uint64_t)prof->samples);
+            else rng.init_philox((uint32_t)i, sidx, seed);
+            V3 o, d;
+            raygen(s, *prof, x, y, rng, o, d);
+            V3 c = render_pixel(s, *prof, o, d, rng, brute != 0, hits, tmp, cnts[t]);
+            accum[i * 3 + 0] += c.x;
+            accum[i * 3 + 1] += c.y;
+            accum[i * 3 + 2] += c.z;
+          }
+        }
+      });
+    for (auto &t : pool) t.join();
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  if (counters_out) {
+    counters_out[0] = counters_out[1] = 0;
+    for (auto &c : cnts) { counters_out[0] += c.extend; counters_out[1] += c.shadow; }
+  }
+  return std::chrono::duration<double, std::milli>(t1 - t0).count();
+}
+
+// Final pass of Renderer::render (mod.rs:150-162) + post_processing (:335-353).
+int oracle_tonemap(const float *accum, uint32_t width, uint32_t height, uint32_t total_samples, int32_t tonemap_type,
+                   uint8_t *rgb8) {
+  const float n = (float)total_samples;
+  for (uint64_t i = 0; i < (uint64_t)width * height; ++i) {
+    V3 c = v3(accum[i * 3], accum[i * 3 + 1], accum[i * 3 + 2]) / n;
+    post_process(tonemap_type, c, rgb8 + i * 3);
+  }
+  return 0;
+}
+
+// Dumps the bounce-`bounce` rays (origin, direction) of a 1-spp Philox trace: the secondary-ray
+// batches of SURVEY.md §8(c).  rays_out: W*H*6 floats; valid_out: W*H bytes.
+int oracle_dump_bounce_rays(const void *sp, const pt_profile *prof, uint64_t seed, uint32_t bounce_wanted,
+                            float *rays_out, uint8_t *valid_out);
+}
+
+// Implemented separately to keep render_pixel identical to the reference's control flow.
+int oracle_dump_bounce_rays(const void *sp, const pt_profile *prof, uint64_t seed, uint32_t bounce_wanted,
+                            float *rays_out, uint8_t *valid_out) {
+  const Scene &s = *(const Scene *)sp;
+  const uint32_t W = prof->width, H = prof->height;
+  std::vector<Hit> hits;
+  for (uint64_t i = 0; i < (uint64_t)W * H; ++i) {
+    PathRng rng;
+    rng.init_philox((uint32_t)i, 0, seed);
+    V3 o, d;
+    raygen(s, *prof, (uint32_t)(i % W), (uint32_t)(i / W), rng, o, d);
+    valid_out[i] = 0;
+    for (uint32_t bounce = 0; bounce <= bounce_wanted; ++bounce) {
+      if (bounce == bounce_wanted) {
+        float r[6] = {o.x, o.y, o.z, d.x, d.y, d.z};
+        std::memcpy(rays_out + i * 6, r, sizeof r);
+        valid_out[i] = 1;
+        break;
+      }
+      ray_cast(s, o, d, hits, false);
+      if (hits.empty()) break;
+      const Hit &h = hits[0];
+      MaterialSample mat = hit_material_sample(s, h, h.model);
+      V3 n = hit_shading_normal(s, h, h.model);
+      CookTorrance brdf(mat);
+      V3 view = -1.0f * d;
+      V3 nd = brdf.sample(n, view, rng.bsdf(bounce, 0), rng.bsdf(bounce, 1));
+      o = h.position + h.normal * NORMAL_BIAS;
+      d = nd;
+      if (!(d.x == d.x && d.y == d.y && d.z == d.z)) break;
+    }
+  }
+  return 0;
+}

@@ -1,0 +1,103 @@
+"""ctypes binding of oracle/_build/liboracle.so (CPU oracle; test infrastructure only)."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from path_tracer_b200.abi import HIT_DTYPE, pt_hit, pt_profile, pt_scene_desc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_LIB = None
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        so = os.path.join(ROOT, "oracle", "_build", "liboracle.so")
+        if not os.path.exists(so):
+            subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")])
+        L = C.CDLL(so)
+        L.oracle_scene_create.restype = C.c_void_p
+        L.oracle_scene_create.argtypes = [C.POINTER(pt_scene_desc)]
+        L.oracle_scene_destroy.argtypes = [C.c_void_p]
+        L.oracle_moller_trumbore.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.oracle_trace_closest.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_int]
+        L.oracle_trace_all.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+        L.oracle_trace_transmittance.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int]
+        L.oracle_render_accum.restype = C.c_double
+        L.oracle_render_accum.argtypes = [C.c_void_p, C.POINTER(pt_profile), C.c_int, C.c_uint64, C.c_uint32,
+                                          C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.oracle_tonemap.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int32, C.c_void_p]
+        L.oracle_dump_bounce_rays.argtypes = [C.c_void_p, C.POINTER(pt_profile), C.c_uint64, C.c_uint32, C.c_void_p,
+                                              C.c_void_p]
+        _LIB = L
+    return _LIB
+
+
+def make_profile(width, height, samples, bounces, tonemap=1):
+    return pt_profile(width, height, bounces, samples, 0, tonemap)
+
+
+class OracleScene:
+    def __init__(self, arrays):
+        self.arrays = arrays
+        self._desc = arrays.to_desc()
+        self.h = lib().oracle_scene_create(C.byref(self._desc))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().oracle_scene_destroy(self.h)
+            self.h = None
+
+    def trace_closest(self, rays, brute=False, threads=8):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        out = np.zeros(rays.shape[0], HIT_DTYPE)
+        lib().oracle_trace_closest(self.h, rays.ctypes.data, rays.shape[0], out.ctypes.data, int(brute), threads)
+        return out
+
+    def trace_all(self, ray, brute=True, max_out=64):
+        ray = np.ascontiguousarray(ray, np.float32).reshape(6)
+        out = np.zeros(max_out, HIT_DTYPE)
+        n = lib().oracle_trace_all(self.h, ray.ctypes.data, out.ctypes.data, max_out, int(brute))
+        return out[:min(n, max_out)]
+
+    def trace_transmittance(self, rays, brute=False):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        out = np.zeros(rays.shape[0], np.float32)
+        lib().oracle_trace_transmittance(self.h, rays.ctypes.data, rays.shape[0], out.ctypes.data, int(brute))
+        return out
+
+    def render_accum(self, profile, rng_mode=1, seed=0, sample_begin=0, sample_stride=1, n_samples=None, threads=8,
+                     brute=False, return_counters=False):
+        n_samples = profile.samples if n_samples is None else n_samples
+        accum = np.zeros((profile.height, profile.width, 3), np.float32)
+        cnt = np.zeros(2, np.uint64)
+        ms = lib().oracle_render_accum(self.h, C.byref(profile), rng_mode, seed, sample_begin, sample_stride, n_samples,
+                                       threads, int(brute), accum.ctypes.data, cnt.ctypes.data)
+        if return_counters:
+            return accum, ms, cnt
+        return accum
+
+    def dump_bounce_rays(self, profile, bounce, seed=0):
+        n = profile.width * profile.height
+        rays = np.zeros((n, 6), np.float32)
+        valid = np.zeros(n, np.uint8)
+        lib().oracle_dump_bounce_rays(self.h, C.byref(profile), seed, bounce, rays.ctypes.data, valid.ctypes.data)
+        return rays[valid != 0]
+
+
+def tonemap(accum, total_samples, tonemap_type=1):
+    accum = np.ascontiguousarray(accum, np.float32)
+    h, w = accum.shape[:2]
+    out = np.zeros((h, w, 3), np.uint8)
+    lib().oracle_tonemap(accum.ctypes.data, w, h, total_samples, tonemap_type, out.ctypes.data)
+    return out
+
+
+def moller_trumbore(ray6, tri9):
+    ray6 = np.ascontiguousarray(ray6, np.float32)
+    tri9 = np.ascontiguousarray(tri9, np.float32)
+    out = np.zeros(4, np.float32)
+    hit = lib().oracle_moller_trumbore(ray6.ctypes.data, tri9.ctypes.data, out.ctypes.data)
+    return bool(hit), out
