@@ -1,0 +1,250 @@
+"""Host-side mirror of the reference's render interface over the C ABI (include/pt_b200.h).
+
+Reference surface mirrored (file:line relative to the reference root):
+  Profile / Profile::load        src/config/profile.rs:10-40, src/config/resolution.rs:4-16
+  load_internal(path) -> Scene   src/scene/mod.rs:16-22
+  Renderer::new / render         src/renderer/mod.rs:61-73, 76-169
+  ray_cast                       src/renderer/utils.rs:11-21 (first hit of the sorted list)
+There is no CPU fallback: every compute call goes through libpt_b200.so and raises PtError when the
+library or a CUDA device is missing.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from .abi import (HIT_DTYPE, TONEMAPS, SceneArrays, pt_hit, pt_profile, pt_scene_desc, pt_stats)
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+EXPORTS = ["pt_last_error", "pt_device_count", "pt_profile_default", "pt_profile_load_yaml", "pt_scene_load_isf",
+           "pt_scene_create", "pt_scene_synthetic", "pt_scene_destroy", "pt_scene_get_desc", "pt_scene_info",
+           "pt_trace_closest", "pt_trace_closest_device", "pt_trace_transmittance", "pt_render_accum_device",
+           "pt_tonemap_device", "pt_render", "pt_write_png", "pt_read_png", "pt_free"]
+
+
+class PtError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("pt_b200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+def lib():
+    """dlopen path-tracer_b200/libpt_b200.so (built in-tree by csrc/Makefile); fails loudly when missing."""
+    global _LIB
+    if _LIB is None:
+        so = os.path.join(_HERE, "libpt_b200.so")
+        if not os.path.exists(so):
+            raise PtError(-4, "libpt_b200.so not built: run `python __graft_entry__.py` (no CPU fallback exists)")
+        L = C.CDLL(so)
+        for name in EXPORTS:
+            getattr(L, name)  # AttributeError if a declared symbol is missing
+        L.pt_last_error.restype = C.c_char_p
+        vp, u32, u64 = C.c_void_p, C.c_uint32, C.c_uint64
+        L.pt_profile_default.argtypes = [C.POINTER(pt_profile)]
+        L.pt_profile_load_yaml.argtypes = [C.c_char_p, C.POINTER(pt_profile)]
+        L.pt_scene_load_isf.argtypes = [C.c_char_p, C.c_int, C.POINTER(vp)]
+        L.pt_scene_create.argtypes = [C.POINTER(pt_scene_desc), C.c_int, C.POINTER(vp)]
+        L.pt_scene_synthetic.argtypes = [C.c_char_p, u64, u64, C.c_int, C.POINTER(vp)]
+        L.pt_scene_destroy.argtypes = [vp]
+        L.pt_scene_destroy.restype = None
+        L.pt_scene_get_desc.argtypes = [vp, C.POINTER(pt_scene_desc)]
+        L.pt_scene_info.argtypes = [vp, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]
+        L.pt_trace_closest.argtypes = [vp, vp, C.c_size_t, vp]
+        L.pt_trace_closest_device.argtypes = [vp, vp, C.c_size_t, vp, vp]
+        L.pt_trace_transmittance.argtypes = [vp, vp, C.c_size_t, vp]
+        L.pt_render_accum_device.argtypes = [vp, C.POINTER(pt_profile), u32, u32, u32, u64, vp, vp, C.POINTER(pt_stats)]
+        L.pt_tonemap_device.argtypes = [vp, u32, u32, u32, C.c_int32, vp, C.c_int, vp]
+        L.pt_render.argtypes = [vp, C.POINTER(pt_profile), u64, vp, vp, C.POINTER(pt_stats)]
+        L.pt_write_png.argtypes = [C.c_char_p, vp, u32, u32]
+        L.pt_read_png.argtypes = [C.c_char_p, u32, C.POINTER(u32), C.POINTER(u32), C.POINTER(C.POINTER(C.c_uint8))]
+        L.pt_free.argtypes = [vp]
+        L.pt_free.restype = None
+        _LIB = L
+    return _LIB
+
+
+def _check(rc):
+    if rc != 0:
+        raise PtError(rc, (lib().pt_last_error() or b"").decode("utf-8", "replace"))
+
+
+def device_count():
+    return lib().pt_device_count()
+
+
+class Profile:
+    """Render profile (config/profile.rs:10-25).  Defaults: 1920x1080, 4 bounces, 64 samples, FILMIC."""
+
+    def __init__(self, width=None, height=None, bounces=None, samples=None, tonemap=None):
+        self.c = pt_profile()
+        lib().pt_profile_default(C.byref(self.c))
+        if width is not None:
+            self.c.width = width
+        if height is not None:
+            self.c.height = height
+        if bounces is not None:
+            self.c.bounces = bounces
+        if samples is not None:
+            self.c.samples = samples
+        if tonemap is not None:
+            self.c.tonemap = TONEMAPS[tonemap] if isinstance(tonemap, str) else int(tonemap)
+
+    @classmethod
+    def load(cls, path):
+        p = cls()
+        _check(lib().pt_profile_load_yaml(os.fsencode(path), C.byref(p.c)))
+        return p
+
+    width = property(lambda s: s.c.width)
+    height = property(lambda s: s.c.height)
+    bounces = property(lambda s: s.c.bounces)
+    samples = property(lambda s: s.c.samples)
+    tonemap = property(lambda s: s.c.tonemap)
+
+
+class Scene:
+    """Immutable device-resident scene (scene::internal::Scene, scene/internal/mod.rs:26-51)."""
+
+    def __init__(self, handle, keep=None):
+        self.h = handle
+        self._keep = keep
+
+    @classmethod
+    def load(cls, path, device=0):
+        h = C.c_void_p()
+        _check(lib().pt_scene_load_isf(os.fsencode(path), device, C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def from_arrays(cls, arrays, device=0):
+        d = arrays.to_desc()
+        h = C.c_void_p()
+        _check(lib().pt_scene_create(C.byref(d), device, C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def synthetic(cls, recipe, n_tris, seed=0, device=0):
+        h = C.c_void_p()
+        _check(lib().pt_scene_synthetic(recipe.encode(), n_tris, seed, device, C.byref(h)))
+        return cls(h)
+
+    def close(self):
+        if self.h:
+            lib().pt_scene_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def info(self):
+        a, b, c, d = C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_uint64()
+        _check(lib().pt_scene_info(self.h, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
+        return dict(n_tris=a.value, n_prims=b.value, n_nodes=c.value, device_bytes=d.value)
+
+    def arrays(self):
+        """Host copy of the flat scene as a SceneArrays (used to hand the same scene to a checker)."""
+        d = pt_scene_desc()
+        _check(lib().pt_scene_get_desc(self.h, C.byref(d)))
+        sa = SceneArrays()
+        nt = d.n_tris
+        f = lambda p, n: np.ctypeslib.as_array(p, shape=(n,)).copy() if n else np.zeros(0, np.float32)
+        sa.tri_pos = f(d.tri_pos, nt * 9).reshape(-1, 9)
+        sa.tri_nrm = f(d.tri_nrm, nt * 9).reshape(-1, 9)
+        sa.tri_uv = f(d.tri_uv, nt * 6).reshape(-1, 6)
+        for i in range(d.n_models):
+            m, ma = d.models[i], d.materials[i]
+            sa.models.append(dict(type=m.type, first_tri=m.first_tri, n_tris=m.n_tris, center=list(m.center), radius=m.radius))
+            md = dict(albedo=list(ma.albedo), emissive=list(ma.emissive))
+            for k in ("opacity", "metalness", "roughness", "ior", "albedo_tex", "emissive_tex", "opacity_tex",
+                      "metalness_tex", "roughness_tex", "normal_tex"):
+                md[k] = getattr(ma, k)
+            sa.materials.append(md)
+        for i in range(d.n_textures):
+            t = d.textures[i]
+            sa.textures.append(np.ctypeslib.as_array(t.data, shape=(t.height, t.width, t.channels)).copy())
+        for i in range(d.n_lights):
+            l = d.lights[i]
+            sa.lights.append(dict(type=l.type, vec=list(l.vec), color=list(l.color), size=l.size))
+        sa.camera = np.array(list(d.camera), np.float32)
+        sa.fov = np.float32(d.fov)
+        sa.background = np.array(list(d.background), np.float32)
+        return sa
+
+    # ray_cast(scene, ray).first()  (renderer/utils.rs:11-21)
+    def trace_closest(self, rays):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        out = np.zeros(rays.shape[0], HIT_DTYPE)
+        _check(lib().pt_trace_closest(self.h, rays.ctypes.data, rays.shape[0], out.ctypes.data))
+        return out
+
+    def trace_transmittance(self, rays):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        out = np.zeros(rays.shape[0], np.float32)
+        _check(lib().pt_trace_transmittance(self.h, rays.ctypes.data, rays.shape[0], out.ctypes.data))
+        return out
+
+
+def load_internal(path, device=0):
+    """scene::load_internal (src/scene/mod.rs:16-22)."""
+    return Scene.load(path, device)
+
+
+class RenderConfig:
+    """Subset of config::RenderConfig (src/config/mod.rs:23-42) that affects rendering."""
+
+    def __init__(self, quiet=True, viewer=False, seed=0):
+        self.quiet, self.viewer, self.seed = quiet, viewer, seed
+
+
+class Renderer:
+    """Renderer::new(&config, profile) / render(&scene) -> RgbImage (src/renderer/mod.rs:61-169)."""
+
+    def __init__(self, config=None, profile=None):
+        self.config = config or RenderConfig()
+        self.profile = profile or Profile()
+        self.last_stats = None
+        self.last_accum = None
+
+    def render(self, scene, keep_accum=False):
+        p = self.profile.c
+        rgb = np.zeros((p.height, p.width, 3), np.uint8)
+        accum = np.zeros((p.height, p.width, 3), np.float32) if keep_accum else None
+        st = pt_stats()
+        _check(lib().pt_render(scene.h, C.byref(p), self.config.seed, rgb.ctypes.data,
+                               accum.ctypes.data if keep_accum else None, C.byref(st)))
+        self.last_stats = st.as_dict()
+        self.last_accum = accum
+        return rgb
+
+
+def render_accum_device(scene, profile, accum_ptr, sample_begin=0, sample_stride=1, n_samples=None, seed=0, stream=None,
+                        want_stats=True):
+    """pt_render_accum_device on a raw device pointer (e.g. torch_tensor.data_ptr()); returns stats dict or None."""
+    n = profile.samples if n_samples is None else n_samples
+    st = pt_stats()
+    _check(lib().pt_render_accum_device(scene.h, C.byref(profile.c), sample_begin, sample_stride, n, seed, accum_ptr,
+                                        stream, C.byref(st) if want_stats else None))
+    return st.as_dict() if want_stats else None
+
+
+def tonemap_device(accum_ptr, width, height, total_samples, tonemap, rgb8_ptr, device=0, stream=None):
+    _check(lib().pt_tonemap_device(accum_ptr, width, height, total_samples, tonemap, rgb8_ptr, device, stream))
+
+
+def write_png(path, rgb):
+    rgb = np.ascontiguousarray(rgb, np.uint8)
+    _check(lib().pt_write_png(os.fsencode(path), rgb.ctypes.data, rgb.shape[1], rgb.shape[0]))
+
+
+def read_png(path, channels=3):
+    w, h = C.c_uint32(), C.c_uint32()
+    p = C.POINTER(C.c_uint8)()
+    _check(lib().pt_read_png(os.fsencode(path), channels, C.byref(w), C.byref(h), C.byref(p)))
+    arr = np.ctypeslib.as_array(p, shape=(h.value, w.value, channels)).copy()
+    lib().pt_free(p)
+    return arr

@@ -1,0 +1,118 @@
+// cli.cpp — `path-tracer` command line.  Mirrors the reference's clap surface (src/config/mod.rs:14-52) and
+// run_render (src/main.rs:32-52): `path-tracer render <input> [-o FILE|$OUTPUT] [-q] [-v] [--debug-textures]
+// [-p FILE|$PROFILE]`, errors printed to stderr with exit code 2 (main.rs:14-21).  Additive flags: --seed,
+// --stats.  The SFML viewer (renderer/viewer.rs) needs a window + GL: unavailable on this box, -v is accepted
+// and ignored with a note.  `convert` (glTF -> isf, scene/gltf.rs) is outside the accelerated path.
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/pt_b200.h"
+
+static int usage(const char *msg) {
+  if (msg) std::fprintf(stderr, "error: %s\n\n", msg);
+  std::fprintf(stderr,
+               "Path-trace awesome things\n\nUsage: path-tracer <COMMAND>\n\nCommands:\n"
+               "  render   <INPUT> [-o, --output <OUTPUT>] [-q, --quiet] [-v, --viewer] [--debug-textures]\n"
+               "           [-p, --profile <PROFILE>] [--seed <N>] [--stats <FILE>]\n"
+               "  convert  <INPUT> <OUTPUT>   (not part of the B200 build)\n");
+  return 2;
+}
+
+int main(int argc, char **argv) {
+  if (argc < 2) return usage("a subcommand is required");
+  std::string cmd = argv[1];
+  if (cmd == "-h" || cmd == "--help") {
+    usage(nullptr);
+    return 0;
+  }
+  if (cmd == "convert") {
+    std::fprintf(stderr, "convert: the glTF -> isf converter is not part of the B200 render path\n");
+    return 2;
+  }
+  if (cmd != "render") return usage(("unrecognized subcommand '" + cmd + "'").c_str());
+
+  const char *env_out = std::getenv("OUTPUT");
+  const char *env_prof = std::getenv("PROFILE");
+  std::string input, output = env_out ? env_out : "render.png", profile_path = env_prof ? env_prof : "", stats_path;
+  bool quiet = false, viewer = false, debug_textures = false;
+  unsigned long long seed = 0;
+  for (int i = 2; i < argc; ++i) {
+    std::string a = argv[i];
+    auto need = [&](const char *name) -> const char * {
+      if (i + 1 >= argc) {
+        usage((std::string("a value is required for '") + name + "'").c_str());
+        std::exit(2);
+      }
+      return argv[++i];
+    };
+    if (a == "-o" || a == "--output") output = need("--output");
+    else if (a.rfind("--output=", 0) == 0) output = a.substr(9);
+    else if (a == "-p" || a == "--profile") profile_path = need("--profile");
+    else if (a.rfind("--profile=", 0) == 0) profile_path = a.substr(10);
+    else if (a == "-q" || a == "--quiet") quiet = true;
+    else if (a == "-v" || a == "--viewer") viewer = true;
+    else if (a == "--debug-textures") debug_textures = true;
+    else if (a == "--seed") seed = std::strtoull(need("--seed"), nullptr, 0);
+    else if (a == "--stats") stats_path = need("--stats");
+    else if (a == "-h" || a == "--help") {
+      usage(nullptr);
+      return 0;
+    } else if (!a.empty() && a[0] == '-') return usage(("unexpected argument '" + a + "'").c_str());
+    else if (input.empty()) input = a;
+    else return usage(("unexpected argument '" + a + "'").c_str());
+  }
+  if (input.empty()) return usage("the following required arguments were not provided: <INPUT>");
+
+  pt_profile prof;
+  pt_profile_default(&prof);
+  if (!profile_path.empty() && pt_profile_load_yaml(profile_path.c_str(), &prof) != PT_OK) {
+    std::fprintf(stderr, "%s\n", pt_last_error());
+    return 2;
+  }
+  if (debug_textures) {
+    std::fprintf(stderr, "--debug-textures: AOV pass not available in this build\n");
+    return 2;
+  }
+  if (viewer && !quiet) std::fprintf(stderr, "note: --viewer needs a window system (unavailable on this box); rendering headless\n");
+
+  auto t0 = std::chrono::steady_clock::now();
+  pt_scene *scene = nullptr;
+  if (pt_scene_load_isf(input.c_str(), 0, &scene) != PT_OK) {
+    std::fprintf(stderr, "%s\n", pt_last_error());
+    return 2;
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  if (!quiet) std::fprintf(stderr, "Rendering: %ux%u, %u samples, %u bounces\n", prof.width, prof.height, prof.samples, prof.bounces);
+  std::vector<uint8_t> rgb((size_t)prof.width * prof.height * 3);
+  pt_stats st{};
+  if (pt_render(scene, &prof, seed, rgb.data(), nullptr, &st) != PT_OK) {
+    std::fprintf(stderr, "%s\n", pt_last_error());
+    pt_scene_destroy(scene);
+    return 2;
+  }
+  auto t2 = std::chrono::steady_clock::now();
+  pt_scene_destroy(scene);
+  if (pt_write_png(output.c_str(), rgb.data(), prof.width, prof.height) != PT_OK) {
+    std::fprintf(stderr, "%s\n", pt_last_error());
+    return 2;
+  }
+  double load_s = std::chrono::duration<double>(t1 - t0).count(), render_s = std::chrono::duration<double>(t2 - t1).count();
+  if (!quiet) std::fprintf(stderr, "Done: %.0fs (load %.2fs, render %.3fs, %.1f Msamples/s)\n", load_s + render_s, load_s, render_s,
+                           st.ms_total > 0 ? (double)st.samples / st.ms_total / 1e3 : 0.0);
+  if (!stats_path.empty()) {
+    FILE *f = std::fopen(stats_path.c_str(), "w");
+    if (f) {
+      std::fprintf(f,
+                   "{\"samples\": %llu, \"extend_rays\": %llu, \"shadow_rays\": %llu, \"alpha_recasts\": %llu, "
+                   "\"kernel_launches\": %llu, \"ms_render\": %.3f, \"load_s\": %.3f}\n",
+                   (unsigned long long)st.samples, (unsigned long long)st.extend_rays, (unsigned long long)st.shadow_rays,
+                   (unsigned long long)st.alpha_recasts, (unsigned long long)st.kernel_launches, st.ms_total, load_s);
+      std::fclose(f);
+    }
+  }
+  return 0;
+}

@@ -1,0 +1,130 @@
+// device_scene.cuh — HBM layout of the immutable scene and of the wavefront path state.
+// All kernels are compiled with --fmad=false: the intersection and shading arithmetic must
+// round exactly like the reference's un-fused f32 Rust code (cgmath operand order).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ptb {
+
+// 48-byte intersection record, leaf order: three 128-bit loads per triangle test.
+//   a = (v0.xyz, global prim id)   b = (e1.xyz, original triangle index)   c = (e2.xyz, flags)
+// e1 = v1-v0 and e2 = v2-v0 are the f32 differences of triangle.rs:43-44, computed once.
+struct DevTri {
+  float4 a, b, c;
+};
+constexpr uint32_t TRI_FLAG_ALPHA = 1u;  // material can yield opacity < 1 (mod.rs:198-204)
+
+// 64-byte shading record, original triangle order (touched only for examined hits).
+struct DevTriShade {
+  float n0[3], n1[3], n2[3];
+  float uv0[2], uv1[2], uv2[2];
+  int32_t model;
+};
+
+struct DevSphere {
+  float cx, cy, cz, radius;
+  int32_t model;
+  int32_t prim_id;  // entry id; exit = prim_id + 1
+  uint32_t flags;
+  uint32_t pad;
+};
+
+struct DevTexture {
+  unsigned long long offset;  // into the texel pool
+  uint32_t width, height, channels, pad;
+};
+
+struct DevMaterial {
+  float albedo[3], emissive[3];
+  float opacity, metalness, roughness, ior;
+  int32_t albedo_tex, emissive_tex, opacity_tex, metalness_tex, roughness_tex, normal_tex;
+};
+
+struct DevLight {
+  int32_t type;
+  float vec[3];
+  float color[3];
+  float pad;
+};
+
+struct DevNode {  // == ptb::Bvh4Node, one 128-byte line
+  float4 lo_x, lo_y, lo_z, hi_x, hi_y, hi_z;
+  uint4 child;
+  uint4 pad;
+};
+
+struct DevScene {
+  const DevNode *nodes;
+  const DevTri *tris;
+  const DevTriShade *shade;
+  const DevSphere *spheres;
+  const DevMaterial *materials;
+  const DevTexture *textures;
+  const uint8_t *texels;
+  const DevLight *lights;
+  const float *tri_pos9;  // original-order positions; only uploaded when a normal map exists
+  uint32_t n_tris, n_spheres, n_lights, n_nodes;
+  uint32_t root_is_valid;
+  uint32_t any_alpha;  // some material may be non-opaque
+  float camera[16];
+  float fov;
+  float background[3];
+};
+
+// Internal hit record.  idx: -1 miss; else bits[29:0] = triangle index, or n_tris + 2*sphere + exit;
+// bit 30 = triangle back face (det < 0).  h = (dist, u, v, global prim id bits).
+struct HitRec {
+  float4 h;
+  int32_t idx;
+};
+constexpr int32_t HIT_BACKFACE = 0x40000000;
+constexpr int32_t HIT_INDEX_MASK = 0x3FFFFFFF;
+
+// One wave of paths, SoA.  Queue position q (compacted every bounce) owns ray/throughput;
+// `slot` = pixel + k*W*H (k-th sample of the wave) owns the radiance sum and the RNG key.
+struct WaveState {
+  float4 *ray_o[2];   // xyz origin
+  float4 *ray_d[2];   // xyz direction, w = slot (int bits)
+  float4 *thr[2];     // xyz throughput
+  float4 *hit;        // HitRec.h
+  int32_t *hit_idx;   // HitRec.idx
+  float4 *radiance;   // per slot: xyz sum of this path's contributions
+  // shadow queue (one entry per light per shaded hit with a non-zero unshadowed contribution)
+  float4 *sh_o;       // xyz origin, w = point-light distance (or -1 for directional)
+  float4 *sh_d;       // xyz direction, w = slot
+  float4 *sh_c;       // rgb unshadowed contribution, w = primary uv.x (NaN: primary hit is a sphere)
+  float4 *sh_p;       // xyz primary hit position, w = primary uv.y
+  uint32_t *counters; // see CTR_* below
+  uint32_t capacity;       // paths per wave
+  uint32_t shadow_capacity;
+};
+
+// counters[] layout (uint32): queue sizes are produced on the device and consumed by the next
+// persistent kernel, so the host never synchronises inside a frame.
+enum {
+  CTR_QUEUE0 = 0,      // size of path queue buffer 0
+  CTR_QUEUE1 = 1,      // size of path queue buffer 1
+  CTR_SHADOW = 2,      // size of the shadow queue
+  CTR_WORK_EXTEND = 3, // persistent work-fetch cursors
+  CTR_WORK_SHADE = 4,
+  CTR_WORK_SHADOW = 5,
+  CTR_PAD0 = 6,
+  CTR_PAD1 = 7,
+  CTR_STAT_EXTEND = 8,   // 64-bit statistics start here (pairs)
+  CTR_STAT_SHADOW = 10,
+  CTR_STAT_RECAST = 12,
+  CTR_COUNT = 16
+};
+
+struct WaveParams {
+  uint32_t width, height;
+  uint32_t bounces;
+  uint32_t spp_in_wave;    // samples of every pixel in this wave
+  uint32_t sample_first;   // sample index of wave-sample 0
+  uint32_t sample_stride;  // distance between consecutive wave samples
+  uint32_t seed_lo, seed_hi;
+  uint32_t n_paths;        // width*height*spp_in_wave
+};
+
+}  // namespace ptb

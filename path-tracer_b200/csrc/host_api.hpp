@@ -1,0 +1,18 @@
+// host_api.hpp — internal glue shared by the host translation units of libpt_b200.so.
+#pragma once
+#include <string>
+
+#include "scene_host.hpp"
+
+namespace ptb {
+void set_error(const char *fmt, ...);
+// Finalises `host`, builds the BVH, uploads to `device`.  Takes ownership of host.
+int scene_from_host(HostScene &&host, int device, pt_scene **out);
+// isf_loader.cpp: scene/mod.rs:16-22 + isf.rs serde schema.  Returns PT_OK or an error (message set).
+int load_isf_file(const char *path, HostScene &out);
+// png.cpp
+int png_read(const char *path, uint32_t channels_out, uint32_t *w, uint32_t *h, std::vector<uint8_t> &data);
+int png_write(const char *path, const uint8_t *rgb8, uint32_t w, uint32_t h);
+// synth.cpp
+int make_synthetic(const char *recipe, uint64_t n_tris, uint64_t seed, HostScene &out);
+}  // namespace ptb

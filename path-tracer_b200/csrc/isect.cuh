@@ -1,0 +1,226 @@
+// isect.cuh — device intersection + BVH4 traversal.
+//   Möller–Trumbore      reference scene/internal/triangle.rs:37-82   (bit-exact: un-fused, cgmath order)
+//   sphere quadratic     reference scene/internal/model.rs:26-64
+//   closest / all hits   reference renderer/utils.rs:11-21 (sorted all-hits list; we return list[k])
+// The box culling is a conservative filter only: results must equal brute force over all primitives
+// with the reference's stable (dist, push order) ordering == lexicographic (dist, global prim id).
+#pragma once
+#include <math_constants.h>
+
+#include "device_scene.cuh"
+
+namespace ptb {
+
+struct V3 {
+  float x, y, z;
+};
+__device__ __forceinline__ V3 mk3(float x, float y, float z) { return V3{x, y, z}; }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ V3 operator*(V3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
+__device__ __forceinline__ V3 operator*(float s, V3 a) { return {s * a.x, s * a.y, s * a.z}; }
+__device__ __forceinline__ V3 operator/(V3 a, float s) { return {a.x / s, a.y / s, a.z / s}; }
+__device__ __forceinline__ V3 operator-(V3 a) { return {-a.x, -a.y, -a.z}; }
+__device__ __forceinline__ V3 mul_el(V3 a, V3 b) { return {a.x * b.x, a.y * b.y, a.z * b.z}; }
+// cgmath: dot = (x*x' + y*y') + z*z'
+__device__ __forceinline__ float dot3(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+__device__ __forceinline__ V3 cross3(V3 a, V3 b) {
+  return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+}
+__device__ __forceinline__ float length3(V3 a) { return sqrtf(dot3(a, a)); }
+__device__ __forceinline__ V3 normalize3(V3 a) { return a * (1.0f / length3(a)); }
+
+struct Ray {
+  V3 o, d;
+};
+
+// Candidate key ordering of the reference's stable sort: (dist, global prim id).
+__device__ __forceinline__ bool key_less(float t, int id, float t2, int id2) { return t < t2 || (t == t2 && id < id2); }
+
+struct TraceState {
+  float best_t;
+  int best_id;
+  float u, v;
+  int idx;        // HitRec.idx encoding
+  uint32_t flags; // TRI_FLAG_* of the best hit
+};
+
+// triangle.rs:37-82 with precomputed edges.  Returns true and t,u,v,det on a hit.
+__device__ __forceinline__ bool moller_trumbore(const Ray &r, V3 v0, V3 e1, V3 e2, float &t, float &u, float &v,
+                                                float &det) {
+  V3 pvec = cross3(r.d, e2);
+  det = dot3(e1, pvec);
+  if (fabsf(det) < 0.000001f) return false;
+  float invdet = __frcp_rn(det);  // correctly rounded 1/det == Rust's `1. / det`
+  V3 tvec = r.o - v0;
+  u = dot3(tvec, pvec) * invdet;
+  if (!(u >= 0.0f && u <= 1.0f)) return false;
+  V3 qvec = cross3(tvec, e1);
+  v = dot3(r.d, qvec) * invdet;
+  if (v < 0.0f || u + v > 1.0f) return false;
+  t = dot3(e2, qvec) * invdet;
+  if (t < 0.000001f) return false;
+  return true;
+}
+
+// model.rs:26-64.  n_hits in {0,1,2}; dist[0] is the entry (or the only, exit) hit.
+// exit_only = 1 when the origin is inside (only the exit hit exists).
+__device__ __forceinline__ int sphere_hits(const Ray &r, const DevSphere &s, float dist[2], float tpar[2], int &exit_only) {
+  V3 c = mk3(s.cx, s.cy, s.cz);
+  V3 oc = r.o - c;
+  float a = dot3(r.d, r.d);
+  float b = 2.0f * dot3(oc, r.d);
+  float cc = dot3(oc, oc) - s.radius * s.radius;
+  float disc = b * b - 4.0f * a * cc;
+  if (disc < 0.0f || disc != disc) return 0;
+  float sq = sqrtf(disc);
+  float t1 = (-b - sq) / (2.0f * a);
+  float t2 = (-b + sq) / (2.0f * a);
+  if (t2 < 0.0f || t2 != t2) return 0;
+  V3 p2 = r.o + r.d * t2;
+  float d2 = length3(p2 - r.o);
+  if (t1 < 0.0f) {
+    exit_only = 1;
+    dist[0] = d2;
+    tpar[0] = t2;
+    return 1;
+  }
+  exit_only = 0;
+  V3 p1 = r.o + r.d * t1;
+  dist[0] = length3(p1 - r.o);
+  tpar[0] = t1;
+  dist[1] = d2;
+  tpar[1] = t2;
+  return 2;
+}
+
+// Reciprocal direction for the slab test, clamped to a finite magnitude so 0*inf never appears;
+// a clamped slab is [-huge, +huge] when the origin is inside it (conservative).
+__device__ __forceinline__ float safe_inv(float d) {
+  float ad = fabsf(d);
+  return ad < 1e-18f ? copysignf(1e18f, d) : 1.0f / d;
+}
+
+struct RayPre {
+  float ix, iy, iz;     // safe reciprocals
+  float prune_scale;    // slab-parameter bound = best key * prune_scale (non-unit directions, rounding margin)
+};
+
+__device__ __forceinline__ RayPre precompute(const Ray &r) {
+  RayPre p;
+  p.ix = safe_inv(r.d.x);
+  p.iy = safe_inv(r.d.y);
+  p.iz = safe_inv(r.d.z);
+  float len = length3(r.d);
+  // Triangle keys are the ray parameter t, sphere keys are Euclidean distances t*|d|: a bound that is
+  // valid for both is key*max(1, 1/|d|); 1.0002 absorbs rounding differences between slab and M-T.
+  float s = len > 0.0f ? fmaxf(1.0f, 1.0f / len) : CUDART_INF_F;
+  p.prune_scale = s * 1.0002f;
+  return p;
+}
+
+// Slab test of child k of a node; returns entry parameter or +inf when the ray misses the box.
+__device__ __forceinline__ float slab(float lox, float loy, float loz, float hix, float hiy, float hiz, const Ray &r,
+                                      const RayPre &p, float t_max) {
+  float t0x = (lox - r.o.x) * p.ix, t1x = (hix - r.o.x) * p.ix;
+  float t0y = (loy - r.o.y) * p.iy, t1y = (hiy - r.o.y) * p.iy;
+  float t0z = (loz - r.o.z) * p.iz, t1z = (hiz - r.o.z) * p.iz;
+  float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.0f));
+  float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
+  // conservative: widen the exit by a few ulps (Ize, "Robust BVH ray traversal") plus an absolute term
+  bool hit = tn <= tf * 1.000002f + 1e-7f && tn <= t_max;
+  return hit ? tn : CUDART_INF_F;
+}
+
+#define PTB_STACK 96
+
+#define PTB_CSWAP(ta, ra, tb, rb) \
+  if (tb < ta) {                  \
+    float _t = ta; ta = tb; tb = _t; \
+    uint32_t _r = ra; ra = rb; rb = _r; \
+  }
+
+// Intersect every primitive of a leaf; keep the smallest key above (t_lo, id_lo).
+__device__ __forceinline__ void leaf_closest(const DevScene &S, uint32_t ref, const Ray &r, float t_lo, int id_lo,
+                                             TraceState &st, float &t_prune, const RayPre &pre) {
+  if (ref & 0x40000000u) {
+    const DevSphere sp = S.spheres[ref & 0x3FFFFFFFu];
+    float dist[2], tp[2];
+    int exit_only = 0;
+    int n = sphere_hits(r, sp, dist, tp, exit_only);
+    for (int k = 0; k < n; ++k) {
+      int is_exit = (n == 1) ? exit_only : k;
+      int id = sp.prim_id + is_exit;
+      float t = dist[k];
+      if (!key_less(t_lo, id_lo, t, id)) continue;
+      if (key_less(t, id, st.best_t, st.best_id)) {
+        st.best_t = t; st.best_id = id; st.u = 0.f; st.v = 0.f;
+        st.idx = (int)(S.n_tris + 2u * (ref & 0x3FFFFFFFu) + (uint32_t)is_exit);
+        st.flags = sp.flags;
+        t_prune = t * pre.prune_scale;
+      }
+    }
+    return;
+  }
+  uint32_t first = (ref & 0x3FFFFFFFu) >> 3, count = (ref & 7u) + 1u;
+  for (uint32_t i = 0; i < count; ++i) {
+    const float4 *tp = reinterpret_cast<const float4 *>(S.tris + first + i);
+    float4 A = __ldg(tp), B = __ldg(tp + 1), C = __ldg(tp + 2);
+    float t, u, v, det;
+    if (!moller_trumbore(r, mk3(A.x, A.y, A.z), mk3(B.x, B.y, B.z), mk3(C.x, C.y, C.z), t, u, v, det)) continue;
+    int id = __float_as_int(A.w);
+    if (!key_less(t_lo, id_lo, t, id)) continue;
+    if (key_less(t, id, st.best_t, st.best_id)) {
+      st.best_t = t; st.best_id = id; st.u = u; st.v = v;
+      st.idx = __float_as_int(B.w) | (det < 0.0f ? HIT_BACKFACE : 0);
+      st.flags = __float_as_uint(C.w);
+      t_prune = t * pre.prune_scale;
+    }
+  }
+}
+
+// Smallest-key hit with key > (t_lo, id_lo); (t_lo, id_lo) = (-1, -1) for the first hit of the list.
+__device__ __forceinline__ void trace_closest(const DevScene &S, const Ray &r, float t_lo, int id_lo, TraceState &st) {
+  st.best_t = CUDART_INF_F;
+  st.best_id = 0x7FFFFFFF;
+  st.idx = -1;
+  st.u = st.v = 0.f;
+  st.flags = 0;
+  const RayPre pre = precompute(r);
+  float t_prune = CUDART_INF_F;
+  float stk_t[PTB_STACK];
+  uint32_t stk_r[PTB_STACK];
+  int sp = 0;
+  uint32_t cur = 0;  // root node
+  for (;;) {
+    if (!(cur & 0x80000000u)) {
+      const float4 *np = reinterpret_cast<const float4 *>(S.nodes + cur);
+      float4 lx = __ldg(np), ly = __ldg(np + 1), lz = __ldg(np + 2);
+      float4 hx = __ldg(np + 3), hy = __ldg(np + 4), hz = __ldg(np + 5);
+      uint4 ch = __ldg(reinterpret_cast<const uint4 *>(np + 6));
+      float t0 = ch.x == 0xFFFFFFFFu ? CUDART_INF_F : slab(lx.x, ly.x, lz.x, hx.x, hy.x, hz.x, r, pre, t_prune);
+      float t1 = ch.y == 0xFFFFFFFFu ? CUDART_INF_F : slab(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, r, pre, t_prune);
+      float t2 = ch.z == 0xFFFFFFFFu ? CUDART_INF_F : slab(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, r, pre, t_prune);
+      float t3 = ch.w == 0xFFFFFFFFu ? CUDART_INF_F : slab(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, r, pre, t_prune);
+      uint32_t r0 = ch.x, r1 = ch.y, r2 = ch.z, r3 = ch.w;
+      // sorting network, ascending entry distance
+      PTB_CSWAP(t0, r0, t1, r1) PTB_CSWAP(t2, r2, t3, r3) PTB_CSWAP(t0, r0, t2, r2) PTB_CSWAP(t1, r1, t3, r3)
+      PTB_CSWAP(t1, r1, t2, r2)
+      if (t3 < CUDART_INF_F && sp < PTB_STACK) { stk_t[sp] = t3; stk_r[sp] = r3; ++sp; }
+      if (t2 < CUDART_INF_F && sp < PTB_STACK) { stk_t[sp] = t2; stk_r[sp] = r2; ++sp; }
+      if (t1 < CUDART_INF_F && sp < PTB_STACK) { stk_t[sp] = t1; stk_r[sp] = r1; ++sp; }
+      if (t0 < CUDART_INF_F) { cur = r0; continue; }
+    } else {
+      leaf_closest(S, cur, r, t_lo, id_lo, st, t_prune, pre);
+    }
+    // pop the nearest pending entry that can still hold a better key
+    bool found = false;
+    while (sp > 0) {
+      --sp;
+      if (stk_t[sp] <= t_prune) { cur = stk_r[sp]; found = true; break; }
+    }
+    if (!found) break;
+  }
+}
+
+}  // namespace ptb

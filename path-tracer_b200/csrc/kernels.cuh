@@ -1,0 +1,15 @@
+// kernels.cuh — launchers of the wavefront kernels (definitions in kernels.cu).
+#pragma once
+#include "../../include/pt_b200.h"
+#include "device_scene.cuh"
+
+namespace ptb {
+void launch_trace_closest(const DevScene &S, const float *rays, uint32_t n, pt_hit *out, uint32_t *cursor, cudaStream_t st);
+void launch_trace_transmittance(const DevScene &S, const float *rays, uint32_t n, float *out, uint32_t *cursor, cudaStream_t st);
+void launch_raygen(const DevScene &S, const WaveParams &P, const WaveState &W, cudaStream_t st);
+void launch_extend(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st);
+void launch_shade(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st);
+void launch_shadow(const DevScene &S, const WaveState &W, cudaStream_t st);
+void launch_resolve(const WaveParams &P, const WaveState &W, float *accum, cudaStream_t st);
+void launch_tonemap(const float *accum, uint32_t npix, uint32_t total_samples, int tonemap, uint8_t *rgb8, cudaStream_t st);
+}  // namespace ptb

@@ -1,0 +1,531 @@
+// render.cu — device scene upload, wave scheduling and the C ABI for the traced/rendered paths.
+// Replaces Renderer::render (reference renderer/mod.rs:76-169): instead of `samples` rayon fork-joins over
+// pixels, whole waves of (pixel, sample) paths advance bounce by bounce through persistent kernels whose
+// queue sizes stay on the device (no host synchronisation inside a frame).
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "host_api.hpp"
+#include "kernels.cuh"
+
+namespace ptb {
+
+thread_local std::string g_last_error;
+void set_error(const char *fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_last_error = buf;
+}
+
+#define CUDA_TRY(expr)                                                                  \
+  do {                                                                                  \
+    cudaError_t _e = (expr);                                                            \
+    if (_e != cudaSuccess) {                                                            \
+      set_error("CUDA error %s at %s:%d (%s)", cudaGetErrorString(_e), __FILE__, __LINE__, #expr); \
+      return PT_ERR_CUDA;                                                               \
+    }                                                                                   \
+  } while (0)
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = false;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    ok = cudaSetDevice(dev) == cudaSuccess;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+}  // namespace ptb
+
+using namespace ptb;
+
+struct pt_scene {
+  HostScene host;
+  Bvh4 bvh;
+  int device = 0;
+  DevScene dev{};
+  std::vector<void *> allocs;
+  uint64_t device_bytes = 0;
+  double build_ms = 0;
+  // wave buffers, grown lazily and reused between renders (guarded: one render at a time per scene)
+  std::mutex mu;
+  WaveState wave{};
+  std::vector<void *> wave_allocs;
+  uint32_t *cursor = nullptr;  // work cursor of the trace entry points
+};
+
+namespace {
+
+template <typename T>
+int upload(pt_scene *sc, const std::vector<T> &v, const T **out) {
+  size_t bytes = std::max<size_t>(v.size(), 1) * sizeof(T);
+  void *p = nullptr;
+  CUDA_TRY(cudaMalloc(&p, bytes));
+  sc->allocs.push_back(p);
+  sc->device_bytes += bytes;
+  if (!v.empty()) CUDA_TRY(cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  *out = reinterpret_cast<const T *>(p);
+  return PT_OK;
+}
+
+bool material_may_be_transparent(const pt_material &m) { return !(m.opacity_tex < 0 && m.opacity >= 1.0f); }
+
+int build_device_scene(pt_scene *sc) {
+  HostScene &h = sc->host;
+  unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+  build_bvh4(h, sc->bvh, (int)std::min(hw, 32u));
+  if (sc->bvh.max_depth * 3 + 4 > 96) {
+    set_error("acceleration structure too deep (%d levels) for the traversal stack", sc->bvh.max_depth);
+    return PT_ERR_INVALID;
+  }
+  const uint32_t nt = (uint32_t)h.n_tris();
+  bool any_alpha = false, any_normal_map = false;
+  for (const pt_material &m : h.materials) {
+    any_alpha |= material_may_be_transparent(m);
+    any_normal_map |= m.normal_tex >= 0;
+  }
+  std::vector<DevTri> tris(sc->bvh.leaf_tris.size());
+  for (size_t i = 0; i < tris.size(); ++i) {
+    uint32_t t = sc->bvh.leaf_tris[i];
+    const float *p = &h.pos[(size_t)t * 9];
+    int model = h.tri_model[t];
+    int prim = h.prim_base[model] + (int)(t - h.models[model].first_tri);
+    uint32_t flags = material_may_be_transparent(h.materials[model]) ? TRI_FLAG_ALPHA : 0u;
+    DevTri d;
+    d.a = make_float4(p[0], p[1], p[2], 0.f);
+    d.b = make_float4(p[3] - p[0], p[4] - p[1], p[5] - p[2], 0.f);  // v0v1, triangle.rs:43
+    d.c = make_float4(p[6] - p[0], p[7] - p[1], p[8] - p[2], 0.f);  // v0v2, triangle.rs:44
+    std::memcpy(&d.a.w, &prim, 4);
+    std::memcpy(&d.b.w, &t, 4);
+    std::memcpy(&d.c.w, &flags, 4);
+    tris[i] = d;
+  }
+  std::vector<DevTriShade> shade(nt);
+  for (uint32_t t = 0; t < nt; ++t) {
+    DevTriShade s;
+    std::memcpy(s.n0, &h.nrm[(size_t)t * 9], 36);
+    std::memcpy(s.uv0, &h.uv[(size_t)t * 6], 24);
+    s.model = h.tri_model[t];
+    shade[t] = s;
+  }
+  std::vector<DevSphere> spheres;
+  for (int m : h.sphere_models) {
+    const pt_model &mo = h.models[m];
+    DevSphere s{mo.center[0], mo.center[1], mo.center[2], mo.radius, m, h.prim_base[m],
+                material_may_be_transparent(h.materials[m]) ? TRI_FLAG_ALPHA : 0u, 0u};
+    spheres.push_back(s);
+  }
+  std::vector<DevMaterial> mats(h.materials.size());
+  for (size_t i = 0; i < mats.size(); ++i) {
+    static_assert(sizeof(DevMaterial) == sizeof(pt_material), "layout");
+    std::memcpy(&mats[i], &h.materials[i], sizeof(pt_material));
+  }
+  std::vector<DevTexture> texs;
+  std::vector<uint8_t> texels;
+  for (size_t i = 0; i < h.textures.size(); ++i) {
+    DevTexture t{(unsigned long long)texels.size(), h.textures[i].width, h.textures[i].height, h.textures[i].channels, 0};
+    texels.insert(texels.end(), h.texdata[i].begin(), h.texdata[i].end());
+    while (texels.size() % 16) texels.push_back(0);
+    texs.push_back(t);
+  }
+  std::vector<DevLight> lights;
+  for (const pt_light &l : h.lights) {
+    DevLight d{l.type, {l.vec[0], l.vec[1], l.vec[2]}, {l.color[0], l.color[1], l.color[2]}, 0.f};
+    lights.push_back(d);
+  }
+  DevScene &D = sc->dev;
+  int rc;
+  static_assert(sizeof(DevNode) == sizeof(Bvh4Node), "node layout");
+  const Bvh4Node *dn = nullptr;
+  if ((rc = upload(sc, sc->bvh.nodes, &dn))) return rc;
+  D.nodes = reinterpret_cast<const DevNode *>(dn);
+  if ((rc = upload(sc, tris, &D.tris))) return rc;
+  if ((rc = upload(sc, shade, &D.shade))) return rc;
+  if ((rc = upload(sc, spheres, &D.spheres))) return rc;
+  if ((rc = upload(sc, mats, &D.materials))) return rc;
+  if ((rc = upload(sc, texs, &D.textures))) return rc;
+  if ((rc = upload(sc, texels, &D.texels))) return rc;
+  if ((rc = upload(sc, lights, &D.lights))) return rc;
+  D.tri_pos9 = nullptr;
+  if (any_normal_map)
+    if ((rc = upload(sc, h.pos, &D.tri_pos9))) return rc;
+  D.n_tris = nt;
+  D.n_spheres = (uint32_t)spheres.size();
+  D.n_lights = (uint32_t)lights.size();
+  D.n_nodes = (uint32_t)sc->bvh.nodes.size();
+  D.root_is_valid = 1;
+  D.any_alpha = any_alpha ? 1u : 0u;
+  std::memcpy(D.camera, h.camera, sizeof D.camera);
+  D.fov = h.fov;
+  std::memcpy(D.background, h.background, sizeof D.background);
+  void *cur = nullptr;
+  CUDA_TRY(cudaMalloc(&cur, 64));
+  sc->allocs.push_back(cur);
+  sc->cursor = reinterpret_cast<uint32_t *>(cur);
+  return PT_OK;
+}
+
+void free_wave(pt_scene *sc) {
+  for (void *p : sc->wave_allocs) cudaFree(p);
+  sc->wave_allocs.clear();
+  sc->wave = WaveState{};
+}
+
+template <typename T>
+int wave_alloc(pt_scene *sc, T **out, size_t count) {
+  void *p = nullptr;
+  CUDA_TRY(cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T)));
+  sc->wave_allocs.push_back(p);
+  *out = reinterpret_cast<T *>(p);
+  return PT_OK;
+}
+
+int ensure_wave(pt_scene *sc, uint32_t n_paths) {
+  uint32_t shadow_cap = n_paths * std::max(1u, sc->dev.n_lights);
+  if (sc->wave.capacity >= n_paths && sc->wave.shadow_capacity >= shadow_cap) return PT_OK;
+  free_wave(sc);
+  WaveState &W = sc->wave;
+  int rc;
+  for (int b = 0; b < 2; ++b) {
+    if ((rc = wave_alloc(sc, &W.ray_o[b], n_paths))) return rc;
+    if ((rc = wave_alloc(sc, &W.ray_d[b], n_paths))) return rc;
+    if ((rc = wave_alloc(sc, &W.thr[b], n_paths))) return rc;
+  }
+  if ((rc = wave_alloc(sc, &W.hit, n_paths))) return rc;
+  if ((rc = wave_alloc(sc, &W.hit_idx, n_paths))) return rc;
+  if ((rc = wave_alloc(sc, &W.radiance, n_paths))) return rc;
+  if ((rc = wave_alloc(sc, &W.sh_o, shadow_cap))) return rc;
+  if ((rc = wave_alloc(sc, &W.sh_d, shadow_cap))) return rc;
+  if ((rc = wave_alloc(sc, &W.sh_c, shadow_cap))) return rc;
+  if ((rc = wave_alloc(sc, &W.sh_p, shadow_cap))) return rc;
+  if ((rc = wave_alloc(sc, &W.counters, (size_t)CTR_COUNT))) return rc;
+  W.capacity = n_paths;
+  W.shadow_capacity = shadow_cap;
+  return PT_OK;
+}
+
+int no_device() {
+  set_error("scene was created host-only (device -1): no CPU fallback exists for tracing or rendering");
+  return PT_ERR_CUDA;
+}
+
+int check_profile(const pt_profile *p) {
+  if (!p || p->width == 0 || p->height == 0) {
+    set_error("profile resolution must be non-zero");
+    return PT_ERR_INVALID;
+  }
+  if ((uint64_t)p->width * p->height > (1ull << 28)) {
+    set_error("resolution too large");
+    return PT_ERR_INVALID;
+  }
+  if (p->tonemap < 0 || p->tonemap > 2 || p->brdf != PT_BRDF_COOK_TORRANCE) {
+    set_error("unknown tonemap or brdf");
+    return PT_ERR_INVALID;
+  }
+  return PT_OK;
+}
+
+}  // namespace
+
+namespace ptb {
+int scene_from_host(HostScene &&host, int device, pt_scene **out) {
+  if (!out) return PT_ERR_INVALID;
+  *out = nullptr;
+  std::string err = host.finalize();
+  if (!err.empty()) {
+    set_error("%s", err.c_str());
+    return PT_ERR_INVALID;
+  }
+  if (device == -1) {  // host-only scene: loaders / generators / introspection without a GPU
+    pt_scene *sc = new pt_scene();
+    sc->host = std::move(host);
+    sc->device = -1;
+    *out = sc;
+    return PT_OK;
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    set_error("no CUDA device available (this library has no CPU fallback)");
+    return PT_ERR_CUDA;
+  }
+  if (device < 0 || device >= ndev) {
+    set_error("device %d out of range (%d devices)", device, ndev);
+    return PT_ERR_INVALID;
+  }
+  DeviceGuard g(device);
+  pt_scene *sc = new pt_scene();
+  sc->host = std::move(host);
+  sc->device = device;
+  int rc = build_device_scene(sc);
+  if (rc != PT_OK) {
+    pt_scene_destroy(sc);
+    return rc;
+  }
+  *out = sc;
+  return PT_OK;
+}
+}  // namespace ptb
+
+extern "C" {
+
+const char *pt_last_error(void) { return g_last_error.c_str(); }
+
+int pt_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+int pt_scene_create(const pt_scene_desc *desc, int device, pt_scene **out) {
+  if (!desc || !out) {
+    set_error("null argument");
+    return PT_ERR_INVALID;
+  }
+  if (desc->n_models && (!desc->models || !desc->materials)) {
+    set_error("null model/material arrays");
+    return PT_ERR_INVALID;
+  }
+  HostScene h;
+  h.from_desc(*desc);
+  return scene_from_host(std::move(h), device, out);
+}
+
+void pt_scene_destroy(pt_scene *sc) {
+  if (!sc) return;
+  if (sc->device < 0) {
+    delete sc;
+    return;
+  }
+  DeviceGuard g(sc->device);
+  free_wave(sc);
+  for (void *p : sc->allocs) cudaFree(p);
+  delete sc;
+}
+
+int pt_scene_get_desc(const pt_scene *sc, pt_scene_desc *out) {
+  if (!sc || !out) return PT_ERR_INVALID;
+  sc->host.to_desc(*out);
+  return PT_OK;
+}
+
+int pt_scene_info(const pt_scene *sc, uint64_t *n_tris, uint64_t *n_prims, uint64_t *n_nodes, uint64_t *device_bytes) {
+  if (!sc) return PT_ERR_INVALID;
+  if (n_tris) *n_tris = sc->host.n_tris();
+  if (n_prims) *n_prims = (uint64_t)sc->host.n_prims;
+  if (n_nodes) *n_nodes = sc->bvh.nodes.size();
+  if (device_bytes) *device_bytes = sc->device_bytes;
+  return PT_OK;
+}
+
+int pt_trace_closest_device(const pt_scene *sc, const float *rays_dev, size_t n, pt_hit *out_dev, void *stream) {
+  if (!sc || (n && (!rays_dev || !out_dev)) || n > 0xFFFFFF00ull) {
+    set_error("bad argument");
+    return PT_ERR_INVALID;
+  }
+  if (n == 0) return PT_OK;
+  if (sc->device < 0) return no_device();
+  DeviceGuard g(sc->device);
+  launch_trace_closest(sc->dev, rays_dev, (uint32_t)n, out_dev, sc->cursor, (cudaStream_t)stream);
+  CUDA_TRY(cudaGetLastError());
+  return PT_OK;
+}
+
+int pt_trace_closest(const pt_scene *sc, const float *rays, size_t n, pt_hit *out) {
+  if (!sc || (n && (!rays || !out))) {
+    set_error("bad argument");
+    return PT_ERR_INVALID;
+  }
+  if (n == 0) return PT_OK;
+  if (sc->device < 0) return no_device();
+  DeviceGuard g(sc->device);
+  float *d_rays = nullptr;
+  pt_hit *d_out = nullptr;
+  CUDA_TRY(cudaMalloc(&d_rays, n * 6 * sizeof(float)));
+  if (cudaMalloc(&d_out, n * sizeof(pt_hit)) != cudaSuccess) {
+    cudaFree(d_rays);
+    set_error("out of device memory");
+    return PT_ERR_NOMEM;
+  }
+  cudaMemcpy(d_rays, rays, n * 6 * sizeof(float), cudaMemcpyHostToDevice);
+  int rc = pt_trace_closest_device(sc, d_rays, n, d_out, nullptr);
+  cudaError_t e = cudaMemcpy(out, d_out, n * sizeof(pt_hit), cudaMemcpyDeviceToHost);
+  cudaFree(d_rays);
+  cudaFree(d_out);
+  if (rc != PT_OK) return rc;
+  CUDA_TRY(e);
+  return PT_OK;
+}
+
+int pt_trace_transmittance(const pt_scene *sc, const float *rays, size_t n, float *out) {
+  if (!sc || (n && (!rays || !out)) || n > 0xFFFFFF00ull) {
+    set_error("bad argument");
+    return PT_ERR_INVALID;
+  }
+  if (n == 0) return PT_OK;
+  if (sc->device < 0) return no_device();
+  DeviceGuard g(sc->device);
+  float *d_rays = nullptr, *d_out = nullptr;
+  CUDA_TRY(cudaMalloc(&d_rays, n * 6 * sizeof(float)));
+  if (cudaMalloc(&d_out, n * sizeof(float)) != cudaSuccess) {
+    cudaFree(d_rays);
+    set_error("out of device memory");
+    return PT_ERR_NOMEM;
+  }
+  cudaMemcpy(d_rays, rays, n * 6 * sizeof(float), cudaMemcpyHostToDevice);
+  launch_trace_transmittance(sc->dev, d_rays, (uint32_t)n, d_out, sc->cursor, nullptr);
+  cudaError_t e = cudaMemcpy(out, d_out, n * sizeof(float), cudaMemcpyDeviceToHost);
+  cudaFree(d_rays);
+  cudaFree(d_out);
+  CUDA_TRY(e);
+  return PT_OK;
+}
+
+int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t sample_begin, uint32_t sample_stride,
+                           uint32_t n_samples, uint64_t seed, float *accum_dev, void *stream, pt_stats *stats_out) {
+  pt_scene *sc = const_cast<pt_scene *>(csc);
+  if (!sc || !accum_dev) {
+    set_error("null argument");
+    return PT_ERR_INVALID;
+  }
+  int rc = check_profile(prof);
+  if (rc) return rc;
+  if (sample_stride == 0) sample_stride = 1;
+  if (sc->device < 0) return no_device();
+  DeviceGuard g(sc->device);
+  std::lock_guard<std::mutex> lock(sc->mu);
+  cudaStream_t st = (cudaStream_t)stream;
+  const uint64_t npix = (uint64_t)prof->width * prof->height;
+  // wave size: as many samples per pixel as fit ~8M paths (amortises launch + tail, bounded memory)
+  const uint64_t target_paths = 8ull << 20;
+  uint32_t spw = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(n_samples ? n_samples : 1, target_paths / npix));
+  if (n_samples == 0) {
+    if (stats_out) std::memset(stats_out, 0, sizeof *stats_out);
+    return PT_OK;
+  }
+  if ((rc = ensure_wave(sc, (uint32_t)(npix * spw)))) return rc;
+  WaveState &W = sc->wave;
+  CUDA_TRY(cudaMemsetAsync(W.counters, 0, CTR_COUNT * sizeof(uint32_t), st));
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (stats_out) {
+    CUDA_TRY(cudaEventCreate(&e0));
+    CUDA_TRY(cudaEventCreate(&e1));
+    CUDA_TRY(cudaEventRecord(e0, st));
+  }
+  uint64_t launches = 0, n_ext = 0, n_shade = 0, n_shadow = 0;
+  for (uint32_t done = 0; done < n_samples; done += spw) {
+    WaveParams P;
+    P.width = prof->width;
+    P.height = prof->height;
+    P.bounces = prof->bounces;
+    P.spp_in_wave = std::min(spw, n_samples - done);
+    P.sample_first = sample_begin + done * sample_stride;
+    P.sample_stride = sample_stride;
+    P.seed_lo = (uint32_t)seed;
+    P.seed_hi = (uint32_t)(seed >> 32);
+    P.n_paths = (uint32_t)(npix * P.spp_in_wave);
+    launch_raygen(sc->dev, P, W, st);
+    ++launches;
+    for (uint32_t b = 0; b <= prof->bounces; ++b) {
+      launch_extend(sc->dev, P, W, b, st);
+      launch_shade(sc->dev, P, W, b, st);
+      launches += 2;
+      ++n_ext;
+      ++n_shade;
+      if (sc->dev.n_lights) {
+        launch_shadow(sc->dev, W, st);
+        ++launches;
+        ++n_shadow;
+      }
+    }
+    launch_resolve(P, W, accum_dev, st);
+    ++launches;
+  }
+  CUDA_TRY(cudaGetLastError());
+  if (stats_out) {
+    CUDA_TRY(cudaEventRecord(e1, st));
+    CUDA_TRY(cudaEventSynchronize(e1));
+    std::memset(stats_out, 0, sizeof *stats_out);
+    cudaEventElapsedTime(&stats_out->ms_total, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    uint32_t ctr[CTR_COUNT];
+    CUDA_TRY(cudaMemcpy(ctr, W.counters, sizeof ctr, cudaMemcpyDeviceToHost));
+    auto u64 = [&](int i) { return (uint64_t)ctr[i] | ((uint64_t)ctr[i + 1] << 32); };
+    stats_out->samples = npix * n_samples;
+    stats_out->extend_rays = u64(CTR_STAT_EXTEND);
+    stats_out->shadow_rays = u64(CTR_STAT_SHADOW);
+    stats_out->alpha_recasts = u64(CTR_STAT_RECAST);
+    stats_out->kernel_launches = launches;
+    stats_out->extend_launches = n_ext;
+    stats_out->shade_launches = n_shade;
+    stats_out->shadow_launches = n_shadow;
+  }
+  return PT_OK;
+}
+
+int pt_tonemap_device(const float *accum_dev, uint32_t width, uint32_t height, uint32_t total_samples, int32_t tonemap,
+                      uint8_t *rgb8_dev, int device, void *stream) {
+  if (!accum_dev || !rgb8_dev || width == 0 || height == 0 || tonemap < 0 || tonemap > 2) {
+    set_error("bad argument");
+    return PT_ERR_INVALID;
+  }
+  DeviceGuard g(device);
+  launch_tonemap(accum_dev, width * height, total_samples, tonemap, rgb8_dev, (cudaStream_t)stream);
+  CUDA_TRY(cudaGetLastError());
+  return PT_OK;
+}
+
+int pt_render(const pt_scene *sc, const pt_profile *prof, uint64_t seed, uint8_t *rgb8_out, float *accum_out,
+              pt_stats *stats_out) {
+  if (!sc || !rgb8_out) {
+    set_error("null argument");
+    return PT_ERR_INVALID;
+  }
+  int rc = check_profile(prof);
+  if (rc) return rc;
+  if (sc->device < 0) return no_device();
+  DeviceGuard g(sc->device);
+  const size_t npix = (size_t)prof->width * prof->height;
+  float *d_accum = nullptr;
+  uint8_t *d_rgb = nullptr;
+  CUDA_TRY(cudaMalloc(&d_accum, npix * 3 * sizeof(float)));
+  if (cudaMalloc(&d_rgb, npix * 3) != cudaSuccess) {
+    cudaFree(d_accum);
+    set_error("out of device memory");
+    return PT_ERR_NOMEM;
+  }
+  cudaMemset(d_accum, 0, npix * 3 * sizeof(float));
+  pt_stats local;
+  rc = pt_render_accum_device(sc, prof, 0, 1, prof->samples, seed, d_accum, nullptr, stats_out ? stats_out : &local);
+  if (rc == PT_OK) rc = pt_tonemap_device(d_accum, prof->width, prof->height, prof->samples, prof->tonemap, d_rgb, sc->device, nullptr);
+  cudaError_t e = cudaSuccess;
+  if (rc == PT_OK) {
+    e = cudaMemcpy(rgb8_out, d_rgb, npix * 3, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && accum_out) e = cudaMemcpy(accum_out, d_accum, npix * 3 * sizeof(float), cudaMemcpyDeviceToHost);
+  }
+  cudaFree(d_accum);
+  cudaFree(d_rgb);
+  if (rc != PT_OK) return rc;
+  CUDA_TRY(e);
+  return PT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,279 @@
+// shade.cuh — device material lookup, Cook-Torrance GGX, Philox RNG, tonemap.
+//   Material::get_*      reference scene/internal/material.rs:115-218
+//   MaterialSample       reference renderer/material_sample.rs:20-40
+//   Hit::new_triangle    reference renderer/hit.rs:100-137 (deferred here from the traversal)
+//   Hit::get_normal      reference renderer/hit.rs:55-82
+//   CookTorrance         reference renderer/brdf/cook_torrance.rs:19-183
+//   transform_to_world   reference renderer/brdf/mod.rs:35-48
+//   reflection           reference renderer/utils.rs:34-36
+//   tonemap              reference renderer/tonemap.rs:15-54
+// Operand order follows the Rust source so that, given equal random numbers, a path computes the
+// same f32 values as the reference up to the last-ulp differences of sinf/cosf/acosf/powf.
+#pragma once
+#include "isect.cuh"
+
+namespace ptb {
+
+#define PTB_PI 3.14159265358979323846f
+
+// ---------------- Philox4x32-10 (counter-based; replaces rand's ChaCha12 StdRng) ----------------
+// key = (pixel, sample), counter = (block, tag, seed_lo, seed_hi).  Draw names:
+//   tag 0 block 0: [jitter x, jitter y, -, -]
+//   tag b+1 block 0: [r1, r2, russian roulette, alpha draw 0] of bounce b
+//   tag b+1 block 1+(j-1)/4, lane (j-1)%4: alpha draw j >= 1
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+    uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+    c = make_uint4(hi1 ^ c.y ^ k0, lo1, hi0 ^ c.w ^ k1, lo0);
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  return c;
+}
+__device__ __forceinline__ float u32_to_unit(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }
+
+struct RngKey {
+  uint32_t pixel, sample, seed_lo, seed_hi;
+};
+__device__ __forceinline__ uint4 rng_block(const RngKey &k, uint32_t tag, uint32_t block) {
+  return philox4x32_10(make_uint4(block, tag, k.seed_lo, k.seed_hi), k.pixel, k.sample);
+}
+__device__ __forceinline__ float rng_alpha(const RngKey &k, uint32_t bounce, uint32_t j) {
+  if (j == 0) return u32_to_unit(rng_block(k, bounce + 1, 0).w);
+  uint4 b = rng_block(k, bounce + 1, 1 + (j - 1) / 4);
+  uint32_t l = (j - 1) & 3u;
+  return u32_to_unit(l == 0 ? b.x : l == 1 ? b.y : l == 2 ? b.z : b.w);
+}
+
+// ---------------- textures / materials ----------------
+// material.rs:115-130: nearest texel, repeat, truncation toward zero (Rust `as i64` saturates).
+__device__ __forceinline__ const uint8_t *get_pixel(const DevScene &S, int tex, float u, float v) {
+  const DevTexture t = S.textures[tex];
+  float cx = u * (float)t.width, cy = v * (float)t.height;
+  long long ix = (cx != cx) ? 0 : __float2ll_rz(cx);  // __float2ll_rz saturates like `as i64`
+  long long iy = (cy != cy) ? 0 : __float2ll_rz(cy);
+  long long w = t.width, h = t.height;
+  long long x = ix % w, y = iy % h;
+  if (x < 0) x += w;
+  if (y < 0) y += h;
+  return S.texels + t.offset + ((size_t)y * t.width + (size_t)x) * t.channels;
+}
+
+struct MatSample {
+  float metalness, roughness, opacity;
+  V3 albedo, emissive;
+};
+
+__device__ __forceinline__ float eval_opacity(const DevScene &S, int model, bool simple, float u, float v) {
+  const DevMaterial &m = S.materials[model];
+  if (!simple && m.opacity_tex >= 0) return (float)get_pixel(S, m.opacity_tex, u, v)[0] / 255.0f * m.opacity;
+  return m.opacity;
+}
+
+__device__ __forceinline__ MatSample material_sample(const DevScene &S, int model, bool simple, float u, float v) {
+  const DevMaterial &m = S.materials[model];
+  MatSample r;
+  V3 af = mk3(m.albedo[0], m.albedo[1], m.albedo[2]);
+  V3 ef = mk3(m.emissive[0], m.emissive[1], m.emissive[2]);
+  r.metalness = m.metalness;
+  float rough = m.roughness;
+  r.albedo = af;
+  r.emissive = ef;
+  r.opacity = m.opacity;
+  if (!simple) {
+    if (m.metalness_tex >= 0) r.metalness = (float)get_pixel(S, m.metalness_tex, u, v)[0] / 255.0f * m.metalness;
+    if (m.roughness_tex >= 0) rough = (float)get_pixel(S, m.roughness_tex, u, v)[0] / 255.0f * m.roughness;
+    if (m.albedo_tex >= 0) {
+      const uint8_t *p = get_pixel(S, m.albedo_tex, u, v);
+      r.albedo = mul_el(mk3(powf((float)p[0] / 255.0f, 2.2f), powf((float)p[1] / 255.0f, 2.2f),
+                            powf((float)p[2] / 255.0f, 2.2f)), af);
+    }
+    if (m.opacity_tex >= 0) r.opacity = (float)get_pixel(S, m.opacity_tex, u, v)[0] / 255.0f * m.opacity;
+    if (m.emissive_tex >= 0) {
+      const uint8_t *p = get_pixel(S, m.emissive_tex, u, v);
+      r.emissive = mul_el(mk3((float)p[0] / 255.0f, (float)p[1] / 255.0f, (float)p[2] / 255.0f), ef);
+    }
+  }
+  r.roughness = fmaxf(rough, 0.0001f);
+  return r;
+}
+
+// ---------------- surface reconstruction from a HitRec ----------------
+struct Surface {
+  V3 position;
+  V3 normal;       // "geometric" normal of the reference = interpolated vertex normal (un-normalised)
+  V3 shading_n;    // Hit::get_normal
+  float tu, tv;    // interpolated texture coordinates
+  int model;
+  bool is_sphere;
+};
+
+// hit.rs:60-69 + :116-127.  e1,e2 = triangle edges, d1,d2 = uv deltas.
+__device__ __forceinline__ V3 normal_from_map(V3 hit_normal, V3 e1, V3 e2, float d1x, float d1y, float d2x, float d2y,
+                                              const uint8_t *p) {
+  float f = 1.0f / (d1x * d2y - d2x * d1y);
+  V3 tangent = normalize3(mk3(f * (d2y * e1.x - d1y * e2.x), f * (d2y * e1.y - d1y * e2.y), f * (d2y * e1.z - d1y * e2.z)));
+  V3 nm = mk3((float)p[0] / 127.5f - 1.0f, (float)p[1] / 127.5f - 1.0f, (float)p[2] / 127.5f - 1.0f);
+  V3 bit = cross3(hit_normal, tangent);
+  V3 w = (tangent * nm.x + bit * nm.y) + hit_normal * nm.z;
+  return normalize3(w);
+}
+
+__device__ __forceinline__ Surface make_surface(const DevScene &S, const Ray &r, float dist, float bu, float bv, int idx) {
+  Surface sf;
+  uint32_t i = (uint32_t)(idx & HIT_INDEX_MASK);
+  if (i >= S.n_tris) {
+    uint32_t k = (i - S.n_tris) >> 1, is_exit = (i - S.n_tris) & 1u;
+    const DevSphere sp = S.spheres[k];
+    // model.rs:42-62: the hit point is recomputed from the quadratic root, not from `dist`
+    V3 c = mk3(sp.cx, sp.cy, sp.cz);
+    V3 oc = r.o - c;
+    float a = dot3(r.d, r.d);
+    float b = 2.0f * dot3(oc, r.d);
+    float cc = dot3(oc, oc) - sp.radius * sp.radius;
+    float sq = sqrtf(b * b - 4.0f * a * cc);
+    float t = is_exit ? (-b + sq) / (2.0f * a) : (-b - sq) / (2.0f * a);
+    V3 p = r.o + r.d * t;
+    V3 n = normalize3(p - c);
+    sf.position = p;
+    sf.normal = is_exit ? -n : n;
+    sf.shading_n = sf.normal;
+    sf.tu = sf.tv = 0.f;
+    sf.model = sp.model;
+    sf.is_sphere = true;
+    return sf;
+  }
+  const DevTriShade &ts = S.shade[i];
+  const float4 *q = reinterpret_cast<const float4 *>(&ts);
+  float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+  V3 n0 = mk3(q0.x, q0.y, q0.z), n1 = mk3(q0.w, q1.x, q1.y), n2 = mk3(q1.z, q1.w, q2.x);
+  float u0x = q2.y, u0y = q2.z, u1x = q2.w, u1y = q3.x, u2x = q3.y, u2y = q3.z;
+  sf.model = __float_as_int(q3.w);
+  sf.is_sphere = false;
+  sf.position = r.o + r.d * dist;
+  sf.normal = ((1.0f - bu - bv) * n0 + bu * n1) + bv * n2;
+  sf.tu = (u0x + bu * (u1x - u0x)) + bv * (u2x - u0x);
+  sf.tv = (u0y + bu * (u1y - u0y)) + bv * (u2y - u0y);
+  V3 n = sf.normal;
+  const DevMaterial &m = S.materials[sf.model];
+  if (m.normal_tex >= 0 && S.tri_pos9 != nullptr) {  // hit.rs:60-69 (tangent: hit.rs:116-127)
+    const float *pp = S.tri_pos9 + (size_t)i * 9;
+    V3 e1 = mk3(pp[3] - pp[0], pp[4] - pp[1], pp[5] - pp[2]);
+    V3 e2 = mk3(pp[6] - pp[0], pp[7] - pp[1], pp[8] - pp[2]);
+    n = normal_from_map(sf.normal, e1, e2, u1x - u0x, u1y - u0y, u2x - u0x, u2y - u0y,
+                        get_pixel(S, m.normal_tex, sf.tu, sf.tv));
+  }
+  if (idx & HIT_BACKFACE) n = -n;
+  sf.shading_n = n;
+  return sf;
+}
+
+// ---------------- Cook-Torrance (cook_torrance.rs) ----------------
+__device__ __forceinline__ float powi5(float a) {  // llvm.powi(x,5): r=a; a*=a; a*=a; r*=a
+  float a2 = a * a;
+  float a4 = a2 * a2;
+  return a * a4;
+}
+
+struct Brdf {
+  float metalness, roughness;
+  V3 albedo, emissive, f0, m;
+};
+
+__device__ __forceinline__ Brdf make_brdf(const MatSample &s) {
+  Brdf b;
+  b.metalness = s.metalness;
+  b.roughness = s.roughness;
+  b.albedo = s.albedo;
+  b.emissive = s.emissive;
+  b.f0 = mk3(0.04f, 0.04f, 0.04f) * (1.0f - s.metalness) + s.albedo * s.metalness;
+  b.m = mk3(0.f, 0.f, 0.f);
+  return b;
+}
+__device__ __forceinline__ V3 fresnel(const Brdf &b, float c) {
+  return b.f0 + mk3(1.0f - b.f0.x, 1.0f - b.f0.y, 1.0f - b.f0.z) * powi5(1.0f - c);
+}
+__device__ __forceinline__ float g1(float ndv, float k) { return ndv / (ndv * (1.0f - k) + k); }
+__device__ __forceinline__ float geometry(const Brdf &b, V3 n, V3 v, V3 l) {
+  float ndv = fmaxf(dot3(n, v), 0.0f), ndl = fmaxf(dot3(n, l), 0.0f);
+  float a1 = b.roughness + 1.0f;
+  float k = (a1 * a1) / 8.0f;
+  return g1(ndv, k) * g1(ndl, k);
+}
+__device__ __forceinline__ float ndf(const Brdf &b, V3 n, V3 h) {
+  float a = b.roughness * b.roughness, a2 = a * a;
+  float ndh = fmaxf(dot3(n, h), 0.0f);
+  float denom = (ndh * ndh) * (a2 - 1.0f) + 1.0f;
+  denom = PTB_PI * denom * denom;
+  return a2 / denom;
+}
+__device__ __forceinline__ V3 diffuse(const Brdf &b, V3 ks, V3 n, V3 l) {
+  V3 kd = mk3(1.0f - ks.x, 1.0f - ks.y, 1.0f - ks.z) * (1.0f - b.metalness);
+  V3 dif = mul_el(kd, b.albedo) / PTB_PI;
+  return dif * fmaxf(dot3(n, l), 0.0f);
+}
+__device__ __forceinline__ V3 transform_to_world(V3 vec, V3 n) {
+  V3 nt;
+  if (fabsf(n.x) > fabsf(n.y)) nt = mk3(n.z, 0.0f, -n.x) / sqrtf(n.x * n.x + n.z * n.z);
+  else nt = mk3(0.0f, -n.z, n.y) / sqrtf(n.y * n.y + n.z * n.z);
+  V3 nb = cross3(n, nt);
+  return mk3(vec.x * nb.x + vec.y * n.x + vec.z * nt.x, vec.x * nb.y + vec.y * n.y + vec.z * nt.y,
+             vec.x * nb.z + vec.y * n.z + vec.z * nt.z);
+}
+__device__ __forceinline__ V3 reflection(V3 i, V3 n) { return (2.0f * fmaxf(dot3(i, n), 0.0f)) * n - i; }
+
+__device__ __forceinline__ V3 brdf_sample(Brdf &b, V3 n, V3 v, float r1, float r2) {
+  float a = b.roughness * b.roughness, a2 = a * a;
+  float theta = acosf(sqrtf((1.0f - r1) / (r1 * (a2 - 1.0f) + 1.0f)));
+  float phi = 2.0f * PTB_PI * r2;
+  float st = sinf(theta);
+  V3 ml = normalize3(mk3(st * cosf(phi), cosf(theta), st * sinf(phi)));
+  b.m = normalize3(transform_to_world(ml, n));
+  return normalize3(reflection(v, b.m));
+}
+__device__ __forceinline__ V3 eval_direct(const Brdf &b, V3 n, V3 v, V3 l) {
+  V3 h = normalize3(v + l);
+  float d = ndf(b, n, h);
+  V3 f = fresnel(b, fmaxf(dot3(h, v), 0.0f));
+  float g = geometry(b, n, v, l);
+  V3 spec = ((d * f) * g) / fmaxf((4.0f * fmaxf(dot3(n, v), 0.0f)) * fmaxf(dot3(n, l), 0.0f), 0.0001f);
+  spec = spec * fmaxf(dot3(n, l), 0.0f);
+  return (diffuse(b, f, n, l) + spec) + b.emissive;
+}
+__device__ __forceinline__ V3 eval_indirect(const Brdf &b, V3 n, V3 v, V3 l) {
+  V3 h = normalize3(v + l);
+  V3 f = fresnel(b, fmaxf(dot3(h, v), 0.0f));
+  float g = geometry(b, n, v, l);
+  V3 spec = mk3(0.f, 0.f, 0.f);
+  if (dot3(n, l) > 0.0f) {
+    float num = fabsf(dot3(v, b.m));
+    float den = fabsf(dot3(v, n)) * fabsf(dot3(b.m, n));
+    spec = (f * g) * (num / den);
+  }
+  return diffuse(b, f, n, l) + spec;
+}
+
+// ---------------- tonemap + post_processing (tonemap.rs, mod.rs:335-353) ----------------
+__device__ __forceinline__ float clamp01_nan(float x) { return x != x ? x : (x < 0.0f ? 0.0f : (x > 1.0f ? 1.0f : x)); }
+__device__ __forceinline__ float tonemap1(int type, float c) {
+  if (type == 0) return c / (c + 1.0f);
+  if (type == 1) {
+    float x = fmaxf(c - 0.004f, 0.0f);
+    float num = x * (6.2f * x + 0.5f);
+    float den = x * (6.2f * x + 1.7f) + 0.06f;
+    return num / den;
+  }
+  float num = c * (2.51f * c + 0.03f);
+  float den = c * (2.43f * c + 0.59f) + 0.14f;
+  return clamp01_nan(num / den);
+}
+__device__ __forceinline__ uint8_t to_u8(float f) {  // Rust `as u8`: saturating, NaN -> 0
+  if (f != f) return 0;
+  if (f <= 0.0f) return 0;
+  if (f >= 255.0f) return 255;
+  return (uint8_t)f;
+}
+
+}  // namespace ptb
