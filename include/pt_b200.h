@@ -113,6 +113,15 @@ typedef struct {
   float t, u, v;
 } pt_hit;
 
+/* One bounce of one path (render_pixel, renderer/mod.rs:172-228), as recorded by pt_trace_paths. */
+typedef struct {
+  float ray_o[3], ray_d[3]; /* the segment cast at this bounce (mod.rs:182)                     */
+  int32_t prim_id;          /* hit accepted by the alpha walk (mod.rs:188-205), -1 = miss        */
+  float t;                  /* its Hit::get_dist                                                 */
+  float throughput[3];      /* after this bounce's update (mod.rs:271-274, roulette included)    */
+  float radiance[3];        /* `color` after this bounce (emissive + shadowed direct light)      */
+} pt_path_vertex;
+
 /* Counters of one render (reference-equivalent ray_cast invocations). */
 typedef struct {
   uint64_t samples;       /* W*H*spp rendered by this call                    */
@@ -161,6 +170,19 @@ int pt_trace_closest_device(const pt_scene *scene, const float *rays_dev, size_t
 /* Directional-light shadow semantics of get_light_info (renderer/mod.rs:291-297):
  * product over every hit of (1 - opacity(hit uv)); out: n floats. */
 int pt_trace_transmittance(const pt_scene *scene, const float *rays, size_t n, float *out);
+
+/* ---- Triangle::intersect (scene/internal/triangle.rs:37-82) on n independent (ray, triangle) pairs ---- */
+/* rays: n*6 host floats; tris: n*9 host floats (v0 v1 v2); out[i].prim_id = -1 miss, 0 front-face hit,
+ * 1 back-face hit (Hit::Triangle.is_backface); t,u,v as tested by triangle.rs:200-233. */
+int pt_triangle_intersect(const pt_scene *scene_or_null, int device, const float *rays, const float *tris, size_t n,
+                          pt_hit *out);
+
+/* ---- render_pixel (renderer/mod.rs:172-228), one recorded path per requested pixel ---- */
+/* Traces sample `sample` of each pixel in pixels[0..n_paths) with the profile's resolution/bounces and records
+ * every bounce: out holds n_paths*(bounces+1) vertices (path i at out[i*(bounces+1)]), counts[i] = vertices
+ * written.  Host pointers.  Lights are evaluated in file order. */
+int pt_trace_paths(const pt_scene *scene, const pt_profile *profile, const uint32_t *pixels, size_t n_paths,
+                   uint32_t sample, uint64_t seed, pt_path_vertex *out, uint32_t *counts);
 
 /* ---- Renderer::render (renderer/mod.rs:76-169) ---- */
 /* Renders samples {sample_begin + k*sample_stride | k in [0,n_samples)} of every pixel

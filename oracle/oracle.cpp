@@ -68,13 +68,31 @@ void light_info(const Scene &s, const pt_light &light, const Hit &hit, bool brut
 }
 
 // render_pixel, renderer/mod.rs:172-228 (+ compute_radiance :230-278 inlined)
+struct Recorder {  // optional per-bounce record (pt_path_vertex), filled by render_pixel
+  pt_path_vertex *out = nullptr;
+  uint32_t n = 0;
+  void put(V3 ro, V3 rd, int32_t prim, float t, V3 thr, V3 color) {
+    pt_path_vertex v;
+    v.ray_o[0] = ro.x; v.ray_o[1] = ro.y; v.ray_o[2] = ro.z;
+    v.ray_d[0] = rd.x; v.ray_d[1] = rd.y; v.ray_d[2] = rd.z;
+    v.prim_id = prim;
+    v.t = t;
+    v.throughput[0] = thr.x; v.throughput[1] = thr.y; v.throughput[2] = thr.z;
+    v.radiance[0] = color.x; v.radiance[1] = color.y; v.radiance[2] = color.z;
+    out[n++] = v;
+  }
+};
+
 V3 render_pixel(const Scene &s, const pt_profile &prof, V3 ro, V3 rd, PathRng &rng, bool brute, std::vector<Hit> &hits,
-                std::vector<Hit> &tmp, Counters &cnt) {
+                std::vector<Hit> &tmp, Counters &cnt, Recorder *rec = nullptr) {
   V3 color = v3(0, 0, 0), thr = v3(1, 1, 1);
   for (uint32_t bounce = 0; bounce < prof.bounces + 1; ++bounce) {
     ray_cast(s, ro, rd, hits, brute);
     ++cnt.extend;
-    if (hits.empty()) return color + mul_el(thr, s.background);
+    if (hits.empty()) {
+      if (rec) rec->put(ro, rd, -1, 0.0f, thr, color + mul_el(thr, s.background));
+      return color + mul_el(thr, s.background);
+    }
     const Hit *hit = nullptr;
     MaterialSample mat{};
     V3 normal{};
@@ -99,6 +117,9 @@ V3 render_pixel(const Scene &s, const pt_profile &prof, V3 ro, V3 rd, PathRng &r
       V3 rl = -1.0f * ldir;
       color = color + mul_el(mul_el(thr, brdf.eval_direct(normal, view, rl)), lr);
     }
+    const V3 seg_o = ro, seg_d = rd;
+    const int32_t seg_prim = hit->prim_id;
+    const float seg_t = hit->dist;
     if (bounce < prof.bounces) {
       V3 no = hit->position + hit->normal * NORMAL_BIAS;
       float r1 = rng.bsdf(bounce, 0);
@@ -112,12 +133,14 @@ V3 render_pixel(const Scene &s, const pt_profile &prof, V3 ro, V3 rd, PathRng &r
       ro = v3(0, 0, 0);
       rd = v3(0, 0, 0);
     }
-    if (dot(thr, thr) < 0.00001f) return color;
-    if (bounce > 3) {  // russian_roulette, utils.rs:23-31
+    bool stop = dot(thr, thr) < 0.00001f;
+    if (!stop && bounce > 3) {  // russian_roulette, utils.rs:23-31
       float p = rmax(rmax(thr.x, thr.y), thr.z);
       thr = thr * (1.0f / p);
-      if (rng.rr(bounce) > p) return color;
+      if (rng.rr(bounce) > p) stop = true;
     }
+    if (rec) rec->put(seg_o, seg_d, seg_prim, seg_t, thr, color);
+    if (stop) return color;
   }
   return color;
 }
@@ -280,6 +303,26 @@ double oracle_render_accum(const void *sp, const pt_profile *prof, int rng_mode,
     for (auto &c : cnts) { counters_out[0] += c.extend; counters_out[1] += c.shadow; }
   }
   return std::chrono::duration<double, std::milli>(t1 - t0).count();
+}
+
+// render_pixel with a per-bounce record (Philox streams), the checker of pt_trace_paths.
+int oracle_trace_paths(const void *sp, const pt_profile *prof, const uint32_t *pixels, size_t n_paths, uint32_t sample,
+                       uint64_t seed, int brute, pt_path_vertex *out, uint32_t *counts) {
+  const Scene &s = *(const Scene *)sp;
+  std::vector<Hit> hits, tmp;
+  Counters cnt;
+  std::memset(out, 0, n_paths * (prof->bounces + 1) * sizeof(pt_path_vertex));
+  for (size_t i = 0; i < n_paths; ++i) {
+    PathRng rng;
+    rng.init_philox(pixels[i], sample, seed);
+    V3 o, d;
+    raygen(s, *prof, pixels[i] % prof->width, pixels[i] / prof->width, rng, o, d);
+    Recorder rec;
+    rec.out = out + i * (prof->bounces + 1);
+    render_pixel(s, *prof, o, d, rng, brute != 0, hits, tmp, cnt, &rec);
+    counts[i] = rec.n;
+  }
+  return 0;
 }
 
 // Final pass of Renderer::render (mod.rs:150-162) + post_processing (:335-353).

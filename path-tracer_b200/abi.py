@@ -55,6 +55,15 @@ class pt_hit(C.Structure):
 HIT_DTYPE = np.dtype([("prim_id", "<i4"), ("t", "<f4"), ("u", "<f4"), ("v", "<f4")])
 
 
+class pt_path_vertex(C.Structure):
+    _fields_ = [("ray_o", C.c_float * 3), ("ray_d", C.c_float * 3), ("prim_id", C.c_int32), ("t", C.c_float),
+                ("throughput", C.c_float * 3), ("radiance", C.c_float * 3)]
+
+
+PATH_VERTEX_DTYPE = np.dtype([("ray_o", "<f4", 3), ("ray_d", "<f4", 3), ("prim_id", "<i4"), ("t", "<f4"),
+                              ("throughput", "<f4", 3), ("radiance", "<f4", 3)])
+
+
 class pt_stats(C.Structure):
     _fields_ = [("samples", C.c_uint64), ("extend_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
                 ("alpha_recasts", C.c_uint64), ("kernel_launches", C.c_uint64), ("ms_total", C.c_float),

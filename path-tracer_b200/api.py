@@ -13,14 +13,15 @@ import os
 
 import numpy as np
 
-from .abi import (HIT_DTYPE, TONEMAPS, SceneArrays, pt_hit, pt_profile, pt_scene_desc, pt_stats)
+from .abi import (HIT_DTYPE, PATH_VERTEX_DTYPE, TONEMAPS, SceneArrays, pt_hit, pt_profile, pt_scene_desc, pt_stats)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
 EXPORTS = ["pt_last_error", "pt_device_count", "pt_profile_default", "pt_profile_load_yaml", "pt_scene_load_isf",
            "pt_scene_create", "pt_scene_synthetic", "pt_scene_destroy", "pt_scene_get_desc", "pt_scene_info",
-           "pt_trace_closest", "pt_trace_closest_device", "pt_trace_transmittance", "pt_render_accum_device",
+           "pt_trace_closest", "pt_trace_closest_device", "pt_trace_transmittance", "pt_triangle_intersect",
+           "pt_trace_paths", "pt_render_accum_device",
            "pt_tonemap_device", "pt_render", "pt_write_png", "pt_read_png", "pt_free"]
 
 
@@ -54,6 +55,8 @@ def lib():
         L.pt_trace_closest.argtypes = [vp, vp, C.c_size_t, vp]
         L.pt_trace_closest_device.argtypes = [vp, vp, C.c_size_t, vp, vp]
         L.pt_trace_transmittance.argtypes = [vp, vp, C.c_size_t, vp]
+        L.pt_triangle_intersect.argtypes = [vp, C.c_int, vp, vp, C.c_size_t, vp]
+        L.pt_trace_paths.argtypes = [vp, C.POINTER(pt_profile), vp, C.c_size_t, u32, u64, vp, vp]
         L.pt_render_accum_device.argtypes = [vp, C.POINTER(pt_profile), u32, u32, u32, u64, vp, vp, C.POINTER(pt_stats)]
         L.pt_tonemap_device.argtypes = [vp, u32, u32, u32, C.c_int32, vp, C.c_int, vp]
         L.pt_render.argtypes = [vp, C.POINTER(pt_profile), u64, vp, vp, C.POINTER(pt_stats)]
@@ -187,6 +190,27 @@ class Scene:
         out = np.zeros(rays.shape[0], np.float32)
         _check(lib().pt_trace_transmittance(self.h, rays.ctypes.data, rays.shape[0], out.ctypes.data))
         return out
+
+
+    # render_pixel (renderer/mod.rs:172-228) with a per-bounce record
+    def trace_paths(self, profile, pixels, sample=0, seed=0):
+        """Returns (vertices[n_paths, bounces+1] of PATH_VERTEX_DTYPE, counts[n_paths])."""
+        pixels = np.ascontiguousarray(pixels, np.uint32)
+        out = np.zeros((len(pixels), profile.bounces + 1), PATH_VERTEX_DTYPE)
+        counts = np.zeros(len(pixels), np.uint32)
+        _check(lib().pt_trace_paths(self.h, C.byref(profile.c), pixels.ctypes.data, len(pixels), sample, seed,
+                                    out.ctypes.data, counts.ctypes.data))
+        return out, counts
+
+
+def triangle_intersect(rays, tris, device=0):
+    """Triangle::intersect (scene/internal/triangle.rs:37-82) on (ray, triangle) pairs; prim_id -1 miss / 0 front / 1 back."""
+    rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+    tris = np.ascontiguousarray(tris, np.float32).reshape(-1, 9)
+    assert len(rays) == len(tris)
+    out = np.zeros(len(rays), HIT_DTYPE)
+    _check(lib().pt_triangle_intersect(None, device, rays.ctypes.data, tris.ctypes.data, len(rays), out.ctypes.data))
+    return out
 
 
 def load_internal(path, device=0):

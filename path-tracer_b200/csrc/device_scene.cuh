@@ -69,6 +69,7 @@ struct DevScene {
   uint32_t any_alpha;  // some material may be non-opaque
   float camera[16];
   float fov;
+  float tan_half_fov;  // (fov / 2).tan() of mod.rs:117,121, evaluated once on the host
   float background[3];
 };
 

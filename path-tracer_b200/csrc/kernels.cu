@@ -8,11 +8,9 @@
 //   k_shadow   renderer/mod.rs:281-333
 //   k_resolve  renderer/mod.rs:130 ; k_tonemap renderer/mod.rs:150-162,335-353
 #include "kernels.cuh"
-#include "shade.cuh"
+#include "path.cuh"
 
 namespace ptb {
-
-constexpr float NORMAL_BIAS = 0.00001f;  // renderer/mod.rs:59
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
 __device__ __forceinline__ uint32_t lanemask_lt() {
@@ -43,18 +41,6 @@ __device__ __forceinline__ void stat_add(uint32_t *counters, int which, unsigned
   atomicAdd(reinterpret_cast<unsigned long long *>(counters + which), v);
 }
 
-// Opacity of an examined hit (Hit::get_material_sample(...).opacity, hit.rs:84-91).
-__device__ __forceinline__ float hit_opacity(const DevScene &S, int idx, float bu, float bv) {
-  uint32_t i = (uint32_t)(idx & HIT_INDEX_MASK);
-  if (i >= S.n_tris) return S.materials[S.spheres[(i - S.n_tris) >> 1].model].opacity;
-  const float4 *q = reinterpret_cast<const float4 *>(S.shade + i);
-  float4 q2 = __ldg(q + 2), q3 = __ldg(q + 3);
-  float u0x = q2.y, u0y = q2.z, u1x = q2.w, u1y = q3.x, u2x = q3.y, u2y = q3.z;
-  float tu = (u0x + bu * (u1x - u0x)) + bv * (u2x - u0x);
-  float tv = (u0y + bu * (u1y - u0y)) + bv * (u2y - u0y);
-  return eval_opacity(S, __float_as_int(q3.w), false, tu, tv);
-}
-
 // ------------------------------------------------------------------------------------------------
 // Fixed ray batch -> first element of ray_cast's sorted list (pt_trace_closest).
 __global__ void __launch_bounds__(128) k_trace_closest(const __grid_constant__ DevScene S, const float *__restrict__ rays,
@@ -77,78 +63,6 @@ __global__ void __launch_bounds__(128) k_trace_closest(const __grid_constant__ D
   }
 }
 
-// All-hits transmittance walk shared by k_shadow and k_trace_transmittance.
-//   limit < 0: directional light (every hit on the ray, occluder sampled at its own uv, mod.rs:291-297)
-//   limit >= 0: point light at distance `limit` from `pos`; occluders farther than the light are ignored and
-//   the occluder's material is sampled with the PRIMARY hit's uv/variant (mod.rs:319-329, puv.x NaN = sphere).
-__device__ __forceinline__ float trace_transmittance(const DevScene &S, const Ray &r, float limit, V3 pos, float pu,
-                                                     float pv) {
-  const RayPre pre = precompute(r);
-  const bool point = limit >= 0.0f;
-  float t_max = CUDART_INF_F;
-  if (point) {
-    float len = length3(r.d);
-    float bias = length3(r.o - pos);
-    t_max = len > 0.f ? (limit + bias) / len * 1.0002f + 1e-6f : CUDART_INF_F;
-  }
-  float tr = 1.0f;
-  uint32_t stk[PTB_STACK];
-  int sp = 0;
-  uint32_t cur = 0;
-  for (;;) {
-    if (!(cur & 0x80000000u)) {
-      const float4 *np = reinterpret_cast<const float4 *>(S.nodes + cur);
-      float4 lx = __ldg(np), ly = __ldg(np + 1), lz = __ldg(np + 2);
-      float4 hx = __ldg(np + 3), hy = __ldg(np + 4), hz = __ldg(np + 5);
-      uint4 ch = __ldg(reinterpret_cast<const uint4 *>(np + 6));
-      if (ch.x != 0xFFFFFFFFu && slab(lx.x, ly.x, lz.x, hx.x, hy.x, hz.x, r, pre, t_max) < CUDART_INF_F && sp < PTB_STACK) stk[sp++] = ch.x;
-      if (ch.y != 0xFFFFFFFFu && slab(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, r, pre, t_max) < CUDART_INF_F && sp < PTB_STACK) stk[sp++] = ch.y;
-      if (ch.z != 0xFFFFFFFFu && slab(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, r, pre, t_max) < CUDART_INF_F && sp < PTB_STACK) stk[sp++] = ch.z;
-      if (ch.w != 0xFFFFFFFFu && slab(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, r, pre, t_max) < CUDART_INF_F && sp < PTB_STACK) stk[sp++] = ch.w;
-    } else if (cur & 0x40000000u) {
-      const DevSphere s = S.spheres[cur & 0x3FFFFFFFu];
-      float dist[2], tp[2];
-      int exit_only = 0;
-      int nh = sphere_hits(r, s, dist, tp, exit_only);
-      for (int k = 0; k < nh; ++k) {
-        if (point) {
-          V3 p = r.o + r.d * tp[k];
-          if (length3(p - pos) > limit) continue;
-        }
-        // sphere occluder: own variant is "simple"; with a point light the primary's variant decides,
-        // but a sphere's material has no texture-dependent difference unless the primary is a triangle
-        float op = point ? eval_opacity(S, s.model, pu != pu, pu, pv) : S.materials[s.model].opacity;
-        tr *= 1.0f - op;
-      }
-    } else {
-      uint32_t first = (cur & 0x3FFFFFFFu) >> 3, count = (cur & 7u) + 1u;
-      for (uint32_t i = 0; i < count; ++i) {
-        const float4 *tp = reinterpret_cast<const float4 *>(S.tris + first + i);
-        float4 A = __ldg(tp), B = __ldg(tp + 1), C = __ldg(tp + 2);
-        float t, u, v, det;
-        if (!moller_trumbore(r, mk3(A.x, A.y, A.z), mk3(B.x, B.y, B.z), mk3(C.x, C.y, C.z), t, u, v, det)) continue;
-        int tri = __float_as_int(B.w);
-        float op;
-        if (point) {
-          V3 p = r.o + r.d * t;
-          if (length3(p - pos) > limit) continue;
-          op = eval_opacity(S, S.shade[tri].model, pu != pu, pu, pv);
-        } else if (__float_as_uint(C.w) & TRI_FLAG_ALPHA) {
-          op = hit_opacity(S, tri, u, v);
-        } else {
-          op = S.materials[S.shade[tri].model].opacity;
-        }
-        tr *= 1.0f - op;
-        if (tr == 0.0f) return 0.0f;
-      }
-    }
-    if (tr == 0.0f) return 0.0f;
-    if (sp == 0) break;
-    cur = stk[--sp];
-  }
-  return tr;
-}
-
 __global__ void __launch_bounds__(128) k_trace_transmittance(const __grid_constant__ DevScene S,
                                                              const float *__restrict__ rays, uint32_t n,
                                                              float *__restrict__ out, uint32_t *cursor) {
@@ -164,16 +78,6 @@ __global__ void __launch_bounds__(128) k_trace_transmittance(const __grid_consta
 }
 
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ RngKey make_key(const WaveParams &P, uint32_t slot) {
-  uint32_t npix = P.width * P.height;
-  RngKey k;
-  k.pixel = slot % npix;
-  k.sample = P.sample_first + (slot / npix) * P.sample_stride;
-  k.seed_lo = P.seed_lo;
-  k.seed_hi = P.seed_hi;
-  return k;
-}
-
 // raygen: one thread per slot; writes queue buffer 0 in slot order (already compact).
 __global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
                                                 WaveState W) {
@@ -183,31 +87,14 @@ __global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene
     W.counters[CTR_WORK_EXTEND] = 0;
   }
   if (slot >= P.n_paths) return;
-  RngKey key = make_key(P, slot);
-  uint32_t x = key.pixel % P.width, y = key.pixel / P.width;
-  uint4 rb = rng_block(key, 0, 0);
-  float wf = (float)P.width, hf = (float)P.height;
-  float ratio = wf / hf;
-  float tn = tanf(S.fov / 2.0f);
-  float sx = (float)x + u32_to_unit(rb.x);
-  sx = sx / wf * 2.0f - 1.0f;
-  sx *= tn * ratio;
-  float sy = (float)y + u32_to_unit(rb.y);
-  sy = 1.0f - sy / hf * 2.0f;
-  sy *= tn;
-  V3 dir = normalize3(mk3(sx, sy, -1.0f));
-  const float *m = S.camera;
-  V3 c0 = mk3(m[0], m[1], m[2]), c1 = mk3(m[4], m[5], m[6]), c2 = mk3(m[8], m[9], m[10]), c3 = mk3(m[12], m[13], m[14]);
-  V3 d = ((c0 * dir.x + c1 * dir.y) + c2 * dir.z) + c3 * 0.0f;
-  W.ray_o[0][slot] = make_float4(c3.x, c3.y, c3.z, 0.f);
-  W.ray_d[0][slot] = make_float4(d.x, d.y, d.z, __int_as_float((int)slot));
+  Ray r = generate_ray(S, P, make_key(P, slot));
+  W.ray_o[0][slot] = make_float4(r.o.x, r.o.y, r.o.z, 0.f);
+  W.ray_d[0][slot] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float((int)slot));
   W.thr[0][slot] = make_float4(1.f, 1.f, 1.f, 0.f);
   W.radiance[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
-// extend: closest accepted hit of every queued ray.  The alpha walk of render_pixel (mod.rs:188-205) is done
-// here by re-casting from the rejected hit's key: accept the first hit with opacity >= 1 or a winning draw,
-// else the farthest examined hit.
+// extend: closest accepted hit (alpha walk included) of every queued ray.
 __global__ void __launch_bounds__(128) k_extend(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
                                                 WaveState W, uint32_t bounce) {
   const uint32_t in = bounce & 1u, outb = in ^ 1u;
@@ -228,23 +115,7 @@ __global__ void __launch_bounds__(128) k_extend(const __grid_constant__ DevScene
     r.o = mk3(o4.x, o4.y, o4.z);
     r.d = mk3(d4.x, d4.y, d4.z);
     TraceState st;
-    trace_closest(S, r, -1.0f, -1, st);
-    if (S.any_alpha && st.idx >= 0 && (st.flags & TRI_FLAG_ALPHA)) {
-      RngKey key = make_key(P, (uint32_t)__float_as_int(d4.w));
-      uint32_t j = 0;
-      for (;;) {
-        float op = hit_opacity(S, st.idx, st.u, st.v);
-        if (op >= 1.0f) break;
-        if (op > 0.001f) {
-          if (rng_alpha(key, bounce, j++) < op) break;
-        }
-        TraceState nx;
-        trace_closest(S, r, st.best_t, st.best_id, nx);
-        ++recasts;
-        if (nx.idx < 0) break;  // nothing behind: the last examined hit is shaded
-        st = nx;
-      }
-    }
+    extend_ray(S, make_key(P, (uint32_t)__float_as_int(d4.w)), bounce, r, st, recasts);
     W.hit[q] = make_float4(st.best_t, st.u, st.v, __int_as_float(st.best_id));
     W.hit_idx[q] = st.idx;
   }
@@ -266,12 +137,9 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DevScene 
     uint32_t q = fetch_work(&W.counters[CTR_WORK_SHADE]);
     if (__all_sync(0xffffffffu, q >= n)) break;
     const bool active = q < n;
-    bool alive = false;
-    bool lit = false;  // hit a surface (lights are evaluated)
     Ray r{};
-    V3 thr{}, rad{}, view{};
-    Surface sf{};
-    Brdf brdf{};
+    V3 thr{}, rad{};
+    ShadeCtx ctx{};
     uint32_t slot = 0;
     if (active) {
       float4 o4 = W.ray_o[in][q], d4 = W.ray_d[in][q], t4 = W.thr[in][q], h4 = W.hit[q];
@@ -282,78 +150,109 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DevScene 
       thr = mk3(t4.x, t4.y, t4.z);
       float4 r4 = W.radiance[slot];
       rad = mk3(r4.x, r4.y, r4.z);
-      if (idx < 0) {
-        rad = rad + mul_el(thr, mk3(S.background[0], S.background[1], S.background[2]));  // mod.rs:184-186
-      } else {
-        lit = true;
-        sf = make_surface(S, r, h4.x, h4.y, h4.z, idx);
-        MatSample ms = material_sample(S, sf.model, sf.is_sphere, sf.tu, sf.tv);
-        brdf = make_brdf(ms);
-        view = -1.0f * r.d;
-        rad = rad + mul_el(thr, ms.emissive);  // mod.rs:245
-      }
+      shade_begin(S, r, h4.x, h4.y, h4.z, idx, thr, rad, ctx);
     }
     // next-event estimation set-up: one shadow-queue entry per light (mod.rs:248-262)
     for (uint32_t li = 0; li < S.n_lights; ++li) {
       bool want = false;
       V3 so{}, sd{}, c{};
       float limit = -1.0f;
-      if (lit) {
-        const DevLight L = S.lights[li];
-        V3 lc = mk3(L.color[0], L.color[1], L.color[2]);
-        V3 dir;
-        if (L.type == PT_LIGHT_DIRECTIONAL) {
-          dir = mk3(L.vec[0], L.vec[1], L.vec[2]);
-        } else {
-          V3 dv = sf.position - mk3(L.vec[0], L.vec[1], L.vec[2]);
-          limit = length3(dv);
-          dir = normalize3(dv);
-          float dissipation = 4.0f * PTB_PI * limit * limit;
-          lc = lc / dissipation;
-        }
-        sd = -1.0f * dir;
-        so = sf.position + sf.normal * NORMAL_BIAS;
-        c = mul_el(mul_el(thr, eval_direct(brdf, sf.shading_n, view, sd)), lc);
-        bool lzero = lc.x == 0.0f && lc.y == 0.0f && lc.z == 0.0f;
-        bool czero = c.x == 0.0f && c.y == 0.0f && c.z == 0.0f;
-        want = !lzero && !czero;
-      }
+      if (ctx.lit) want = light_request(S, ctx, thr, li, so, sd, c, limit);
       uint32_t pos = warp_append(&W.counters[CTR_SHADOW], want);
       if (want && pos < W.shadow_capacity) {
         W.sh_o[pos] = make_float4(so.x, so.y, so.z, limit);
         W.sh_d[pos] = make_float4(sd.x, sd.y, sd.z, __int_as_float((int)slot));
-        W.sh_c[pos] = make_float4(c.x, c.y, c.z, sf.is_sphere ? __int_as_float(0x7fc00000) : sf.tu);
-        W.sh_p[pos] = make_float4(sf.position.x, sf.position.y, sf.position.z, sf.tv);
+        W.sh_c[pos] = make_float4(c.x, c.y, c.z, ctx.sf.is_sphere ? __int_as_float(0x7fc00000) : ctx.sf.tu);
+        W.sh_p[pos] = make_float4(ctx.sf.position.x, ctx.sf.position.y, ctx.sf.position.z, ctx.sf.tv);
       }
     }
-    V3 no{}, nd{};
-    if (lit) {
-      alive = true;
-      if (bounce < P.bounces) {  // mod.rs:265-275
-        RngKey key = make_key(P, slot);
-        uint4 rb = rng_block(key, bounce + 1, 0);
-        no = sf.position + sf.normal * NORMAL_BIAS;
-        nd = brdf_sample(brdf, sf.shading_n, view, u32_to_unit(rb.x), u32_to_unit(rb.y));
-        V3 w = eval_indirect(brdf, sf.shading_n, view, nd) / 1.0f;
-        thr = mul_el(thr, w);
-        if (dot3(thr, thr) < 0.00001f) alive = false;  // mod.rs:219-221
-        if (alive && bounce > 3) {                        // utils.rs:23-31
-          float p = fmaxf(fmaxf(thr.x, thr.y), thr.z);
-          thr = thr * (1.0f / p);
-          if (u32_to_unit(rb.z) > p) alive = false;
-        }
-      } else {
-        alive = false;  // last iteration of `for bounce in 0..=bounces`
-      }
+    Ray next{};
+    bool alive = false;
+    if (active) {
+      alive = shade_finish(P, make_key(P, slot), bounce, ctx, thr, next);
+      W.radiance[slot] = make_float4(rad.x, rad.y, rad.z, 0.f);
     }
-    if (active) W.radiance[slot] = make_float4(rad.x, rad.y, rad.z, 0.f);
     uint32_t pos = warp_append(&W.counters[CTR_QUEUE0 + outb], alive);
     if (alive) {
-      W.ray_o[outb][pos] = make_float4(no.x, no.y, no.z, 0.f);
-      W.ray_d[outb][pos] = make_float4(nd.x, nd.y, nd.z, __int_as_float((int)slot));
+      W.ray_o[outb][pos] = make_float4(next.o.x, next.o.y, next.o.z, 0.f);
+      W.ray_d[outb][pos] = make_float4(next.d.x, next.d.y, next.d.z, __int_as_float((int)slot));
       W.thr[outb][pos] = make_float4(thr.x, thr.y, thr.z, 0.f);
     }
   }
+}
+
+// One thread follows one whole path (render_pixel, mod.rs:172-228) and records every bounce: the per-vertex
+// parity harness (pt_trace_paths).  Lights are evaluated in file order with the shadow walk inline.
+__global__ void __launch_bounds__(128) k_trace_paths(const __grid_constant__ DevScene S,
+                                                     const __grid_constant__ WaveParams P,
+                                                     const uint32_t *__restrict__ pixels, uint32_t n_paths,
+                                                     pt_path_vertex *__restrict__ out, uint32_t *__restrict__ counts) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_paths) return;
+  RngKey key;
+  key.pixel = pixels[i];
+  key.sample = P.sample_first;
+  key.seed_lo = P.seed_lo;
+  key.seed_hi = P.seed_hi;
+  Ray r = generate_ray(S, P, key);
+  V3 thr = mk3(1.f, 1.f, 1.f), rad = mk3(0.f, 0.f, 0.f);
+  pt_path_vertex *rec = out + (size_t)i * (P.bounces + 1);
+  uint32_t nv = 0, recasts = 0;
+  for (uint32_t bounce = 0; bounce <= P.bounces; ++bounce) {
+    TraceState st;
+    extend_ray(S, key, bounce, r, st, recasts);
+    ShadeCtx ctx;
+    shade_begin(S, r, st.best_t, st.u, st.v, st.idx, thr, rad, ctx);
+    if (ctx.lit) {
+      for (uint32_t li = 0; li < S.n_lights; ++li) {
+        V3 so, sd, c;
+        float limit;
+        if (!light_request(S, ctx, thr, li, so, sd, c, limit)) continue;
+        Ray sr;
+        sr.o = so;
+        sr.d = sd;
+        float tr = trace_transmittance(S, sr, limit, ctx.sf.position,
+                                       ctx.sf.is_sphere ? __int_as_float(0x7fc00000) : ctx.sf.tu, ctx.sf.tv);
+        if (tr != 0.0f) rad = rad + c * tr;
+      }
+    }
+    Ray next{};
+    bool alive = shade_finish(P, key, bounce, ctx, thr, next);
+    pt_path_vertex v;
+    v.ray_o[0] = r.o.x; v.ray_o[1] = r.o.y; v.ray_o[2] = r.o.z;
+    v.ray_d[0] = r.d.x; v.ray_d[1] = r.d.y; v.ray_d[2] = r.d.z;
+    v.prim_id = st.idx < 0 ? -1 : st.best_id;
+    v.t = st.idx < 0 ? 0.f : st.best_t;
+    v.throughput[0] = thr.x; v.throughput[1] = thr.y; v.throughput[2] = thr.z;
+    v.radiance[0] = rad.x; v.radiance[1] = rad.y; v.radiance[2] = rad.z;
+    rec[nv++] = v;
+    if (!alive) break;
+    r = next;
+  }
+  counts[i] = nv;
+}
+
+// Triangle::intersect (scene/internal/triangle.rs:37-82) on independent (ray, triangle) pairs: the entry point
+// behind the reference's own hit/miss unit vectors (triangle.rs:200-233).
+__global__ void __launch_bounds__(256) k_triangle_intersect(const float *__restrict__ rays, const float *__restrict__ tris,
+                                                            uint32_t n, pt_hit *__restrict__ out) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float *q = rays + (size_t)i * 6, *p = tris + (size_t)i * 9;
+  Ray r;
+  r.o = mk3(q[0], q[1], q[2]);
+  r.d = mk3(q[3], q[4], q[5]);
+  V3 v0 = mk3(p[0], p[1], p[2]);
+  V3 e1 = mk3(p[3] - p[0], p[4] - p[1], p[5] - p[2]);
+  V3 e2 = mk3(p[6] - p[0], p[7] - p[1], p[8] - p[2]);
+  float t = 0.f, u = 0.f, v = 0.f, det = 0.f;
+  bool hit = moller_trumbore(r, v0, e1, e2, t, u, v, det);
+  pt_hit h;
+  h.prim_id = hit ? (det < 0.0f ? 1 : 0) : -1;  // 0 front face, 1 back face (is_backface = det < 0)
+  h.t = hit ? t : 0.f;
+  h.u = hit ? u : 0.f;
+  h.v = hit ? v : 0.f;
+  out[i] = h;
 }
 
 // shadow: transmittance of every queued shadow ray; adds contribution * transmittance to the path's radiance.
@@ -426,6 +325,13 @@ void launch_trace_closest(const DevScene &S, const float *rays, uint32_t n, pt_h
 void launch_trace_transmittance(const DevScene &S, const float *rays, uint32_t n, float *out, uint32_t *cursor, cudaStream_t st) {
   cudaMemsetAsync(cursor, 0, sizeof(uint32_t), st);
   k_trace_transmittance<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, rays, n, out, cursor);
+}
+void launch_trace_paths(const DevScene &S, const WaveParams &P, const uint32_t *pixels, uint32_t n, pt_path_vertex *out,
+                        uint32_t *counts, cudaStream_t st) {
+  k_trace_paths<<<(n + 127) / 128, 128, 0, st>>>(S, P, pixels, n, out, counts);
+}
+void launch_triangle_intersect(const float *rays, const float *tris, uint32_t n, pt_hit *out, cudaStream_t st) {
+  k_triangle_intersect<<<(n + 255) / 256, 256, 0, st>>>(rays, tris, n, out);
 }
 void launch_raygen(const DevScene &S, const WaveParams &P, const WaveState &W, cudaStream_t st) {
   k_raygen<<<(P.n_paths + 255) / 256, 256, 0, st>>>(S, P, W);

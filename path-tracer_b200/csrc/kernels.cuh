@@ -6,6 +6,9 @@
 namespace ptb {
 void launch_trace_closest(const DevScene &S, const float *rays, uint32_t n, pt_hit *out, uint32_t *cursor, cudaStream_t st);
 void launch_trace_transmittance(const DevScene &S, const float *rays, uint32_t n, float *out, uint32_t *cursor, cudaStream_t st);
+void launch_trace_paths(const DevScene &S, const WaveParams &P, const uint32_t *pixels, uint32_t n, pt_path_vertex *out,
+                        uint32_t *counts, cudaStream_t st);
+void launch_triangle_intersect(const float *rays, const float *tris, uint32_t n, pt_hit *out, cudaStream_t st);
 void launch_raygen(const DevScene &S, const WaveParams &P, const WaveState &W, cudaStream_t st);
 void launch_extend(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st);
 void launch_shade(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st);

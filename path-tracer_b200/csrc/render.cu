@@ -172,6 +172,7 @@ int build_device_scene(pt_scene *sc) {
   D.any_alpha = any_alpha ? 1u : 0u;
   std::memcpy(D.camera, h.camera, sizeof D.camera);
   D.fov = h.fov;
+  D.tan_half_fov = std::tan(h.fov / 2.0f);  // f32 tanf of the C library == Rust's f32::tan
   std::memcpy(D.background, h.background, sizeof D.background);
   void *cur = nullptr;
   CUDA_TRY(cudaMalloc(&cur, 64));
@@ -393,6 +394,85 @@ int pt_trace_transmittance(const pt_scene *sc, const float *rays, size_t n, floa
   launch_trace_transmittance(sc->dev, d_rays, (uint32_t)n, d_out, sc->cursor, nullptr);
   cudaError_t e = cudaMemcpy(out, d_out, n * sizeof(float), cudaMemcpyDeviceToHost);
   cudaFree(d_rays);
+  cudaFree(d_out);
+  CUDA_TRY(e);
+  return PT_OK;
+}
+
+int pt_triangle_intersect(const pt_scene *sc, int device, const float *rays, const float *tris, size_t n, pt_hit *out) {
+  if ((n && (!rays || !tris || !out)) || n > 0x7FFFFFFFull) {
+    set_error("bad argument");
+    return PT_ERR_INVALID;
+  }
+  if (n == 0) return PT_OK;
+  if (sc) device = sc->device;
+  if (device < 0 || device >= pt_device_count()) {
+    set_error("no CUDA device %d (this library has no CPU fallback)", device);
+    return PT_ERR_CUDA;
+  }
+  DeviceGuard g(device);
+  float *d_rays = nullptr, *d_tris = nullptr;
+  pt_hit *d_out = nullptr;
+  cudaError_t e = cudaMalloc(&d_rays, n * 6 * sizeof(float));
+  if (e == cudaSuccess) e = cudaMalloc(&d_tris, n * 9 * sizeof(float));
+  if (e == cudaSuccess) e = cudaMalloc(&d_out, n * sizeof(pt_hit));
+  if (e == cudaSuccess) e = cudaMemcpy(d_rays, rays, n * 6 * sizeof(float), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(d_tris, tris, n * 9 * sizeof(float), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    launch_triangle_intersect(d_rays, d_tris, (uint32_t)n, d_out, nullptr);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(out, d_out, n * sizeof(pt_hit), cudaMemcpyDeviceToHost);
+  cudaFree(d_rays);
+  cudaFree(d_tris);
+  cudaFree(d_out);
+  CUDA_TRY(e);
+  return PT_OK;
+}
+
+int pt_trace_paths(const pt_scene *sc, const pt_profile *prof, const uint32_t *pixels, size_t n_paths, uint32_t sample,
+                   uint64_t seed, pt_path_vertex *out, uint32_t *counts) {
+  if (!sc || (n_paths && (!pixels || !out || !counts)) || n_paths > 0x7FFFFFFFull) {
+    set_error("bad argument");
+    return PT_ERR_INVALID;
+  }
+  int rc = check_profile(prof);
+  if (rc) return rc;
+  if (n_paths == 0) return PT_OK;
+  if (sc->device < 0) return no_device();
+  const uint64_t npix = (uint64_t)prof->width * prof->height;
+  for (size_t i = 0; i < n_paths; ++i)
+    if (pixels[i] >= npix) {
+      set_error("pixel index %u out of range", pixels[i]);
+      return PT_ERR_INVALID;
+    }
+  DeviceGuard g(sc->device);
+  WaveParams P{};
+  P.width = prof->width;
+  P.height = prof->height;
+  P.bounces = prof->bounces;
+  P.spp_in_wave = 1;
+  P.sample_first = sample;
+  P.sample_stride = 1;
+  P.seed_lo = (uint32_t)seed;
+  P.seed_hi = (uint32_t)(seed >> 32);
+  P.n_paths = (uint32_t)n_paths;
+  const size_t nv = n_paths * ((size_t)prof->bounces + 1);
+  uint32_t *d_pix = nullptr, *d_cnt = nullptr;
+  pt_path_vertex *d_out = nullptr;
+  cudaError_t e = cudaMalloc(&d_pix, n_paths * sizeof(uint32_t));
+  if (e == cudaSuccess) e = cudaMalloc(&d_cnt, n_paths * sizeof(uint32_t));
+  if (e == cudaSuccess) e = cudaMalloc(&d_out, nv * sizeof(pt_path_vertex));
+  if (e == cudaSuccess) e = cudaMemcpy(d_pix, pixels, n_paths * sizeof(uint32_t), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemset(d_out, 0, nv * sizeof(pt_path_vertex));
+  if (e == cudaSuccess) {
+    launch_trace_paths(sc->dev, P, d_pix, (uint32_t)n_paths, d_out, d_cnt, nullptr);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(out, d_out, nv * sizeof(pt_path_vertex), cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess) e = cudaMemcpy(counts, d_cnt, n_paths * sizeof(uint32_t), cudaMemcpyDeviceToHost);
+  cudaFree(d_pix);
+  cudaFree(d_cnt);
   cudaFree(d_out);
   CUDA_TRY(e);
   return PT_OK;

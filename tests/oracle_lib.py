@@ -5,7 +5,7 @@ import subprocess
 
 import numpy as np
 
-from path_tracer_b200.abi import HIT_DTYPE, pt_hit, pt_profile, pt_scene_desc
+from path_tracer_b200.abi import HIT_DTYPE, PATH_VERTEX_DTYPE, pt_hit, pt_profile, pt_scene_desc
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 _LIB = None
@@ -31,6 +31,8 @@ def lib():
         L.oracle_tonemap.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int32, C.c_void_p]
         L.oracle_dump_bounce_rays.argtypes = [C.c_void_p, C.POINTER(pt_profile), C.c_uint64, C.c_uint32, C.c_void_p,
                                               C.c_void_p]
+        L.oracle_trace_paths.argtypes = [C.c_void_p, C.POINTER(pt_profile), C.c_void_p, C.c_size_t, C.c_uint32,
+                                         C.c_uint64, C.c_int, C.c_void_p, C.c_void_p]
         _LIB = L
     return _LIB
 
@@ -78,6 +80,14 @@ class OracleScene:
         if return_counters:
             return accum, ms, cnt
         return accum
+
+    def trace_paths(self, profile, pixels, sample=0, seed=0, brute=False):
+        pixels = np.ascontiguousarray(pixels, np.uint32)
+        out = np.zeros((len(pixels), profile.bounces + 1), PATH_VERTEX_DTYPE)
+        counts = np.zeros(len(pixels), np.uint32)
+        lib().oracle_trace_paths(self.h, C.byref(profile), pixels.ctypes.data, len(pixels), sample, seed, int(brute),
+                                 out.ctypes.data, counts.ctypes.data)
+        return out, counts
 
     def dump_bounce_rays(self, profile, bounce, seed=0):
         n = profile.width * profile.height
