@@ -130,7 +130,7 @@ typedef struct {
   uint64_t alpha_recasts; /* continuation re-casts (implementation artefact) */
   uint64_t kernel_launches;
   float ms_total;         /* raygen -> accumulation resident, CUDA events     */
-  float ms_extend, ms_shade, ms_shadow, ms_other;
+  float ms_extend, ms_shade, ms_shadow, ms_other; /* filled only while pt_set_kernel_timing(1) */
   uint64_t extend_launches, shade_launches, shadow_launches;
 } pt_stats;
 
@@ -155,6 +155,10 @@ int pt_scene_create(const pt_scene_desc *desc, int device, pt_scene **out);
  * n_tris is a target triangle count. */
 int pt_scene_synthetic(const char *recipe, uint64_t n_tris, uint64_t seed, int device, pt_scene **out);
 void pt_scene_destroy(pt_scene *scene);
+/* Re-sends every device array of the scene (nodes, triangles, shading records, materials, texels, lights) from
+ * its pinned host image, asynchronously on `stream`: the host->device leg of a call that starts from host
+ * memory (Scene::load's result living on the host).  *bytes_out = bytes copied. */
+int pt_scene_upload(pt_scene *scene, void *stream, uint64_t *bytes_out);
 /* Introspection (host copies; pointers valid until pt_scene_destroy). */
 int pt_scene_get_desc(const pt_scene *scene, pt_scene_desc *out);
 int pt_scene_info(const pt_scene *scene, uint64_t *n_tris, uint64_t *n_prims, uint64_t *n_nodes,
@@ -183,6 +187,10 @@ int pt_triangle_intersect(const pt_scene *scene_or_null, int device, const float
  * written.  Host pointers.  Lights are evaluated in file order. */
 int pt_trace_paths(const pt_scene *scene, const pt_profile *profile, const uint32_t *pixels, size_t n_paths,
                    uint32_t sample, uint64_t seed, pt_path_vertex *out, uint32_t *counts);
+
+/* Per-kernel CUDA-event timing inside pt_render_accum_device (one event per launch; replaces the reference's only
+ * timer, the whole-second "Done: {}s" of renderer/mod.rs:103,164-166).  Off by default. */
+void pt_set_kernel_timing(int on);
 
 /* ---- Renderer::render (renderer/mod.rs:76-169) ---- */
 /* Renders samples {sample_begin + k*sample_stride | k in [0,n_samples)} of every pixel

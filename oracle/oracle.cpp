@@ -15,6 +15,7 @@
 #include <cstring>
 #include <thread>
 
+#include "canonical.hpp"
 #include "shading.hpp"
 
 using namespace orc;
@@ -25,6 +26,8 @@ const float NORMAL_BIAS = 0.00001f;  // renderer/mod.rs:59
 
 struct Counters {
   uint64_t extend = 0, shadow = 0;
+  bool canon_on = false;  // also run the canonical work counter on every ray (canonical.hpp)
+  CanonCounts canon;
 };
 
 // get_light_info, renderer/mod.rs:281-333
@@ -38,6 +41,7 @@ void light_info(const Scene &s, const pt_light &light, const Hit &hit, bool brut
     V3 color = lc;
     ray_cast(s, ori, sdir, tmp, brute);
     ++cnt.shadow;
+    if (cnt.canon_on) s.canon->count_any(s, ori, sdir, FLT_MAX, cnt.canon);
     for (const Hit &sh : tmp) {
       MaterialSample ms = hit_material_sample(s, sh, sh.model);
       color = color * (1.0f - ms.opacity);
@@ -56,6 +60,7 @@ void light_info(const Scene &s, const pt_light &light, const Hit &hit, bool brut
   V3 ld = lc / dissipation;
   ray_cast(s, ori, sdir, tmp, brute);
   ++cnt.shadow;
+  if (cnt.canon_on) s.canon->count_any(s, ori, sdir, dist, cnt.canon);
   for (const Hit &sh : tmp) {
     if (magnitude(sh.position - hit.position) > dist) break;
     // quirk (mod.rs:324): the PRIMARY hit's variant/uv with the occluder's material
@@ -89,6 +94,7 @@ V3 render_pixel(const Scene &s, const pt_profile &prof, V3 ro, V3 rd, PathRng &r
   for (uint32_t bounce = 0; bounce < prof.bounces + 1; ++bounce) {
     ray_cast(s, ro, rd, hits, brute);
     ++cnt.extend;
+    if (cnt.canon_on) s.canon->count_closest(s, ro, rd, cnt.canon);
     if (hits.empty()) {
       if (rec) rec->put(ro, rd, -1, 0.0f, thr, color + mul_el(thr, s.background));
       return color + mul_el(thr, s.background);
@@ -209,7 +215,11 @@ void *oracle_scene_create(const pt_scene_desc *d) {
   return s;
 }
 
-void oracle_scene_destroy(void *p) { delete (Scene *)p; }
+void oracle_scene_destroy(void *p) {
+  Scene *s = (Scene *)p;
+  if (s) delete s->canon;
+  delete s;
+}
 
 // ray_cast(...).first(): closest hit of each ray.  brute != 0 bypasses the BVH filter.
 int oracle_trace_closest(const void *sp, const float *rays, size_t n, pt_hit *out, int brute, int threads) {
@@ -303,6 +313,42 @@ double oracle_render_accum(const void *sp, const pt_profile *prof, int rng_mode,
     for (auto &c : cnts) { counters_out[0] += c.extend; counters_out[1] += c.shadow; }
   }
   return std::chrono::duration<double, std::milli>(t1 - t0).count();
+}
+
+// Canonical per-ray work of a profile: traces sample 0 of every `pixel_stride`-th pixel and counts
+// the canonical BVH2 traversal of every path segment (closest hit) and every shadow ray (any hit).
+// out6 = [rays_closest, nodes_closest, prims_closest, rays_any, nodes_any, prims_any].
+int oracle_canonical_counts(void *sp, const pt_profile *prof, uint32_t pixel_stride, uint64_t seed, int threads,
+                            uint64_t *out6) {
+  Scene &s = *(Scene *)sp;
+  if (!s.canon) {
+    s.canon = new CanonBvh();
+    s.canon->build(s);
+  }
+  if (threads < 1) threads = 1;
+  if (pixel_stride < 1) pixel_stride = 1;
+  const uint64_t npix = (uint64_t)prof->width * prof->height;
+  std::vector<Counters> cnts(threads);
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; ++t)
+    pool.emplace_back([&, t]() {
+      std::vector<Hit> hits, tmp;
+      cnts[t].canon_on = true;
+      for (uint64_t i = (uint64_t)t * pixel_stride; i < npix; i += (uint64_t)threads * pixel_stride) {
+        PathRng rng;
+        rng.init_philox((uint32_t)i, 0, seed);
+        V3 o, d;
+        raygen(s, *prof, (uint32_t)(i % prof->width), (uint32_t)(i / prof->width), rng, o, d);
+        render_pixel(s, *prof, o, d, rng, false, hits, tmp, cnts[t]);
+      }
+    });
+  for (auto &t : pool) t.join();
+  for (int k = 0; k < 6; ++k) out6[k] = 0;
+  for (auto &c : cnts) {
+    out6[0] += c.canon.rays_closest; out6[1] += c.canon.nodes_closest; out6[2] += c.canon.prims_closest;
+    out6[3] += c.canon.rays_any; out6[4] += c.canon.nodes_any; out6[5] += c.canon.prims_any;
+  }
+  return 0;
 }
 
 // render_pixel with a per-bounce record (Philox streams), the checker of pt_trace_paths.

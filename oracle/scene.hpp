@@ -17,6 +17,8 @@
 
 namespace orc {
 
+struct CanonBvh;  // canonical.hpp
+
 struct Hit {
   float dist;
   V3 position;
@@ -51,6 +53,7 @@ struct Scene {
   };
   std::vector<Node> nodes;
   std::vector<int32_t> bvh_prims;  // >=0: triangle index; <0: ~model (sphere)
+  CanonBvh *canon = nullptr;       // canonical work counter (built on demand, canonical.hpp)
 
   V3 P(uint32_t tri, int k) const { return {pos[tri * 9 + k * 3], pos[tri * 9 + k * 3 + 1], pos[tri * 9 + k * 3 + 2]}; }
   V3 N(uint32_t tri, int k) const { return {nrm[tri * 9 + k * 3], nrm[tri * 9 + k * 3 + 1], nrm[tri * 9 + k * 3 + 2]}; }

@@ -19,7 +19,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
 EXPORTS = ["pt_last_error", "pt_device_count", "pt_profile_default", "pt_profile_load_yaml", "pt_scene_load_isf",
-           "pt_scene_create", "pt_scene_synthetic", "pt_scene_destroy", "pt_scene_get_desc", "pt_scene_info",
+           "pt_scene_create", "pt_scene_synthetic", "pt_scene_destroy", "pt_scene_upload", "pt_set_kernel_timing", "pt_scene_get_desc", "pt_scene_info",
            "pt_trace_closest", "pt_trace_closest_device", "pt_trace_transmittance", "pt_triangle_intersect",
            "pt_trace_paths", "pt_render_accum_device",
            "pt_tonemap_device", "pt_render", "pt_write_png", "pt_read_png", "pt_free"]
@@ -50,6 +50,9 @@ def lib():
         L.pt_scene_synthetic.argtypes = [C.c_char_p, u64, u64, C.c_int, C.POINTER(vp)]
         L.pt_scene_destroy.argtypes = [vp]
         L.pt_scene_destroy.restype = None
+        L.pt_scene_upload.argtypes = [vp, vp, C.POINTER(u64)]
+        L.pt_set_kernel_timing.argtypes = [C.c_int]
+        L.pt_set_kernel_timing.restype = None
         L.pt_scene_get_desc.argtypes = [vp, C.POINTER(pt_scene_desc)]
         L.pt_scene_info.argtypes = [vp, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]
         L.pt_trace_closest.argtypes = [vp, vp, C.c_size_t, vp]
@@ -143,6 +146,12 @@ class Scene:
             self.close()
         except Exception:
             pass
+
+    def upload(self, stream=None):
+        """Re-send the scene's device arrays from pinned host memory (async on `stream`); returns bytes copied."""
+        n = C.c_uint64()
+        _check(lib().pt_scene_upload(self.h, stream, C.byref(n)))
+        return n.value
 
     def info(self):
         a, b, c, d = C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_uint64()
@@ -254,6 +263,10 @@ def render_accum_device(scene, profile, accum_ptr, sample_begin=0, sample_stride
     _check(lib().pt_render_accum_device(scene.h, C.byref(profile.c), sample_begin, sample_stride, n, seed, accum_ptr,
                                         stream, C.byref(st) if want_stats else None))
     return st.as_dict() if want_stats else None
+
+
+def set_kernel_timing(on):
+    lib().pt_set_kernel_timing(1 if on else 0)
 
 
 def tonemap_device(accum_ptr, width, height, total_samples, tonemap, rgb8_ptr, device=0, stream=None):

@@ -60,6 +60,12 @@ struct pt_scene {
   int device = 0;
   DevScene dev{};
   std::vector<void *> allocs;
+  struct Staged {  // device array + its pinned host image (pt_scene_upload re-sends it)
+    void *dev, *host;
+    size_t bytes;
+  };
+  std::vector<Staged> staged;
+  std::vector<cudaEvent_t> events;  // pool for per-kernel timing (pt_set_kernel_timing)
   uint64_t device_bytes = 0;
   double build_ms = 0;
   // wave buffers, grown lazily and reused between renders (guarded: one render at a time per scene)
@@ -78,7 +84,13 @@ int upload(pt_scene *sc, const std::vector<T> &v, const T **out) {
   CUDA_TRY(cudaMalloc(&p, bytes));
   sc->allocs.push_back(p);
   sc->device_bytes += bytes;
-  if (!v.empty()) CUDA_TRY(cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  if (!v.empty()) {
+    void *hp = nullptr;
+    CUDA_TRY(cudaMallocHost(&hp, v.size() * sizeof(T)));
+    std::memcpy(hp, v.data(), v.size() * sizeof(T));
+    sc->staged.push_back({p, hp, v.size() * sizeof(T)});
+    CUDA_TRY(cudaMemcpy(p, hp, v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  }
   *out = reinterpret_cast<const T *>(p);
   return PT_OK;
 }
@@ -318,8 +330,29 @@ void pt_scene_destroy(pt_scene *sc) {
   DeviceGuard g(sc->device);
   free_wave(sc);
   for (void *p : sc->allocs) cudaFree(p);
+  for (auto &s : sc->staged) cudaFreeHost(s.host);
+  for (cudaEvent_t e : sc->events) cudaEventDestroy(e);
   delete sc;
 }
+
+int pt_scene_upload(pt_scene *sc, void *stream, uint64_t *bytes_out) {
+  if (!sc) {
+    set_error("null argument");
+    return PT_ERR_INVALID;
+  }
+  if (sc->device < 0) return no_device();
+  DeviceGuard g(sc->device);
+  uint64_t total = 0;
+  for (auto &s : sc->staged) {
+    CUDA_TRY(cudaMemcpyAsync(s.dev, s.host, s.bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    total += s.bytes;
+  }
+  if (bytes_out) *bytes_out = total;
+  return PT_OK;
+}
+
+static int g_kernel_timing = 0;
+void pt_set_kernel_timing(int on) { g_kernel_timing = on; }
 
 int pt_scene_get_desc(const pt_scene *sc, pt_scene_desc *out) {
   if (!sc || !out) return PT_ERR_INVALID;
@@ -510,6 +543,20 @@ int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t
     CUDA_TRY(cudaEventRecord(e0, st));
   }
   uint64_t launches = 0, n_ext = 0, n_shade = 0, n_shadow = 0;
+  // optional per-kernel timing: one event after every launch, classes 0 extend, 1 shade, 2 shadow, 3 other
+  const bool timing = stats_out && g_kernel_timing;
+  std::vector<int> marks;
+  auto mark = [&](int cls) {
+    if (!timing) return;
+    if (marks.size() >= sc->events.size()) {
+      cudaEvent_t e = nullptr;
+      cudaEventCreate(&e);
+      sc->events.push_back(e);
+    }
+    cudaEventRecord(sc->events[marks.size()], st);
+    marks.push_back(cls);
+  };
+  mark(3);
   for (uint32_t done = 0; done < n_samples; done += spw) {
     WaveParams P;
     P.width = prof->width;
@@ -522,20 +569,25 @@ int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t
     P.seed_hi = (uint32_t)(seed >> 32);
     P.n_paths = (uint32_t)(npix * P.spp_in_wave);
     launch_raygen(sc->dev, P, W, st);
+    mark(3);
     ++launches;
     for (uint32_t b = 0; b <= prof->bounces; ++b) {
       launch_extend(sc->dev, P, W, b, st);
+      mark(0);
       launch_shade(sc->dev, P, W, b, st);
+      mark(1);
       launches += 2;
       ++n_ext;
       ++n_shade;
       if (sc->dev.n_lights) {
         launch_shadow(sc->dev, W, st);
+        mark(2);
         ++launches;
         ++n_shadow;
       }
     }
     launch_resolve(P, W, accum_dev, st);
+    mark(3);
     ++launches;
   }
   CUDA_TRY(cudaGetLastError());
@@ -557,6 +609,18 @@ int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t
     stats_out->extend_launches = n_ext;
     stats_out->shade_launches = n_shade;
     stats_out->shadow_launches = n_shadow;
+    if (timing) {
+      float acc[4] = {0, 0, 0, 0};
+      for (size_t i = 1; i < marks.size(); ++i) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, sc->events[i - 1], sc->events[i]);
+        acc[marks[i]] += ms;
+      }
+      stats_out->ms_extend = acc[0];
+      stats_out->ms_shade = acc[1];
+      stats_out->ms_shadow = acc[2];
+      stats_out->ms_other = acc[3];
+    }
   }
   return PT_OK;
 }

@@ -1,0 +1,85 @@
+"""Multi-GPU rendering: one process per GPU, samples split by index, ONE reduce of the float accumulation buffer.
+
+The reference is a single process (rayon over pixels, renderer/mod.rs:105-106) whose samples are independent
+because its RNG is seeded per (pixel, sample) (mod.rs:110-112).  Here rank g of G renders the samples
+{s : s mod G == g} of the FULL frame into its own W*H*3 f32 buffer, the buffers are summed onto rank 0 with a
+single `torch.distributed.reduce` (NCCL over NVLink on GPUs, gloo in the CPU tests), and rank 0 runs
+mean -> tonemap -> gamma -> u8 (post_processing, mod.rs:335-353).  The union of samples is identical for any G, so
+the image differs between G only by the f32 summation order.
+
+No collective is issued inside a frame; the reduce is the only exchange step of the path.
+"""
+import torch
+import torch.distributed as dist
+
+
+def sample_partition(total_samples, world_size, rank):
+    """Samples of `rank`: (begin, stride, count) with sample indices begin + k*stride, k < count."""
+    if world_size < 1 or not (0 <= rank < world_size):
+        raise ValueError("bad rank/world_size")
+    count = (total_samples - rank + world_size - 1) // world_size if total_samples > rank else 0
+    return rank, world_size, count
+
+
+def world():
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def reduce_accum(accum, dst=0):
+    """Sum the per-rank accumulation buffers onto `dst` (in place there); a no-op for a single process."""
+    rank, size = world()
+    if size > 1:
+        dist.reduce(accum, dst=dst, op=dist.ReduceOp.SUM)
+    return accum
+
+
+def render_distributed(render_fn, tonemap_fn, total_samples, accum):
+    """Generic driver used by both the CUDA path and the CPU (gloo) tests.
+
+    render_fn(sample_begin, sample_stride, n_samples, accum) adds this rank's samples into `accum`;
+    tonemap_fn(accum, total_samples) -> image runs on rank 0 only.  Returns the image on rank 0, None elsewhere.
+    """
+    rank, size = world()
+    begin, stride, count = sample_partition(total_samples, size, rank)
+    accum.zero_()
+    render_fn(begin, stride, count, accum)
+    reduce_accum(accum, 0)
+    if rank == 0:
+        return tonemap_fn(accum, total_samples)
+    return None
+
+
+class DistributedRenderer:
+    """Renderer::render (renderer/mod.rs:76-169) across the ranks of the default process group.
+
+    Every rank holds its own replica of the scene on its own GPU (`scene` was created with device=LOCAL_RANK).
+    """
+
+    def __init__(self, scene, profile, seed=0, device=None):
+        from . import api
+        self.api = api
+        self.scene, self.profile, self.seed = scene, profile, seed
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        h, w = profile.height, profile.width
+        self.accum = torch.zeros(h, w, 3, dtype=torch.float32, device=self.device)
+        self.rgb = torch.zeros(h, w, 3, dtype=torch.uint8, device=self.device)
+        self.last_stats = None
+
+    def _render(self, begin, stride, count, accum, want_stats=False):
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        self.last_stats = self.api.render_accum_device(self.scene, self.profile, accum.data_ptr(), begin, stride, count,
+                                                       self.seed, stream, want_stats)
+
+    def _tonemap(self, accum, total_samples):
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        p = self.profile
+        self.api.tonemap_device(accum.data_ptr(), p.width, p.height, total_samples, p.tonemap, self.rgb.data_ptr(),
+                                self.device.index or 0, stream)
+        return self.rgb
+
+    def render(self, total_samples=None, want_stats=False):
+        """Asynchronous on the current stream; returns the device RGB8 image on rank 0 (None elsewhere)."""
+        total = self.profile.samples if total_samples is None else total_samples
+        return render_distributed(lambda b, s, c, a: self._render(b, s, c, a, want_stats), self._tonemap, total, self.accum)

@@ -33,6 +33,7 @@ def lib():
                                               C.c_void_p]
         L.oracle_trace_paths.argtypes = [C.c_void_p, C.POINTER(pt_profile), C.c_void_p, C.c_size_t, C.c_uint32,
                                          C.c_uint64, C.c_int, C.c_void_p, C.c_void_p]
+        L.oracle_canonical_counts.argtypes = [C.c_void_p, C.POINTER(pt_profile), C.c_uint32, C.c_uint64, C.c_int, C.c_void_p]
         _LIB = L
     return _LIB
 
@@ -88,6 +89,14 @@ class OracleScene:
         lib().oracle_trace_paths(self.h, C.byref(profile), pixels.ctypes.data, len(pixels), sample, seed, int(brute),
                                  out.ctypes.data, counts.ctypes.data)
         return out, counts
+
+    def canonical_counts(self, profile, pixel_stride=1, seed=0, threads=8):
+        """Canonical BVH2 work per ray: dict with n_node/n_tri means for path segments and shadow rays."""
+        out = np.zeros(6, np.uint64)
+        lib().oracle_canonical_counts(self.h, C.byref(profile), pixel_stride, seed, threads, out.ctypes.data)
+        rc, nc, pc, ra, na, pa = [int(x) for x in out]
+        return dict(rays_closest=rc, n_node_closest=nc / max(rc, 1), n_tri_closest=pc / max(rc, 1),
+                    rays_any=ra, n_node_any=na / max(ra, 1), n_tri_any=pa / max(ra, 1))
 
     def dump_bounce_rays(self, profile, bounce, seed=0):
         n = profile.width * profile.height
