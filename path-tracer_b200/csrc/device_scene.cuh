@@ -48,8 +48,8 @@ struct DevLight {
   float pad;
 };
 
-struct DevNode {  // == ptb::Bvh4Node, one 128-byte line
-  float4 lo_x, lo_y, lo_z, hi_x, hi_y, hi_z;
+struct DevNode {  // == ptb::Bvh4Node, one 128-byte line = four 32-byte chunks: x planes, y planes, z planes, children
+  float4 lo_x, hi_x, lo_y, hi_y, lo_z, hi_z;
   uint4 child;
   uint4 pad;
 };

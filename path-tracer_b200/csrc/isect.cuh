@@ -132,6 +132,53 @@ __device__ __forceinline__ float slab(float lox, float loy, float loz, float hix
   return hit ? tn : CUDART_INF_F;
 }
 
+// Slab test of the persistent kernels: (plane - o) * inv is evaluated as one fused multiply-add
+// fma(plane, inv, -o*inv).  The box test is only a conservative filter (boxes are inflated by
+// 4e-6 relative, ~33 ulp, and the exit is widened below), so its rounding may differ from the un-fused arithmetic that
+// Moller-Trumbore must use; the absolute error of either form is ~1 ulp of the coordinate magnitude / |d|.
+struct NodeOrder {
+  float oix, oiy, oiz;  // -o * inv
+};
+__device__ __forceinline__ NodeOrder node_order(const Ray &r, const RayPre &p) {
+  NodeOrder n;
+  n.oix = -(r.o.x * p.ix);
+  n.oiy = -(r.o.y * p.iy);
+  n.oiz = -(r.o.z * p.iz);
+  return n;
+}
+__device__ __forceinline__ float slab_fma(float lox, float loy, float loz, float hix, float hiy, float hiz, const RayPre &p,
+                                          const NodeOrder &n, float t_max, uint32_t child) {
+  float t0x = __fmaf_rn(lox, p.ix, n.oix), t1x = __fmaf_rn(hix, p.ix, n.oix);
+  float t0y = __fmaf_rn(loy, p.iy, n.oiy), t1y = __fmaf_rn(hiy, p.iy, n.oiy);
+  float t0z = __fmaf_rn(loz, p.iz, n.oiz), t1z = __fmaf_rn(hiz, p.iz, n.oiz);
+  float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.0f));
+  float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
+  bool hit = child != 0xFFFFFFFFu && tn <= __fmaf_rn(tf, 1.000002f, 1e-7f) && tn <= t_max;
+  return hit ? tn : CUDART_INF_F;
+}
+
+// One node = four 256-bit read-only loads (LDG.E.256): a lane whose ray is alone in its node touches the node's
+// cache line four times instead of seven (the L1 processes one line per load instruction per cycle, and incoherent
+// rays make every lane's node a different line: the traversal kernels are bound by exactly that).
+struct NodeData {
+  float4 lo_x, hi_x, lo_y, hi_y, lo_z, hi_z;
+  uint4 ch;
+};
+__device__ __forceinline__ void ldg256(const void *p, float4 &a, float4 &b) {
+  asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+               : "l"(p));
+}
+__device__ __forceinline__ NodeData load_node(const DevNode *nodes, uint32_t idx) {
+  const char *p = reinterpret_cast<const char *>(nodes + idx);
+  NodeData n;
+  ldg256(p, n.lo_x, n.hi_x);
+  ldg256(p + 32, n.lo_y, n.hi_y);
+  ldg256(p + 64, n.lo_z, n.hi_z);
+  n.ch = __ldg(reinterpret_cast<const uint4 *>(p + 96));
+  return n;
+}
+
 #define PTB_STACK 96
 
 #define PTB_CSWAP(ta, ra, tb, rb) \
@@ -194,10 +241,9 @@ __device__ __forceinline__ void trace_closest(const DevScene &S, const Ray &r, f
   uint32_t cur = 0;  // root node
   for (;;) {
     if (!(cur & 0x80000000u)) {
-      const float4 *np = reinterpret_cast<const float4 *>(S.nodes + cur);
-      float4 lx = __ldg(np), ly = __ldg(np + 1), lz = __ldg(np + 2);
-      float4 hx = __ldg(np + 3), hy = __ldg(np + 4), hz = __ldg(np + 5);
-      uint4 ch = __ldg(reinterpret_cast<const uint4 *>(np + 6));
+      const NodeData nd = load_node(S.nodes, cur);
+      const float4 lx = nd.lo_x, ly = nd.lo_y, lz = nd.lo_z, hx = nd.hi_x, hy = nd.hi_y, hz = nd.hi_z;
+      const uint4 ch = nd.ch;
       float t0 = ch.x == 0xFFFFFFFFu ? CUDART_INF_F : slab(lx.x, ly.x, lz.x, hx.x, hy.x, hz.x, r, pre, t_prune);
       float t1 = ch.y == 0xFFFFFFFFu ? CUDART_INF_F : slab(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, r, pre, t_prune);
       float t2 = ch.z == 0xFFFFFFFFu ? CUDART_INF_F : slab(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, r, pre, t_prune);

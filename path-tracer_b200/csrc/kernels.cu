@@ -7,8 +7,10 @@
 //   k_shade    renderer/mod.rs:184-186,207-225,230-278; brdf/cook_torrance.rs; utils.rs:23-31
 //   k_shadow   renderer/mod.rs:281-333
 //   k_resolve  renderer/mod.rs:130 ; k_tonemap renderer/mod.rs:150-162,335-353
+#include <cstdlib>
+
 #include "kernels.cuh"
-#include "path.cuh"
+#include "traverse.cuh"
 
 namespace ptb {
 
@@ -95,8 +97,8 @@ __global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene
 }
 
 // extend: closest accepted hit (alpha walk included) of every queued ray.
-__global__ void __launch_bounds__(128) k_extend(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
-                                                WaveState W, uint32_t bounce) {
+__global__ void __launch_bounds__(128) k_extend_v1(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
+                                                   WaveState W, uint32_t bounce) {
   const uint32_t in = bounce & 1u, outb = in ^ 1u;
   const uint32_t n = W.counters[CTR_QUEUE0 + in];
   if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -118,6 +120,96 @@ __global__ void __launch_bounds__(128) k_extend(const __grid_constant__ DevScene
     extend_ray(S, make_key(P, (uint32_t)__float_as_int(d4.w)), bounce, r, st, recasts);
     W.hit[q] = make_float4(st.best_t, st.u, st.v, __int_as_float(st.best_id));
     W.hit_idx[q] = st.idx;
+  }
+  recasts = __reduce_add_sync(0xffffffffu, recasts);
+  if (lane_id() == 0 && recasts) stat_add(W.counters, CTR_STAT_RECAST, recasts);
+}
+
+// Lane-level work fetch: every idle lane of the warp takes the next queue position (one atomic per refill).
+// `drained` becomes true (warp-uniformly) once the cursor has passed n.
+__device__ __forceinline__ uint32_t refill(uint32_t *cursor, bool idle, uint32_t n, bool &drained) {
+  uint32_t m = __ballot_sync(0xffffffffu, idle);
+  uint32_t idx = 0xFFFFFFFFu;
+  if (m && !drained) {
+    int leader = __ffs(m) - 1;
+    uint32_t cnt = (uint32_t)__popc(m), base = 0;
+    if ((int)lane_id() == leader) base = atomicAdd(cursor, cnt);
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (idle) idx = base + (uint32_t)__popc(m & lanemask_lt());
+    if (base + cnt >= n) drained = true;
+  }
+  return idx < n ? idx : 0xFFFFFFFFu;
+}
+
+constexpr int REFILL_THRESHOLD = 24;  // refill when fewer lanes than this still own a ray
+constexpr int LEAF_THRESHOLD = 12;    // run the (divergent) primitive test once this many lanes wait at a leaf
+
+// extend: closest accepted hit (alpha walk included) of every queued ray.  Persistent warps with lane-level ray
+// replacement; inside a warp, lanes that reach a leaf wait until LEAF_THRESHOLD lanes have one (or nobody is at an
+// inner node any more), so that node visits and primitive tests each run with most lanes active ("while-while").
+__global__ void __launch_bounds__(128) k_extend(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
+                                                WaveState W, uint32_t bounce) {
+  const uint32_t in = bounce & 1u, outb = in ^ 1u;
+  const uint32_t n = W.counters[CTR_QUEUE0 + in];
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    W.counters[CTR_QUEUE0 + outb] = 0;
+    W.counters[CTR_SHADOW] = 0;
+    W.counters[CTR_WORK_SHADE] = 0;
+    stat_add(W.counters, CTR_STAT_EXTEND, n);
+  }
+  constexpr uint32_t NONE = 0xFFFFFFFFu;
+  uint32_t recasts = 0;
+  ClosestTrav tv;
+  NodeOrder no{};
+  float stk_t[PTB_STACK];
+  uint32_t stk_r[PTB_STACK];
+  uint32_t q = NONE, slot = 0, alpha_j = 0;
+  bool drained = false;
+  tv.cur = ClosestTrav::DONE;
+  for (;;) {
+    uint32_t nq = refill(&W.counters[CTR_WORK_EXTEND], q == NONE, n, drained);
+    if (nq != NONE) {
+      q = nq;
+      float4 o4 = W.ray_o[in][q], d4 = W.ray_d[in][q];
+      Ray r;
+      r.o = mk3(o4.x, o4.y, o4.z);
+      r.d = mk3(d4.x, d4.y, d4.z);
+      slot = (uint32_t)__float_as_int(d4.w);
+      alpha_j = 0;
+      tv.begin(r, -1.0f, -1);
+      no = node_order(tv.r, tv.pre);
+      W.hit_idx[q] = -1;  // a miss unless a hit is recorded below
+    }
+    if (__ballot_sync(0xffffffffu, q != NONE) == 0) break;
+    for (;;) {
+      const bool has = q != NONE;
+      if (has && tv.at_inner()) tv.node_step(S, no, stk_t, stk_r);
+      const bool leaf = has && tv.at_leaf();
+      const uint32_t m_leaf = __ballot_sync(0xffffffffu, leaf);
+      const uint32_t m_inner = __ballot_sync(0xffffffffu, has && tv.at_inner());
+      if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) tv.leaf_step(S, stk_t, stk_r);
+      if (has && tv.cur == ClosestTrav::DONE) {
+        bool done = true;
+        if (tv.st.idx >= 0) {
+          // record the examined hit: it is shaded unless a later hit of the alpha walk replaces it (mod.rs:188-205)
+          W.hit[q] = make_float4(tv.st.best_t, tv.st.u, tv.st.v, __int_as_float(tv.st.best_id));
+          W.hit_idx[q] = tv.st.idx;
+          if (S.any_alpha && (tv.st.flags & TRI_FLAG_ALPHA)) {
+            float op = hit_opacity(S, tv.st.idx, tv.st.u, tv.st.v);
+            bool accept = op >= 1.0f;
+            if (!accept && op > 0.001f) accept = rng_alpha(make_key(P, slot), bounce, alpha_j++) < op;
+            if (!accept) {
+              tv.restart_behind();
+              ++recasts;
+              done = false;
+            }
+          }
+        }
+        if (done) q = NONE;
+      }
+      const uint32_t busy = __ballot_sync(0xffffffffu, q != NONE);
+      if (busy == 0 || (!drained && __popc(busy) < REFILL_THRESHOLD)) break;
+    }
   }
   recasts = __reduce_add_sync(0xffffffffu, recasts);
   if (lane_id() == 0 && recasts) stat_add(W.counters, CTR_STAT_RECAST, recasts);
@@ -256,7 +348,7 @@ __global__ void __launch_bounds__(256) k_triangle_intersect(const float *__restr
 }
 
 // shadow: transmittance of every queued shadow ray; adds contribution * transmittance to the path's radiance.
-__global__ void __launch_bounds__(128) k_shadow(const __grid_constant__ DevScene S, WaveState W) {
+__global__ void __launch_bounds__(128) k_shadow_v1(const __grid_constant__ DevScene S, WaveState W) {
   uint32_t n = W.counters[CTR_SHADOW];
   if (n > W.shadow_capacity) n = W.shadow_capacity;
   if (blockIdx.x == 0 && threadIdx.x == 0) stat_add(W.counters, CTR_STAT_SHADOW, n);
@@ -274,6 +366,56 @@ __global__ void __launch_bounds__(128) k_shadow(const __grid_constant__ DevScene
       atomicAdd(dst + 0, c4.x * tr);
       atomicAdd(dst + 1, c4.y * tr);
       atomicAdd(dst + 2, c4.z * tr);
+    }
+  }
+}
+
+// shadow: transmittance of every queued shadow ray; adds contribution * transmittance to the path's radiance.
+// Same lane-level ray replacement and node / primitive phases as k_extend.
+__global__ void __launch_bounds__(128) k_shadow(const __grid_constant__ DevScene S, WaveState W) {
+  uint32_t n = W.counters[CTR_SHADOW];
+  if (n > W.shadow_capacity) n = W.shadow_capacity;
+  if (blockIdx.x == 0 && threadIdx.x == 0) stat_add(W.counters, CTR_STAT_SHADOW, n);
+  constexpr uint32_t NONE = 0xFFFFFFFFu;
+  ShadowTrav tv;
+  NodeOrder no{};
+  uint32_t stk[PTB_STACK];
+  uint32_t q = NONE, slot = 0;
+  V3 c{};
+  bool drained = false;
+  tv.cur = ShadowTrav::DONE;
+  for (;;) {
+    uint32_t nq = refill(&W.counters[CTR_WORK_SHADOW], q == NONE, n, drained);
+    if (nq != NONE) {
+      q = nq;
+      float4 o4 = W.sh_o[q], d4 = W.sh_d[q], c4 = W.sh_c[q], p4 = W.sh_p[q];
+      Ray r;
+      r.o = mk3(o4.x, o4.y, o4.z);
+      r.d = mk3(d4.x, d4.y, d4.z);
+      slot = (uint32_t)__float_as_int(d4.w);
+      c = mk3(c4.x, c4.y, c4.z);
+      tv.begin(r, o4.w, mk3(p4.x, p4.y, p4.z), c4.w, p4.w);
+      no = node_order(tv.r, tv.pre);
+    }
+    if (__ballot_sync(0xffffffffu, q != NONE) == 0) break;
+    for (;;) {
+      const bool has = q != NONE;
+      if (has && tv.at_inner()) tv.node_step(S, no, stk);
+      const bool leaf = has && tv.at_leaf();
+      const uint32_t m_leaf = __ballot_sync(0xffffffffu, leaf);
+      const uint32_t m_inner = __ballot_sync(0xffffffffu, has && tv.at_inner());
+      if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) tv.leaf_step(S, stk);
+      if (has && tv.cur == ShadowTrav::DONE) {
+        if (tv.tr != 0.0f) {
+          float *dst = reinterpret_cast<float *>(W.radiance + slot);
+          atomicAdd(dst + 0, c.x * tv.tr);
+          atomicAdd(dst + 1, c.y * tv.tr);
+          atomicAdd(dst + 2, c.z * tv.tr);
+        }
+        q = NONE;
+      }
+      const uint32_t busy = __ballot_sync(0xffffffffu, q != NONE);
+      if (busy == 0 || (!drained && __popc(busy) < REFILL_THRESHOLD)) break;
     }
   }
 }
@@ -316,7 +458,15 @@ static int sm_count() {
   }
   return g_sm_count;
 }
-constexpr int PERSIST_CTAS_PER_SM = 8;  // 8 x 128 threads = 1024 resident threads per SM
+constexpr int PERSIST_CTAS_PER_SM = 8;
+static int variant() {  // PT_B200_VARIANT=1 selects the warp-granular work fetch kernels (A/B measurements only)
+  static int v = -1;
+  if (v < 0) {
+    const char *e = getenv("PT_B200_VARIANT");
+    v = e ? atoi(e) : 0;
+  }
+  return v;
+}  // 8 x 128 threads = 1024 resident threads per SM
 
 void launch_trace_closest(const DevScene &S, const float *rays, uint32_t n, pt_hit *out, uint32_t *cursor, cudaStream_t st) {
   cudaMemsetAsync(cursor, 0, sizeof(uint32_t), st);
@@ -337,13 +487,15 @@ void launch_raygen(const DevScene &S, const WaveParams &P, const WaveState &W, c
   k_raygen<<<(P.n_paths + 255) / 256, 256, 0, st>>>(S, P, W);
 }
 void launch_extend(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st) {
-  k_extend<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, P, W, bounce);
+  if (variant() == 1) k_extend_v1<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, P, W, bounce);
+  else k_extend<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, P, W, bounce);
 }
 void launch_shade(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st) {
   k_shade<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, P, W, bounce);
 }
 void launch_shadow(const DevScene &S, const WaveState &W, cudaStream_t st) {
-  k_shadow<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, W);
+  if (variant() == 1) k_shadow_v1<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, W);
+  else k_shadow<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, W);
 }
 void launch_resolve(const WaveParams &P, const WaveState &W, float *accum, cudaStream_t st) {
   uint32_t npix = P.width * P.height;

@@ -99,10 +99,9 @@ __device__ __forceinline__ float trace_transmittance(const DevScene &S, const Ra
   uint32_t cur = 0;
   for (;;) {
     if (!(cur & 0x80000000u)) {
-      const float4 *np = reinterpret_cast<const float4 *>(S.nodes + cur);
-      float4 lx = __ldg(np), ly = __ldg(np + 1), lz = __ldg(np + 2);
-      float4 hx = __ldg(np + 3), hy = __ldg(np + 4), hz = __ldg(np + 5);
-      uint4 ch = __ldg(reinterpret_cast<const uint4 *>(np + 6));
+      const NodeData nd = load_node(S.nodes, cur);
+      const float4 lx = nd.lo_x, ly = nd.lo_y, lz = nd.lo_z, hx = nd.hi_x, hy = nd.hi_y, hz = nd.hi_z;
+      const uint4 ch = nd.ch;
       if (ch.x != 0xFFFFFFFFu && slab(lx.x, ly.x, lz.x, hx.x, hy.x, hz.x, r, pre, t_max) < CUDART_INF_F) stk[sp++] = ch.x;
       if (ch.y != 0xFFFFFFFFu && slab(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, r, pre, t_max) < CUDART_INF_F) stk[sp++] = ch.y;
       if (ch.z != 0xFFFFFFFFu && slab(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, r, pre, t_max) < CUDART_INF_F) stk[sp++] = ch.z;

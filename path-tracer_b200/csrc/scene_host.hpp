@@ -42,7 +42,7 @@ struct HostScene {
 //                         bits[2:0] = count-1
 //   bit31=1, bit30=1      sphere leaf: bits[29:0] = index into the sphere array
 struct alignas(128) Bvh4Node {
-  float lo_x[4], lo_y[4], lo_z[4], hi_x[4], hi_y[4], hi_z[4];
+  float lo_x[4], hi_x[4], lo_y[4], hi_y[4], lo_z[4], hi_z[4];  // one 32-byte chunk per axis (256-bit loads)
   uint32_t child[4];
   uint32_t pad[4];
 };
