@@ -35,7 +35,7 @@ def lib():
     """dlopen path-tracer_b200/libpt_b200.so (built in-tree by csrc/Makefile); fails loudly when missing."""
     global _LIB
     if _LIB is None:
-        so = os.path.join(_HERE, "libpt_b200.so")
+        so = os.environ.get("PT_B200_LIB") or os.path.join(_HERE, "libpt_b200.so")  # override: A/B builds only
         if not os.path.exists(so):
             raise PtError(-4, "libpt_b200.so not built: run `python __graft_entry__.py` (no CPU fallback exists)")
         L = C.CDLL(so)

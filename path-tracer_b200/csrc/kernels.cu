@@ -12,6 +12,16 @@
 #include "kernels.cuh"
 #include "traverse.cuh"
 
+#ifndef PTB_EXTEND_MINB
+#define PTB_EXTEND_MINB 1
+#endif
+#ifndef PTB_SHADE_MINB
+#define PTB_SHADE_MINB 1
+#endif
+#ifndef PTB_SHADOW_MINB
+#define PTB_SHADOW_MINB 1
+#endif
+
 namespace ptb {
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
@@ -147,7 +157,7 @@ constexpr int LEAF_THRESHOLD = 12;    // run the (divergent) primitive test once
 // extend: closest accepted hit (alpha walk included) of every queued ray.  Persistent warps with lane-level ray
 // replacement; inside a warp, lanes that reach a leaf wait until LEAF_THRESHOLD lanes have one (or nobody is at an
 // inner node any more), so that node visits and primitive tests each run with most lanes active ("while-while").
-__global__ void __launch_bounds__(128) k_extend(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
+__global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
                                                 WaveState W, uint32_t bounce) {
   const uint32_t in = bounce & 1u, outb = in ^ 1u;
   const uint32_t n = W.counters[CTR_QUEUE0 + in];
@@ -217,7 +227,7 @@ __global__ void __launch_bounds__(128) k_extend(const __grid_constant__ DevScene
 
 // shade: miss/background, emissive, next-event setup (shadow queue), GGX sample, throughput, cutoff, RR,
 // and compaction of the surviving paths into the other queue buffer.
-__global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
+__global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
                                                WaveState W, uint32_t bounce) {
   const uint32_t in = bounce & 1u, outb = in ^ 1u;
   const uint32_t n = W.counters[CTR_QUEUE0 + in];
@@ -372,7 +382,7 @@ __global__ void __launch_bounds__(128) k_shadow_v1(const __grid_constant__ DevSc
 
 // shadow: transmittance of every queued shadow ray; adds contribution * transmittance to the path's radiance.
 // Same lane-level ray replacement and node / primitive phases as k_extend.
-__global__ void __launch_bounds__(128) k_shadow(const __grid_constant__ DevScene S, WaveState W) {
+__global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_constant__ DevScene S, WaveState W) {
   uint32_t n = W.counters[CTR_SHADOW];
   if (n > W.shadow_capacity) n = W.shadow_capacity;
   if (blockIdx.x == 0 && threadIdx.x == 0) stat_add(W.counters, CTR_STAT_SHADOW, n);
