@@ -88,9 +88,8 @@ struct WaveState {
   float4 *ray_o[2];   // xyz origin
   float4 *ray_d[2];   // xyz direction, w = slot (int bits)
   float4 *thr[2];     // xyz throughput
-  float4 *hit;        // HitRec.h
-  int32_t *hit_idx;   // HitRec.idx
-  float4 *radiance;   // per slot: xyz sum of this path's contributions
+  float4 *hit;        // (dist, u, v, HitRec.idx bits; idx < 0 = miss)
+  float4 *radiance;   // per slot: xyz sum of this path's contributions (zeroed by raygen, atomically added to)
   // shadow queue (one entry per light per shaded hit with a non-zero unshadowed contribution)
   float4 *sh_o;       // xyz origin, w = point-light distance (or -1 for directional)
   float4 *sh_d;       // xyz direction, w = slot
@@ -101,22 +100,24 @@ struct WaveState {
   uint32_t shadow_capacity;
 };
 
-// counters[] layout (uint32): queue sizes are produced on the device and consumed by the next
-// persistent kernel, so the host never synchronises inside a frame.
+// counters[] layout (uint32): queue sizes are produced on the device and consumed by the next persistent kernel, so
+// the host never synchronises inside a frame.  Path queue buffer b and the shadow queue filled together with it
+// share one aligned 64-bit word (low = path queue size, high = shadow queue size) so that k_shade reserves its slots
+// in both with ONE atomic.
 enum {
-  CTR_QUEUE0 = 0,      // size of path queue buffer 0
-  CTR_QUEUE1 = 1,      // size of path queue buffer 1
-  CTR_SHADOW = 2,      // size of the shadow queue
-  CTR_WORK_EXTEND = 3, // persistent work-fetch cursors
-  CTR_WORK_SHADE = 4,
+  CTR_QUEUE0 = 0,   // size of path queue buffer 0        } one 64-bit word
+  CTR_SHADOW0 = 1,  // shadow rays emitted with buffer 0  }
+  CTR_QUEUE1 = 2,   // size of path queue buffer 1        } one 64-bit word
+  CTR_SHADOW1 = 3,  // shadow rays emitted with buffer 1  }
+  CTR_WORK_EXTEND = 4,  // persistent work-fetch cursors
   CTR_WORK_SHADOW = 5,
-  CTR_PAD0 = 6,
-  CTR_PAD1 = 7,
-  CTR_STAT_EXTEND = 8,   // 64-bit statistics start here (pairs)
+  CTR_STAT_EXTEND = 8,  // 64-bit statistics start here (pairs)
   CTR_STAT_SHADOW = 10,
   CTR_STAT_RECAST = 12,
   CTR_COUNT = 16
 };
+#define CTR_QUEUE(b) (2u * (b))
+#define CTR_SHADOW(b) (2u * (b) + 1u)
 
 struct WaveParams {
   uint32_t width, height;

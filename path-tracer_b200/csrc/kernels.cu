@@ -13,10 +13,10 @@
 #include "traverse.cuh"
 
 #ifndef PTB_EXTEND_MINB
-#define PTB_EXTEND_MINB 1
+#define PTB_EXTEND_MINB 7
 #endif
 #ifndef PTB_SHADE_MINB
-#define PTB_SHADE_MINB 1
+#define PTB_SHADE_MINB 6
 #endif
 #ifndef PTB_SHADOW_MINB
 #define PTB_SHADOW_MINB 1
@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene
                                                 WaveState W) {
   uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
   if (slot == 0) {
-    W.counters[CTR_QUEUE0] = P.n_paths;
+    W.counters[CTR_QUEUE(0)] = P.n_paths;
     W.counters[CTR_WORK_EXTEND] = 0;
   }
   if (slot >= P.n_paths) return;
@@ -104,35 +104,6 @@ __global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene
   W.ray_d[0][slot] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float((int)slot));
   W.thr[0][slot] = make_float4(1.f, 1.f, 1.f, 0.f);
   W.radiance[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
-}
-
-// extend: closest accepted hit (alpha walk included) of every queued ray.
-__global__ void __launch_bounds__(128) k_extend_v1(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
-                                                   WaveState W, uint32_t bounce) {
-  const uint32_t in = bounce & 1u, outb = in ^ 1u;
-  const uint32_t n = W.counters[CTR_QUEUE0 + in];
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    W.counters[CTR_QUEUE0 + outb] = 0;
-    W.counters[CTR_SHADOW] = 0;
-    W.counters[CTR_WORK_SHADE] = 0;
-    stat_add(W.counters, CTR_STAT_EXTEND, n);
-  }
-  uint32_t recasts = 0;
-  for (;;) {
-    uint32_t q = fetch_work(&W.counters[CTR_WORK_EXTEND]);
-    if (__all_sync(0xffffffffu, q >= n)) break;
-    if (q >= n) continue;
-    float4 o4 = W.ray_o[in][q], d4 = W.ray_d[in][q];
-    Ray r;
-    r.o = mk3(o4.x, o4.y, o4.z);
-    r.d = mk3(d4.x, d4.y, d4.z);
-    TraceState st;
-    extend_ray(S, make_key(P, (uint32_t)__float_as_int(d4.w)), bounce, r, st, recasts);
-    W.hit[q] = make_float4(st.best_t, st.u, st.v, __int_as_float(st.best_id));
-    W.hit_idx[q] = st.idx;
-  }
-  recasts = __reduce_add_sync(0xffffffffu, recasts);
-  if (lane_id() == 0 && recasts) stat_add(W.counters, CTR_STAT_RECAST, recasts);
 }
 
 // Lane-level work fetch: every idle lane of the warp takes the next queue position (one atomic per refill).
@@ -160,11 +131,11 @@ constexpr int LEAF_THRESHOLD = 12;    // run the (divergent) primitive test once
 __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
                                                 WaveState W, uint32_t bounce) {
   const uint32_t in = bounce & 1u, outb = in ^ 1u;
-  const uint32_t n = W.counters[CTR_QUEUE0 + in];
+  const uint32_t n = W.counters[CTR_QUEUE(in)];
   if (blockIdx.x == 0 && threadIdx.x == 0) {
-    W.counters[CTR_QUEUE0 + outb] = 0;
-    W.counters[CTR_SHADOW] = 0;
-    W.counters[CTR_WORK_SHADE] = 0;
+    W.counters[CTR_QUEUE(outb)] = 0;  // the queues k_shade(bounce) appends to
+    W.counters[CTR_SHADOW(outb)] = 0;
+    W.counters[CTR_WORK_SHADOW] = 0;
     stat_add(W.counters, CTR_STAT_EXTEND, n);
   }
   constexpr uint32_t NONE = 0xFFFFFFFFu;
@@ -174,7 +145,7 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
   float stk_t[PTB_STACK];
   uint32_t stk_r[PTB_STACK];
   uint32_t q = NONE, slot = 0, alpha_j = 0;
-  bool drained = false;
+  bool drained = false, recorded = false;
   tv.cur = ClosestTrav::DONE;
   for (;;) {
     uint32_t nq = refill(&W.counters[CTR_WORK_EXTEND], q == NONE, n, drained);
@@ -188,7 +159,7 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
       alpha_j = 0;
       tv.begin(r, -1.0f, -1);
       no = node_order(tv.r, tv.pre);
-      W.hit_idx[q] = -1;  // a miss unless a hit is recorded below
+      recorded = false;
     }
     if (__ballot_sync(0xffffffffu, q != NONE) == 0) break;
     for (;;) {
@@ -202,8 +173,8 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
         bool done = true;
         if (tv.st.idx >= 0) {
           // record the examined hit: it is shaded unless a later hit of the alpha walk replaces it (mod.rs:188-205)
-          W.hit[q] = make_float4(tv.st.best_t, tv.st.u, tv.st.v, __int_as_float(tv.st.best_id));
-          W.hit_idx[q] = tv.st.idx;
+          W.hit[q] = make_float4(tv.st.best_t, tv.st.u, tv.st.v, __int_as_float(tv.st.idx));
+          recorded = true;
           if (S.any_alpha && (tv.st.flags & TRI_FLAG_ALPHA)) {
             float op = hit_opacity(S, tv.st.idx, tv.st.u, tv.st.v);
             bool accept = op >= 1.0f;
@@ -215,7 +186,10 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
             }
           }
         }
-        if (done) q = NONE;
+        if (done) {
+          if (!recorded) W.hit[q] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));  // miss
+          q = NONE;
+        }
       }
       const uint32_t busy = __ballot_sync(0xffffffffu, q != NONE);
       if (busy == 0 || (!drained && __popc(busy) < REFILL_THRESHOLD)) break;
@@ -225,60 +199,92 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
   if (lane_id() == 0 && recasts) stat_add(W.counters, CTR_STAT_RECAST, recasts);
 }
 
+// Warp-aggregated append to the path queue AND the shadow queue filled with it: one 64-bit atomic per warp reserves
+// slots in both (low word = path queue, high word = shadow queue).  Returns the lane's positions.
+__device__ __forceinline__ void warp_append2(uint32_t *pair, bool want_path, bool want_shadow, uint32_t &pos_path,
+                                             uint32_t &pos_shadow) {
+  const uint32_t mp = __ballot_sync(0xffffffffu, want_path), ms = __ballot_sync(0xffffffffu, want_shadow);
+  pos_path = pos_shadow = 0;
+  if ((mp | ms) == 0) return;
+  unsigned long long base = 0;
+  if (lane_id() == 0)
+    base = atomicAdd(reinterpret_cast<unsigned long long *>(pair),
+                     (unsigned long long)__popc(mp) | ((unsigned long long)__popc(ms) << 32));
+  base = __shfl_sync(0xffffffffu, base, 0);
+  pos_path = (uint32_t)base + (uint32_t)__popc(mp & lanemask_lt());
+  pos_shadow = (uint32_t)(base >> 32) + (uint32_t)__popc(ms & lanemask_lt());
+}
+
+__device__ __forceinline__ void add_radiance(float4 *radiance, uint32_t slot, V3 c) {
+  float *dst = reinterpret_cast<float *>(radiance + slot);
+  if (c.x != 0.0f) atomicAdd(dst + 0, c.x);
+  if (c.y != 0.0f) atomicAdd(dst + 1, c.y);
+  if (c.z != 0.0f) atomicAdd(dst + 2, c.z);
+}
+
 // shade: miss/background, emissive, next-event setup (shadow queue), GGX sample, throughput, cutoff, RR,
-// and compaction of the surviving paths into the other queue buffer.
-__global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
-                                               WaveState W, uint32_t bounce) {
+// and compaction of the surviving paths into the other queue buffer.  Queue positions are assigned statically
+// (warp-strided): no work-fetch atomic; the last light's shadow entry and the next ray share one reservation atomic.
+__global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_constant__ DevScene S,
+                                                               const __grid_constant__ WaveParams P, WaveState W,
+                                                               uint32_t bounce) {
   const uint32_t in = bounce & 1u, outb = in ^ 1u;
-  const uint32_t n = W.counters[CTR_QUEUE0 + in];
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
-    W.counters[CTR_WORK_EXTEND] = 0;
-    W.counters[CTR_WORK_SHADOW] = 0;
-  }
-  for (;;) {
-    uint32_t q = fetch_work(&W.counters[CTR_WORK_SHADE]);
-    if (__all_sync(0xffffffffu, q >= n)) break;
+  const uint32_t n = W.counters[CTR_QUEUE(in)];
+  if (blockIdx.x == 0 && threadIdx.x == 0) W.counters[CTR_WORK_EXTEND] = 0;
+  uint32_t *pair = &W.counters[CTR_QUEUE(outb)];
+  const uint32_t warps = gridDim.x * (blockDim.x >> 5), warp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  for (uint32_t base = warp * 32u; base < n; base += warps * 32u) {
+    const uint32_t q = base + lane_id();
     const bool active = q < n;
     Ray r{};
-    V3 thr{}, rad{};
+    V3 thr{}, rad = mk3(0.f, 0.f, 0.f);
     ShadeCtx ctx{};
     uint32_t slot = 0;
     if (active) {
       float4 o4 = W.ray_o[in][q], d4 = W.ray_d[in][q], t4 = W.thr[in][q], h4 = W.hit[q];
-      int idx = W.hit_idx[q];
       slot = (uint32_t)__float_as_int(d4.w);
       r.o = mk3(o4.x, o4.y, o4.z);
       r.d = mk3(d4.x, d4.y, d4.z);
       thr = mk3(t4.x, t4.y, t4.z);
-      float4 r4 = W.radiance[slot];
-      rad = mk3(r4.x, r4.y, r4.z);
-      shade_begin(S, r, h4.x, h4.y, h4.z, idx, thr, rad, ctx);
+      shade_begin(S, r, h4.x, h4.y, h4.z, __float_as_int(h4.w), thr, rad, ctx);
+      add_radiance(W.radiance, slot, rad);  // background (miss) or emissive: usually zero, then no memory traffic
     }
-    // next-event estimation set-up: one shadow-queue entry per light (mod.rs:248-262)
-    for (uint32_t li = 0; li < S.n_lights; ++li) {
-      bool want = false;
-      V3 so{}, sd{}, c{};
-      float limit = -1.0f;
+    // next-event estimation set-up: one shadow-queue entry per light (mod.rs:248-262); the LAST light's reservation
+    // is fused with the path-queue reservation below
+    const uint32_t nl = S.n_lights;
+    bool want = false;
+    V3 so{}, sd{}, c{};
+    float limit = -1.0f;
+    for (uint32_t li = 0; li < nl; ++li) {
+      want = false;
       if (ctx.lit) want = light_request(S, ctx, thr, li, so, sd, c, limit);
-      uint32_t pos = warp_append(&W.counters[CTR_SHADOW], want);
-      if (want && pos < W.shadow_capacity) {
-        W.sh_o[pos] = make_float4(so.x, so.y, so.z, limit);
-        W.sh_d[pos] = make_float4(sd.x, sd.y, sd.z, __int_as_float((int)slot));
-        W.sh_c[pos] = make_float4(c.x, c.y, c.z, ctx.sf.is_sphere ? __int_as_float(0x7fc00000) : ctx.sf.tu);
-        W.sh_p[pos] = make_float4(ctx.sf.position.x, ctx.sf.position.y, ctx.sf.position.z, ctx.sf.tv);
+      if (li + 1 == nl) break;
+      uint32_t pp, ps;
+      warp_append2(pair, false, want, pp, ps);
+      if (want && ps < W.shadow_capacity) {
+        W.sh_o[ps] = make_float4(so.x, so.y, so.z, limit);
+        W.sh_d[ps] = make_float4(sd.x, sd.y, sd.z, __int_as_float((int)slot));
+        W.sh_c[ps] = make_float4(c.x, c.y, c.z, ctx.sf.is_sphere ? __int_as_float(0x7fc00000) : ctx.sf.tu);
+        W.sh_p[ps] = make_float4(ctx.sf.position.x, ctx.sf.position.y, ctx.sf.position.z, ctx.sf.tv);
       }
     }
+    const float pu = ctx.sf.is_sphere ? __int_as_float(0x7fc00000) : ctx.sf.tu, pv = ctx.sf.tv;
+    const V3 ppos = ctx.sf.position;
     Ray next{};
     bool alive = false;
-    if (active) {
-      alive = shade_finish(P, make_key(P, slot), bounce, ctx, thr, next);
-      W.radiance[slot] = make_float4(rad.x, rad.y, rad.z, 0.f);
+    if (active) alive = shade_finish(P, make_key(P, slot), bounce, ctx, thr, next);
+    uint32_t pp, ps;
+    warp_append2(pair, alive, want, pp, ps);
+    if (want && ps < W.shadow_capacity) {
+      W.sh_o[ps] = make_float4(so.x, so.y, so.z, limit);
+      W.sh_d[ps] = make_float4(sd.x, sd.y, sd.z, __int_as_float((int)slot));
+      W.sh_c[ps] = make_float4(c.x, c.y, c.z, pu);
+      W.sh_p[ps] = make_float4(ppos.x, ppos.y, ppos.z, pv);
     }
-    uint32_t pos = warp_append(&W.counters[CTR_QUEUE0 + outb], alive);
     if (alive) {
-      W.ray_o[outb][pos] = make_float4(next.o.x, next.o.y, next.o.z, 0.f);
-      W.ray_d[outb][pos] = make_float4(next.d.x, next.d.y, next.d.z, __int_as_float((int)slot));
-      W.thr[outb][pos] = make_float4(thr.x, thr.y, thr.z, 0.f);
+      W.ray_o[outb][pp] = make_float4(next.o.x, next.o.y, next.o.z, 0.f);
+      W.ray_d[outb][pp] = make_float4(next.d.x, next.d.y, next.d.z, __int_as_float((int)slot));
+      W.thr[outb][pp] = make_float4(thr.x, thr.y, thr.z, 0.f);
     }
   }
 }
@@ -358,32 +364,9 @@ __global__ void __launch_bounds__(256) k_triangle_intersect(const float *__restr
 }
 
 // shadow: transmittance of every queued shadow ray; adds contribution * transmittance to the path's radiance.
-__global__ void __launch_bounds__(128) k_shadow_v1(const __grid_constant__ DevScene S, WaveState W) {
-  uint32_t n = W.counters[CTR_SHADOW];
-  if (n > W.shadow_capacity) n = W.shadow_capacity;
-  if (blockIdx.x == 0 && threadIdx.x == 0) stat_add(W.counters, CTR_STAT_SHADOW, n);
-  for (;;) {
-    uint32_t q = fetch_work(&W.counters[CTR_WORK_SHADOW]);
-    if (__all_sync(0xffffffffu, q >= n)) break;
-    if (q >= n) continue;
-    float4 o4 = W.sh_o[q], d4 = W.sh_d[q], c4 = W.sh_c[q], p4 = W.sh_p[q];
-    Ray r;
-    r.o = mk3(o4.x, o4.y, o4.z);
-    r.d = mk3(d4.x, d4.y, d4.z);
-    float tr = trace_transmittance(S, r, o4.w, mk3(p4.x, p4.y, p4.z), c4.w, p4.w);
-    if (tr != 0.0f) {
-      float *dst = reinterpret_cast<float *>(W.radiance + (uint32_t)__float_as_int(d4.w));
-      atomicAdd(dst + 0, c4.x * tr);
-      atomicAdd(dst + 1, c4.y * tr);
-      atomicAdd(dst + 2, c4.z * tr);
-    }
-  }
-}
-
-// shadow: transmittance of every queued shadow ray; adds contribution * transmittance to the path's radiance.
 // Same lane-level ray replacement and node / primitive phases as k_extend.
-__global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_constant__ DevScene S, WaveState W) {
-  uint32_t n = W.counters[CTR_SHADOW];
+__global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_constant__ DevScene S, WaveState W, uint32_t bounce) {
+  uint32_t n = W.counters[CTR_SHADOW((bounce & 1u) ^ 1u)];
   if (n > W.shadow_capacity) n = W.shadow_capacity;
   if (blockIdx.x == 0 && threadIdx.x == 0) stat_add(W.counters, CTR_STAT_SHADOW, n);
   constexpr uint32_t NONE = 0xFFFFFFFFu;
@@ -469,14 +452,14 @@ static int sm_count() {
   return g_sm_count;
 }
 constexpr int PERSIST_CTAS_PER_SM = 8;
-static int variant() {  // PT_B200_VARIANT=1 selects the warp-granular work fetch kernels (A/B measurements only)
-  static int v = -1;
-  if (v < 0) {
-    const char *e = getenv("PT_B200_VARIANT");
-    v = e ? atoi(e) : 0;
-  }
-  return v;
-}  // 8 x 128 threads = 1024 resident threads per SM
+// Grid of a persistent kernel: exactly the CTAs that are resident at once (occupancy API), so that statically
+// partitioned kernels have no second round of CTAs.
+template <typename K>
+static int resident_grid(K kernel, int threads) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0) != cudaSuccess || per_sm <= 0) per_sm = 4;
+  return sm_count() * per_sm;
+}
 
 void launch_trace_closest(const DevScene &S, const float *rays, uint32_t n, pt_hit *out, uint32_t *cursor, cudaStream_t st) {
   cudaMemsetAsync(cursor, 0, sizeof(uint32_t), st);
@@ -497,15 +480,15 @@ void launch_raygen(const DevScene &S, const WaveParams &P, const WaveState &W, c
   k_raygen<<<(P.n_paths + 255) / 256, 256, 0, st>>>(S, P, W);
 }
 void launch_extend(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st) {
-  if (variant() == 1) k_extend_v1<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, P, W, bounce);
-  else k_extend<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, P, W, bounce);
+  k_extend<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, P, W, bounce);
 }
 void launch_shade(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st) {
-  k_shade<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, P, W, bounce);
+  static int grid = 0;
+  if (!grid) grid = resident_grid(k_shade, 128);
+  k_shade<<<grid, 128, 0, st>>>(S, P, W, bounce);
 }
-void launch_shadow(const DevScene &S, const WaveState &W, cudaStream_t st) {
-  if (variant() == 1) k_shadow_v1<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, W);
-  else k_shadow<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, W);
+void launch_shadow(const DevScene &S, const WaveState &W, uint32_t bounce, cudaStream_t st) {
+  k_shadow<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, W, bounce);
 }
 void launch_resolve(const WaveParams &P, const WaveState &W, float *accum, cudaStream_t st) {
   uint32_t npix = P.width * P.height;

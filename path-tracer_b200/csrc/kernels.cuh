@@ -12,7 +12,7 @@ void launch_triangle_intersect(const float *rays, const float *tris, uint32_t n,
 void launch_raygen(const DevScene &S, const WaveParams &P, const WaveState &W, cudaStream_t st);
 void launch_extend(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st);
 void launch_shade(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st);
-void launch_shadow(const DevScene &S, const WaveState &W, cudaStream_t st);
+void launch_shadow(const DevScene &S, const WaveState &W, uint32_t bounce, cudaStream_t st);
 void launch_resolve(const WaveParams &P, const WaveState &W, float *accum, cudaStream_t st);
 void launch_tonemap(const float *accum, uint32_t npix, uint32_t total_samples, int tonemap, uint8_t *rgb8, cudaStream_t st);
 }  // namespace ptb

@@ -221,7 +221,6 @@ int ensure_wave(pt_scene *sc, uint32_t n_paths) {
     if ((rc = wave_alloc(sc, &W.thr[b], n_paths))) return rc;
   }
   if ((rc = wave_alloc(sc, &W.hit, n_paths))) return rc;
-  if ((rc = wave_alloc(sc, &W.hit_idx, n_paths))) return rc;
   if ((rc = wave_alloc(sc, &W.radiance, n_paths))) return rc;
   if ((rc = wave_alloc(sc, &W.sh_o, shadow_cap))) return rc;
   if ((rc = wave_alloc(sc, &W.sh_d, shadow_cap))) return rc;
@@ -535,7 +534,7 @@ int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t
   {
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
-      uint64_t per_path = 228 + 64ull * std::max(1u, sc->dev.n_lights);
+      uint64_t per_path = 224 + 64ull * std::max(1u, sc->dev.n_lights);
       uint64_t have = (uint64_t)sc->wave.capacity * per_path;  // already allocated wave buffers count as free
       target_paths = std::min<uint64_t>(target_paths, std::max<uint64_t>(npix, (free_b + have) / 2 / per_path));
     }
@@ -592,7 +591,7 @@ int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t
       ++n_ext;
       ++n_shade;
       if (sc->dev.n_lights) {
-        launch_shadow(sc->dev, W, st);
+        launch_shadow(sc->dev, W, b, st);
         mark(2);
         ++launches;
         ++n_shadow;
