@@ -281,7 +281,8 @@ def run_ours(args, wl):
         traffic = None
         try:
             with open(TRAFFIC_FILE) as f:
-                traffic = json.load(f).get(args.workload, {}).get("k_extend_dram_bytes_per_launch")
+                per_ray = json.load(f).get(args.workload, {}).get("k_extend_dram_bytes_per_ray")
+                traffic = per_ray * st["extend_rays"] / max(1, st["extend_launches"]) if per_ray else None
         except Exception:
             pass
         roof = {"bound": "hbm", "kernel": "k_extend", "achieved": achieved, "peak": peak, "unit": "GB/s",
