@@ -211,6 +211,29 @@ int pt_tonemap_device(const float *accum_dev, uint32_t width, uint32_t height, u
 int pt_render(const pt_scene *scene, const pt_profile *profile, uint64_t seed, uint8_t *rgb8_out,
               float *accum_out, pt_stats *stats_out);
 
+/* ---- debug_render (renderer/debug_renderer.rs:11-105): `render --debug-textures` ---- */
+/* One pixel-centre ray per pixel, first element of ray_cast, material sampled at the hit.  planes_out holds
+ * PT_AOV_COUNT consecutive row-major RGB8 images of width*height pixels (host memory), each channel
+ * `(value * 255.) as u8`; pixels whose ray hits nothing are 0.  *pixels_hit = rays that hit (the reference
+ * writes no PNG at all when it is 0).  ior is stored as ior/3 (debug_renderer.rs:102). */
+enum { PT_AOV_NORMAL = 0, PT_AOV_ALBEDO, PT_AOV_OPACITY, PT_AOV_METALNESS, PT_AOV_ROUGHNESS, PT_AOV_EMISSIVE,
+       PT_AOV_IOR, PT_AOV_COUNT };
+const char *pt_aov_name(int aov); /* "normal", "albedo", ...: the PNG base names of debug_renderer.rs:59 */
+int pt_debug_textures(const pt_scene *scene, uint32_t width, uint32_t height, uint8_t *planes_out,
+                      uint64_t *pixels_hit);
+
+/* ---- progressive output: the viewer feed of Renderer::render (renderer/mod.rs:133-141, viewer.rs) ---- */
+/* The SFML window itself is unavailable (no graphics stack); its content is delivered headless instead: after
+ * every `snapshot_every` samples per pixel the running mean (`*pixel / current_sample`, mod.rs:137) is
+ * post-processed and handed to on_snapshot(user, rgb8, width, height, samples_done) (rgb8 = rgb8_out, valid during
+ * the call).  A non-zero return stops further snapshots (the window was closed, mod.rs:139-141); rendering
+ * continues.  The final image is identical to pt_render's.  snapshot_every = 0 or on_snapshot = NULL: no snapshots. */
+typedef int (*pt_snapshot_fn)(void *user, const uint8_t *rgb8, uint32_t width, uint32_t height,
+                              uint32_t samples_done);
+int pt_render_progressive(const pt_scene *scene, const pt_profile *profile, uint64_t seed, uint32_t snapshot_every,
+                          pt_snapshot_fn on_snapshot, void *user, uint8_t *rgb8_out, float *accum_out,
+                          pt_stats *stats_out);
+
 /* ---- image output: RgbImage::save (main.rs:50) ---- */
 int pt_write_png(const char *path, const uint8_t *rgb8, uint32_t width, uint32_t height);
 /* 8-bit PNG decode used by the texture bank (texture_bank.rs:33,49); channels_out in {1,3}.

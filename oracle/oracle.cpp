@@ -382,6 +382,54 @@ int oracle_tonemap(const float *accum, uint32_t width, uint32_t height, uint32_t
   return 0;
 }
 
+// debug_render + render_debug_pixels, renderer/debug_renderer.rs:11-105: one pixel-centre ray per pixel, the first
+// element of ray_cast, seven AOV planes in the order normal, albedo, opacity, metalness, roughness, emissive, ior.
+// planes: 7 * W*H*3 bytes, row-major (the reference's x*H+y buffer index is used for both the write and the read,
+// debug_renderer.rs:38,52, so image[(x,y)] is simply pixel (x,y)); pixels without a hit stay 0.  Returns the number of
+// pixels that hit something (the reference writes no file at all when it is 0).
+int oracle_debug_textures(const void *sp, uint32_t W, uint32_t H, uint8_t *planes) {
+  const Scene &s = *(const Scene *)sp;
+  const size_t plane = (size_t)W * H * 3;
+  std::memset(planes, 0, plane * 7);
+  std::vector<Hit> hits;
+  const float wf = (float)W, hf = (float)H, ratio = wf / hf;
+  int n_hit = 0;
+  auto put = [&](int k, size_t px, V3 c) {  // `(pixel.x * 255.) as u8` (debug_renderer.rs:53-57)
+    uint8_t *o = planes + plane * k + px * 3;
+    const float v[3] = {c.x * 255.0f, c.y * 255.0f, c.z * 255.0f};
+    for (int i = 0; i < 3; ++i) o[i] = !(v[i] == v[i]) || v[i] <= 0.0f ? 0 : v[i] >= 255.0f ? 255 : (uint8_t)v[i];
+  };
+  for (uint32_t y = 0; y < H; ++y)
+    for (uint32_t x = 0; x < W; ++x) {
+      float sx = (float)x + 0.5f;
+      sx = sx / wf * 2.0f - 1.0f;
+      sx *= std::tan(s.fov / 2.0f) * ratio;
+      float sy = (float)y + 0.5f;
+      sy = 1.0f - sy / hf * 2.0f;
+      sy *= std::tan(s.fov / 2.0f);
+      V3 dir = normalize(v3(sx, sy, -1.0f));
+      const float *m = s.camera;
+      V3 c0 = v3(m[0], m[1], m[2]), c1 = v3(m[4], m[5], m[6]), c2 = v3(m[8], m[9], m[10]), c3 = v3(m[12], m[13], m[14]);
+      V3 d = ((c0 * dir.x + c1 * dir.y) + c2 * dir.z) + c3 * 0.0f;
+      ray_cast(s, c3, d, hits, false);
+      if (hits.empty()) continue;
+      ++n_hit;
+      const Hit &h = hits[0];
+      MaterialSample mat = hit_material_sample(s, h, h.model);
+      V3 n = hit_shading_normal(s, h, h.model);
+      const size_t px = (size_t)y * W + x;
+      const V3 one = v3(1.0f, 1.0f, 1.0f);
+      put(0, px, n * 0.5f + v3(0.5f, 0.5f, 0.5f));
+      put(1, px, mat.albedo);
+      put(2, px, one * mat.opacity);
+      put(3, px, one * mat.metalness);
+      put(4, px, one * mat.roughness);
+      put(5, px, mat.emissive);
+      put(6, px, one * mat.ior / 3.0f);
+    }
+  return n_hit;
+}
+
 // Dumps the bounce-`bounce` rays (origin, direction) of a 1-spp Philox trace: the secondary-ray
 // batches of SURVEY.md §8(c).  rays_out: W*H*6 floats; valid_out: W*H bytes.
 int oracle_dump_bounce_rays(const void *sp, const pt_profile *prof, uint64_t seed, uint32_t bounce_wanted,

@@ -21,8 +21,12 @@ _LIB = None
 EXPORTS = ["pt_last_error", "pt_device_count", "pt_profile_default", "pt_profile_load_yaml", "pt_scene_load_isf",
            "pt_scene_create", "pt_scene_synthetic", "pt_scene_destroy", "pt_scene_upload", "pt_set_kernel_timing", "pt_scene_get_desc", "pt_scene_info",
            "pt_trace_closest", "pt_trace_closest_device", "pt_trace_transmittance", "pt_triangle_intersect",
-           "pt_trace_paths", "pt_render_accum_device",
+           "pt_trace_paths", "pt_render_accum_device", "pt_aov_name", "pt_debug_textures", "pt_render_progressive",
            "pt_tonemap_device", "pt_render", "pt_write_png", "pt_read_png", "pt_free"]
+
+
+SNAPSHOT_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_uint8), C.c_uint32, C.c_uint32, C.c_uint32)
+AOV_NAMES = ("normal", "albedo", "opacity", "metalness", "roughness", "emissive", "ior")  # debug_renderer.rs:80-102
 
 
 class PtError(RuntimeError):
@@ -65,6 +69,10 @@ def lib():
         L.pt_render.argtypes = [vp, C.POINTER(pt_profile), u64, vp, vp, C.POINTER(pt_stats)]
         L.pt_write_png.argtypes = [C.c_char_p, vp, u32, u32]
         L.pt_read_png.argtypes = [C.c_char_p, u32, C.POINTER(u32), C.POINTER(u32), C.POINTER(C.POINTER(C.c_uint8))]
+        L.pt_aov_name.argtypes = [C.c_int]
+        L.pt_aov_name.restype = C.c_char_p
+        L.pt_debug_textures.argtypes = [vp, u32, u32, vp, C.POINTER(u64)]
+        L.pt_render_progressive.argtypes = [vp, C.POINTER(pt_profile), u64, u32, SNAPSHOT_FN, vp, vp, vp, C.POINTER(pt_stats)]
         L.pt_free.argtypes = [vp]
         L.pt_free.restype = None
         _LIB = L
@@ -243,16 +251,37 @@ class Renderer:
         self.last_stats = None
         self.last_accum = None
 
-    def render(self, scene, keep_accum=False):
+    def render(self, scene, keep_accum=False, snapshot_every=0, on_snapshot=None):
+        """on_snapshot(rgb[h, w, 3] copy, samples_done) -> truthy to stop watching: the headless form of the viewer
+        feed (renderer/mod.rs:133-141), called after every `snapshot_every` samples per pixel."""
         p = self.profile.c
         rgb = np.zeros((p.height, p.width, 3), np.uint8)
         accum = np.zeros((p.height, p.width, 3), np.float32) if keep_accum else None
         st = pt_stats()
-        _check(lib().pt_render(scene.h, C.byref(p), self.config.seed, rgb.ctypes.data,
-                               accum.ctypes.data if keep_accum else None, C.byref(st)))
+        if on_snapshot is not None and snapshot_every > 0:
+            def _cb(user, img, w, h, done):
+                arr = np.ctypeslib.as_array(img, shape=(h, w, 3)).copy()
+                return 1 if on_snapshot(arr, done) else 0
+            cb = SNAPSHOT_FN(_cb)
+            _check(lib().pt_render_progressive(scene.h, C.byref(p), self.config.seed, snapshot_every, cb, None,
+                                               rgb.ctypes.data, accum.ctypes.data if keep_accum else None, C.byref(st)))
+        else:
+            _check(lib().pt_render(scene.h, C.byref(p), self.config.seed, rgb.ctypes.data,
+                                   accum.ctypes.data if keep_accum else None, C.byref(st)))
         self.last_stats = st.as_dict()
         self.last_accum = accum
         return rgb
+
+
+def debug_render(scene, width, height):
+    """debug_render (src/renderer/debug_renderer.rs:11-62): dict AOV name -> rgb8[h, w, 3], plus the hit-pixel count
+    under the key "pixels_hit" (the reference writes `<name>.png` for each plane, and nothing when no ray hits)."""
+    planes = np.zeros((len(AOV_NAMES), height, width, 3), np.uint8)
+    n = C.c_uint64()
+    _check(lib().pt_debug_textures(scene.h, width, height, planes.ctypes.data, C.byref(n)))
+    out = {lib().pt_aov_name(i).decode(): planes[i] for i in range(len(AOV_NAMES))}
+    out["pixels_hit"] = n.value
+    return out
 
 
 def render_accum_device(scene, profile, accum_ptr, sample_begin=0, sample_stride=1, n_samples=None, seed=0, stream=None,

@@ -1,8 +1,11 @@
 // cli.cpp — `path-tracer` command line.  Mirrors the reference's clap surface (src/config/mod.rs:14-52) and
 // run_render (src/main.rs:32-52): `path-tracer render <input> [-o FILE|$OUTPUT] [-q] [-v] [--debug-textures]
 // [-p FILE|$PROFILE]`, errors printed to stderr with exit code 2 (main.rs:14-21).  Additive flags: --seed,
-// --stats.  The SFML viewer (renderer/viewer.rs) needs a window + GL: unavailable on this box, -v is accepted
-// and ignored with a note.  `convert` (glTF -> isf, scene/gltf.rs) is outside the accelerated path.
+// --stats, --snapshot-every.  The SFML viewer (renderer/viewer.rs) needs a window + GL: unavailable on this box; -v
+// delivers the same feed headless instead: the running mean image is written over <OUTPUT> after every
+// --snapshot-every samples per pixel (default 16).  --debug-textures writes the seven AOV PNGs of
+// renderer/debug_renderer.rs into the working directory.  `convert` (glTF -> isf, scene/gltf.rs) is outside the
+// accelerated path.
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -17,7 +20,7 @@ static int usage(const char *msg) {
   std::fprintf(stderr,
                "Path-trace awesome things\n\nUsage: path-tracer <COMMAND>\n\nCommands:\n"
                "  render   <INPUT> [-o, --output <OUTPUT>] [-q, --quiet] [-v, --viewer] [--debug-textures]\n"
-               "           [-p, --profile <PROFILE>] [--seed <N>] [--stats <FILE>]\n"
+               "           [-p, --profile <PROFILE>] [--seed <N>] [--stats <FILE>] [--snapshot-every <SPP>]\n"
                "  convert  <INPUT> <OUTPUT>   (not part of the B200 build)\n");
   return 2;
 }
@@ -40,6 +43,7 @@ int main(int argc, char **argv) {
   std::string input, output = env_out ? env_out : "render.png", profile_path = env_prof ? env_prof : "", stats_path;
   bool quiet = false, viewer = false, debug_textures = false;
   unsigned long long seed = 0;
+  unsigned snapshot_every = 16;
   for (int i = 2; i < argc; ++i) {
     std::string a = argv[i];
     auto need = [&](const char *name) -> const char * {
@@ -58,6 +62,7 @@ int main(int argc, char **argv) {
     else if (a == "--debug-textures") debug_textures = true;
     else if (a == "--seed") seed = std::strtoull(need("--seed"), nullptr, 0);
     else if (a == "--stats") stats_path = need("--stats");
+    else if (a == "--snapshot-every") snapshot_every = (unsigned)std::strtoul(need("--snapshot-every"), nullptr, 0);
     else if (a == "-h" || a == "--help") {
       usage(nullptr);
       return 0;
@@ -73,11 +78,9 @@ int main(int argc, char **argv) {
     std::fprintf(stderr, "%s\n", pt_last_error());
     return 2;
   }
-  if (debug_textures) {
-    std::fprintf(stderr, "--debug-textures: AOV pass not available in this build\n");
-    return 2;
-  }
-  if (viewer && !quiet) std::fprintf(stderr, "note: --viewer needs a window system (unavailable on this box); rendering headless\n");
+  if (viewer && !quiet && !debug_textures)
+    std::fprintf(stderr, "note: --viewer needs a window system (unavailable on this box); writing the running image to %s every %u spp\n",
+                 output.c_str(), snapshot_every);
 
   auto t0 = std::chrono::steady_clock::now();
   pt_scene *scene = nullptr;
@@ -86,10 +89,42 @@ int main(int argc, char **argv) {
     return 2;
   }
   auto t1 = std::chrono::steady_clock::now();
+  if (debug_textures) {  // main.rs:41-44 + debug_renderer.rs:11-62: seven "<buffer_name>.png" in the working directory
+    const size_t plane = (size_t)prof.width * prof.height * 3;
+    std::vector<uint8_t> planes(plane * PT_AOV_COUNT);
+    uint64_t n_hit = 0;
+    int rc = pt_debug_textures(scene, prof.width, prof.height, planes.data(), &n_hit);
+    pt_scene_destroy(scene);
+    if (rc != PT_OK) {
+      std::fprintf(stderr, "%s\n", pt_last_error());
+      return 2;
+    }
+    // the reference creates a buffer on the first pixel that hits something: no hit at all, no file
+    for (int k = 0; n_hit && k < PT_AOV_COUNT; ++k) {
+      std::string name = std::string(pt_aov_name(k)) + ".png";
+      if (pt_write_png(name.c_str(), planes.data() + plane * k, prof.width, prof.height) != PT_OK) {
+        std::fprintf(stderr, "%s\n", pt_last_error());
+        return 2;
+      }
+    }
+    return 0;
+  }
   if (!quiet) std::fprintf(stderr, "Rendering: %ux%u, %u samples, %u bounces\n", prof.width, prof.height, prof.samples, prof.bounces);
   std::vector<uint8_t> rgb((size_t)prof.width * prof.height * 3);
   pt_stats st{};
-  if (pt_render(scene, &prof, seed, rgb.data(), nullptr, &st) != PT_OK) {
+  struct Snap {
+    const char *path;
+    bool quiet;
+  } snap{output.c_str(), quiet};
+  auto on_snapshot = [](void *user, const uint8_t *img, uint32_t w, uint32_t h, uint32_t done) -> int {
+    const Snap *s = static_cast<const Snap *>(user);
+    if (pt_write_png(s->path, img, w, h) != PT_OK) return 1;  // like a closed viewer: stop sending, keep rendering
+    if (!s->quiet) std::fprintf(stderr, "  %u spp -> %s\n", done, s->path);
+    return 0;
+  };
+  int rrc = viewer ? pt_render_progressive(scene, &prof, seed, snapshot_every, on_snapshot, &snap, rgb.data(), nullptr, &st)
+                   : pt_render(scene, &prof, seed, rgb.data(), nullptr, &st);
+  if (rrc != PT_OK) {
     std::fprintf(stderr, "%s\n", pt_last_error());
     pt_scene_destroy(scene);
     return 2;

@@ -363,6 +363,57 @@ __global__ void __launch_bounds__(256) k_triangle_intersect(const float *__restr
   out[i] = h;
 }
 
+// debug_render / render_debug_pixels (renderer/debug_renderer.rs:11-105): one pixel-centre ray per pixel, the first
+// element of ray_cast (no alpha walk), seven AOV planes: normal, albedo, opacity, metalness, roughness, emissive, ior.
+// planes: 7 * W*H*3 bytes (caller-zeroed: pixels without a hit stay 0); n_hit counts the pixels that hit something.
+__global__ void __launch_bounds__(128) k_debug_aov(const __grid_constant__ DevScene S, uint32_t width, uint32_t height,
+                                                   uint8_t *__restrict__ planes, uint32_t *n_hit) {
+  const uint32_t npix = width * height;
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  bool got = false;
+  if (p < npix) {
+    const uint32_t x = p % width, y = p / width;
+    const float wf = (float)width, hf = (float)height, ratio = wf / hf, tn = S.tan_half_fov;
+    float sx = (float)x + 0.5f;  // debug_renderer.rs:24-30
+    sx = sx / wf * 2.0f - 1.0f;
+    sx *= tn * ratio;
+    float sy = (float)y + 0.5f;
+    sy = 1.0f - sy / hf * 2.0f;
+    sy *= tn;
+    V3 dir = normalize3(mk3(sx, sy, -1.0f));
+    const float *m = S.camera;
+    V3 c0 = mk3(m[0], m[1], m[2]), c1 = mk3(m[4], m[5], m[6]), c2 = mk3(m[8], m[9], m[10]), c3 = mk3(m[12], m[13], m[14]);
+    Ray r;
+    r.d = ((c0 * dir.x + c1 * dir.y) + c2 * dir.z) + c3 * 0.0f;
+    r.o = c3;
+    TraceState st;
+    trace_closest(S, r, -1.0f, -1, st);
+    if (st.idx >= 0) {
+      got = true;
+      const Surface sf = make_surface(S, r, st.best_t, st.u, st.v, st.idx);
+      const MatSample ms = material_sample(S, sf.model, sf.is_sphere, sf.tu, sf.tv);
+      const float ior = S.materials[sf.model].ior;
+      const size_t plane = (size_t)npix * 3;
+      auto put = [&](int k, V3 c) {  // `(pixel.x * 255.) as u8`, debug_renderer.rs:53-57
+        uint8_t *o = planes + plane * k + (size_t)p * 3;
+        o[0] = to_u8(c.x * 255.0f);
+        o[1] = to_u8(c.y * 255.0f);
+        o[2] = to_u8(c.z * 255.0f);
+      };
+      const V3 one = mk3(1.0f, 1.0f, 1.0f);
+      put(0, sf.shading_n * 0.5f + mk3(0.5f, 0.5f, 0.5f));
+      put(1, ms.albedo);
+      put(2, one * ms.opacity);
+      put(3, one * ms.metalness);
+      put(4, one * ms.roughness);
+      put(5, ms.emissive);
+      put(6, one * ior / 3.0f);
+    }
+  }
+  const uint32_t m = __ballot_sync(0xffffffffu, got);
+  if (lane_id() == 0 && m) atomicAdd(n_hit, (uint32_t)__popc(m));
+}
+
 // shadow: transmittance of every queued shadow ray; adds contribution * transmittance to the path's radiance.
 // Same lane-level ray replacement and node / primitive phases as k_extend.
 __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_constant__ DevScene S, WaveState W, uint32_t bounce) {
@@ -475,6 +526,9 @@ void launch_trace_paths(const DevScene &S, const WaveParams &P, const uint32_t *
 }
 void launch_triangle_intersect(const float *rays, const float *tris, uint32_t n, pt_hit *out, cudaStream_t st) {
   k_triangle_intersect<<<(n + 255) / 256, 256, 0, st>>>(rays, tris, n, out);
+}
+void launch_debug_aov(const DevScene &S, uint32_t width, uint32_t height, uint8_t *planes, uint32_t *n_hit, cudaStream_t st) {
+  k_debug_aov<<<(width * height + 127) / 128, 128, 0, st>>>(S, width, height, planes, n_hit);
 }
 void launch_raygen(const DevScene &S, const WaveParams &P, const WaveState &W, cudaStream_t st) {
   k_raygen<<<(P.n_paths + 255) / 256, 256, 0, st>>>(S, P, W);

@@ -683,4 +683,102 @@ int pt_render(const pt_scene *sc, const pt_profile *prof, uint64_t seed, uint8_t
   return PT_OK;
 }
 
+const char *pt_aov_name(int aov) {
+  static const char *names[PT_AOV_COUNT] = {"normal", "albedo", "opacity", "metalness", "roughness", "emissive", "ior"};
+  return aov >= 0 && aov < PT_AOV_COUNT ? names[aov] : nullptr;
+}
+
+int pt_debug_textures(const pt_scene *sc, uint32_t width, uint32_t height, uint8_t *planes_out, uint64_t *pixels_hit) {
+  if (!sc || !planes_out || width == 0 || height == 0 || (uint64_t)width * height > (1ull << 28)) {
+    set_error("bad argument");
+    return PT_ERR_INVALID;
+  }
+  if (sc->device < 0) return no_device();
+  DeviceGuard g(sc->device);
+  const size_t bytes = (size_t)width * height * 3 * PT_AOV_COUNT;
+  uint8_t *d_planes = nullptr;
+  uint32_t *d_hit = nullptr;
+  CUDA_TRY(cudaMalloc(&d_planes, bytes));
+  cudaError_t e = cudaMalloc(&d_hit, sizeof(uint32_t));
+  if (e == cudaSuccess) e = cudaMemset(d_planes, 0, bytes);
+  if (e == cudaSuccess) e = cudaMemset(d_hit, 0, sizeof(uint32_t));
+  if (e == cudaSuccess) {
+    launch_debug_aov(sc->dev, width, height, d_planes, d_hit, nullptr);
+    e = cudaGetLastError();
+  }
+  uint32_t n_hit = 0;
+  if (e == cudaSuccess) e = cudaMemcpy(planes_out, d_planes, bytes, cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess) e = cudaMemcpy(&n_hit, d_hit, sizeof n_hit, cudaMemcpyDeviceToHost);
+  cudaFree(d_planes);
+  cudaFree(d_hit);
+  CUDA_TRY(e);
+  if (pixels_hit) *pixels_hit = n_hit;
+  return PT_OK;
+}
+
+int pt_render_progressive(const pt_scene *sc, const pt_profile *prof, uint64_t seed, uint32_t snapshot_every,
+                          pt_snapshot_fn on_snapshot, void *user, uint8_t *rgb8_out, float *accum_out,
+                          pt_stats *stats_out) {
+  if (!sc || !rgb8_out) {
+    set_error("null argument");
+    return PT_ERR_INVALID;
+  }
+  int rc = check_profile(prof);
+  if (rc) return rc;
+  if (sc->device < 0) return no_device();
+  if (snapshot_every == 0 || !on_snapshot) snapshot_every = prof->samples ? prof->samples : 1;
+  DeviceGuard g(sc->device);
+  const size_t npix = (size_t)prof->width * prof->height;
+  float *d_accum = nullptr;
+  uint8_t *d_rgb = nullptr;
+  CUDA_TRY(cudaMalloc(&d_accum, npix * 3 * sizeof(float)));
+  if (cudaMalloc(&d_rgb, npix * 3) != cudaSuccess) {
+    cudaFree(d_accum);
+    set_error("out of device memory");
+    return PT_ERR_NOMEM;
+  }
+  cudaMemset(d_accum, 0, npix * 3 * sizeof(float));
+  pt_stats total{}, part{};
+  bool watching = on_snapshot != nullptr;
+  cudaError_t e = cudaSuccess;
+  uint32_t done = 0;
+  do {  // at least one pass so that samples == 0 still yields the (NaN -> 0) image the reference would produce
+    const uint32_t chunk = std::min(snapshot_every, prof->samples - done);
+    rc = pt_render_accum_device(sc, prof, done, 1, chunk, seed, d_accum, nullptr, &part);
+    if (rc != PT_OK) break;
+    done += chunk;
+    total.samples += part.samples;
+    total.extend_rays += part.extend_rays;
+    total.shadow_rays += part.shadow_rays;
+    total.alpha_recasts += part.alpha_recasts;
+    total.kernel_launches += part.kernel_launches + 1;
+    total.extend_launches += part.extend_launches;
+    total.shade_launches += part.shade_launches;
+    total.shadow_launches += part.shadow_launches;
+    total.ms_total += part.ms_total;
+    total.ms_extend += part.ms_extend;
+    total.ms_shade += part.ms_shade;
+    total.ms_shadow += part.ms_shadow;
+    total.ms_other += part.ms_other;
+    const bool last = done >= prof->samples;
+    if (!last && !watching) continue;
+    // `*pixel / current_sample` then post_processing: what the viewer shows (mod.rs:137-138), and the final pass
+    rc = pt_tonemap_device(d_accum, prof->width, prof->height, last ? prof->samples : done, prof->tonemap, d_rgb,
+                           sc->device, nullptr);
+    if (rc != PT_OK) break;
+    e = cudaMemcpy(rgb8_out, d_rgb, npix * 3, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) break;
+    // a non-zero return is the viewer window being closed (mod.rs:139-141): rendering goes on without snapshots
+    if (watching && on_snapshot(user, rgb8_out, prof->width, prof->height, done) != 0) watching = false;
+  } while (done < prof->samples);
+  if (rc == PT_OK && e == cudaSuccess && accum_out)
+    e = cudaMemcpy(accum_out, d_accum, npix * 3 * sizeof(float), cudaMemcpyDeviceToHost);
+  cudaFree(d_accum);
+  cudaFree(d_rgb);
+  if (rc != PT_OK) return rc;
+  CUDA_TRY(e);
+  if (stats_out) *stats_out = total;
+  return PT_OK;
+}
+
 }  // extern "C"

@@ -34,6 +34,7 @@ def lib():
         L.oracle_trace_paths.argtypes = [C.c_void_p, C.POINTER(pt_profile), C.c_void_p, C.c_size_t, C.c_uint32,
                                          C.c_uint64, C.c_int, C.c_void_p, C.c_void_p]
         L.oracle_canonical_counts.argtypes = [C.c_void_p, C.POINTER(pt_profile), C.c_uint32, C.c_uint64, C.c_int, C.c_void_p]
+        L.oracle_debug_textures.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
         _LIB = L
     return _LIB
 
@@ -97,6 +98,12 @@ class OracleScene:
         rc, nc, pc, ra, na, pa = [int(x) for x in out]
         return dict(rays_closest=rc, n_node_closest=nc / max(rc, 1), n_tri_closest=pc / max(rc, 1),
                     rays_any=ra, n_node_any=na / max(ra, 1), n_tri_any=pa / max(ra, 1))
+
+    def debug_textures(self, width, height):
+        """debug_renderer.rs:11-105: (planes[7, h, w, 3] uint8 in AOV order, pixels that hit)."""
+        planes = np.zeros((7, height, width, 3), np.uint8)
+        n = lib().oracle_debug_textures(self.h, width, height, planes.ctypes.data)
+        return planes, n
 
     def dump_bounce_rays(self, profile, bounce, seed=0):
         n = profile.width * profile.height

@@ -166,3 +166,9 @@ def test_no_cpu_fallback_without_device():
         pt.Renderer(profile=pt.Profile(width=8, height=8, samples=1)).render(host)
     with pytest.raises(pt.PtError):
         pt.triangle_intersect(np.zeros((1, 6), np.float32), np.zeros((1, 9), np.float32))
+    with pytest.raises(pt.PtError) as e:
+        pt.debug_render(host, 8, 8)
+    assert e.value.code == -4
+    with pytest.raises(pt.PtError) as e:
+        pt.Renderer(profile=pt.Profile(width=8, height=8, samples=2)).render(host, snapshot_every=1, on_snapshot=lambda a, d: False)
+    assert e.value.code == -4

@@ -407,3 +407,88 @@ def test_textured_materials_vs_oracle():
     close = np.abs(rend.last_accum - oacc) <= 1e-3 * np.maximum(np.abs(oacc), 1.0)
     assert close.mean() > 0.97, close.mean()
     assert rend.last_stats["alpha_recasts"] > 0
+
+
+# ---------------------------------------------------------------- debug_render (debug_renderer.rs:11-105)
+@pytest.mark.parametrize("name", ["head", "alpha_transparency", "spheres", "cube"])
+def test_debug_textures_vs_oracle(loaded, name):
+    sa, osc, gsc = loaded[name]
+    w, h = 200, 150
+    got = pt.debug_render(gsc, w, h)
+    want, n_hit = osc.debug_textures(w, h)
+    assert got["pixels_hit"] == n_hit > 0
+    for k, aov in enumerate(pt.AOV_NAMES):
+        d = np.abs(got[aov].astype(np.int16) - want[k].astype(np.int16))
+        if aov == "albedo":  # powf(texel, 2.2): CUDA vs glibc last-ulp differences may flip a u8 truncation
+            assert d.max() <= 1 and (d == 0).mean() > 0.995, (aov, d.max(), (d == 0).mean())
+        elif aov == "normal":  # normalised TBN / sphere normals: last-ulp differences at u8 truncation boundaries
+            assert d.max() <= 1 and (d == 0).mean() > 0.999, (aov, d.max(), (d == 0).mean())
+        else:
+            assert d.max() == 0, aov
+    # pixels without a hit stay 0 in every plane; ior plane = ior / 3 on hit pixels
+    miss = (want[0] == 0).all(-1) & (want[6] == 0).all(-1)
+    for aov in pt.AOV_NAMES:
+        assert (got[aov][miss] == 0).all()
+
+
+def test_debug_textures_textured_scene_and_errors():
+    sa = textured_scene()
+    gsc, osc = pt.Scene.from_arrays(sa), oracle_lib.OracleScene(sa)
+    got = pt.debug_render(gsc, 160, 120)
+    want, n_hit = osc.debug_textures(160, 120)
+    assert got["pixels_hit"] == n_hit
+    for k, aov in enumerate(pt.AOV_NAMES):
+        d = np.abs(got[aov].astype(np.int16) - want[k].astype(np.int16))
+        assert d.max() <= 1 and (d == 0).mean() > 0.99, (aov, d.max(), (d == 0).mean())
+    assert len(np.unique(got["metalness"])) > 2 and len(np.unique(got["roughness"])) > 2  # the maps are really sampled
+    with pytest.raises(pt.PtError):
+        pt.debug_render(gsc, 0, 10)
+
+
+def test_cli_debug_textures(tmp_path, loaded):
+    import subprocess
+    exe = os.path.join(os.path.dirname(pt.__file__), "path-tracer")
+    prof = tmp_path / "p.yml"
+    prof.write_text("resolution:\n  width: 96\n  height: 64\n")
+    r = subprocess.run([exe, "render", scene_path("head"), "--debug-textures", "-p", str(prof)], cwd=tmp_path, capture_output=True)
+    assert r.returncode == 0, r.stderr
+    got = pt.debug_render(loaded["head"][2], 96, 64)
+    for aov in pt.AOV_NAMES:  # debug_renderer.rs:59: "<buffer_name>.png" in the working directory
+        assert np.array_equal(pt.read_png(str(tmp_path / (aov + ".png")), 3), got[aov]), aov
+    assert not (tmp_path / "render.png").exists()  # main.rs:41-44 returns before rendering
+
+
+# ---------------------------------------------------------------- viewer feed (mod.rs:133-141) as headless snapshots
+def test_progressive_snapshots(loaded):
+    sa, osc, gsc = loaded["cube"]
+    prof = pt.Profile(width=96, height=64, samples=10, bounces=3)
+    rend = pt.Renderer(profile=prof)
+    full = rend.render(gsc, keep_accum=True)
+    full_acc = rend.last_accum.copy()
+    snaps = []
+    img = rend.render(gsc, keep_accum=True, snapshot_every=4, on_snapshot=lambda a, done: snaps.append((done, a)) and False)
+    assert [d for d, _ in snaps] == [4, 8, 10]
+    assert np.array_equal(img, full) and np.array_equal(snaps[-1][1], full)
+    assert np.allclose(rend.last_accum, full_acc, rtol=1e-5, atol=1e-6)  # same samples, summed in three chunks
+    assert rend.last_stats["samples"] == 96 * 64 * 10
+    # snapshot k shows `*pixel / current_sample` post-processed (mod.rs:137-138) == a render of the first k samples
+    first4 = pt.Renderer(profile=pt.Profile(width=96, height=64, samples=4, bounces=3)).render(gsc)
+    assert np.array_equal(snaps[0][1], first4)
+    # a truthy return closes the feed (mod.rs:139-141): no more snapshots, the render still completes
+    seen = []
+    img2 = rend.render(gsc, snapshot_every=2, on_snapshot=lambda a, done: seen.append(done) or True)
+    assert seen == [2] and np.array_equal(img2, full)
+
+
+def test_cli_viewer_snapshots(tmp_path):
+    import subprocess
+    exe = os.path.join(os.path.dirname(pt.__file__), "path-tracer")
+    prof = tmp_path / "p.yml"
+    prof.write_text("resolution:\n  width: 64\n  height: 48\nsamples: 6\nbounces: 2\n")
+    a, b = tmp_path / "a.png", tmp_path / "b.png"
+    r = subprocess.run([exe, "render", scene_path("cube"), "-v", "--snapshot-every", "2", "-o", str(a), "-p", str(prof)], capture_output=True)
+    assert r.returncode == 0, r.stderr
+    assert r.stderr.count(b"spp ->") == 3
+    r = subprocess.run([exe, "render", scene_path("cube"), "-q", "-o", str(b), "-p", str(prof)], capture_output=True)
+    assert r.returncode == 0
+    assert np.array_equal(pt.read_png(str(a)), pt.read_png(str(b)))
