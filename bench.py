@@ -306,7 +306,7 @@ def run_ours(args, wl):
                    "brdf": "COOK_TORRANCE", "split": "sample index mod n_gpus, one NCCL reduce of W*H*3 f32 per step",
                    "l2": "inputs larger than L2: scene %.0f MB + %.0f MB of wave state per wave vs 126 MB L2; no flush"
                          % (info["device_bytes"] / 1e6, 8.4e6 * 228 / 1e6),
-                   "scene_build_s": build_s},
+                   "scene_build_s": build_s, "accel": scene.accel_info()},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d),
                 "d2h_bytes_per_step": int(w * h * 3), "ms_per_step": ms_e2e / args.steps},

@@ -155,6 +155,16 @@ int pt_scene_create(const pt_scene_desc *desc, int device, pt_scene **out);
  * n_tris is a target triangle count. */
 int pt_scene_synthetic(const char *recipe, uint64_t n_tris, uint64_t seed, int device, pt_scene **out);
 void pt_scene_destroy(pt_scene *scene);
+/* Acceleration-structure builder used by the scene constructors above (process-wide; default PT_ACCEL_SAH, or the
+ * value of $PT_B200_ACCEL = sah|lbvh|auto).  Replaces KDTree::build of the kdtree-ray crate (call sites
+ * scene/internal/model.rs:96, scene/internal/mod.rs:42).  Either tree is a conservative candidate filter: traced
+ * results are identical.  SAH: binned-SAH build on the host cores (best traversal speed).  LBVH: Morton-code radix
+ * sort + Karras hierarchy on the GPU (fastest build, for large meshes).  AUTO: LBVH from 4 M primitives up. */
+enum { PT_ACCEL_SAH = 0, PT_ACCEL_LBVH = 1, PT_ACCEL_AUTO = 2 };
+int pt_set_accel_builder(int accel);
+/* What the scene was built with: *accel = PT_ACCEL_SAH or PT_ACCEL_LBVH, *build_ms = acceleration-structure build
+ * time (host wall clock for SAH; device time for LBVH), *max_depth = levels of 4-wide nodes. */
+int pt_scene_accel_info(const pt_scene *scene, int *accel, double *build_ms, int *max_depth);
 /* Re-sends every device array of the scene (nodes, triangles, shading records, materials, texels, lights) from
  * its pinned host image, asynchronously on `stream`: the host->device leg of a call that starts from host
  * memory (Scene::load's result living on the host).  *bytes_out = bytes copied. */

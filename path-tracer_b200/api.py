@@ -19,7 +19,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
 EXPORTS = ["pt_last_error", "pt_device_count", "pt_profile_default", "pt_profile_load_yaml", "pt_scene_load_isf",
-           "pt_scene_create", "pt_scene_synthetic", "pt_scene_destroy", "pt_scene_upload", "pt_set_kernel_timing", "pt_scene_get_desc", "pt_scene_info",
+           "pt_scene_create", "pt_scene_synthetic", "pt_scene_destroy", "pt_set_accel_builder", "pt_scene_accel_info", "pt_scene_upload", "pt_set_kernel_timing", "pt_scene_get_desc", "pt_scene_info",
            "pt_trace_closest", "pt_trace_closest_device", "pt_trace_transmittance", "pt_triangle_intersect",
            "pt_trace_paths", "pt_render_accum_device", "pt_aov_name", "pt_debug_textures", "pt_render_progressive",
            "pt_tonemap_device", "pt_render", "pt_write_png", "pt_read_png", "pt_free"]
@@ -69,6 +69,8 @@ def lib():
         L.pt_render.argtypes = [vp, C.POINTER(pt_profile), u64, vp, vp, C.POINTER(pt_stats)]
         L.pt_write_png.argtypes = [C.c_char_p, vp, u32, u32]
         L.pt_read_png.argtypes = [C.c_char_p, u32, C.POINTER(u32), C.POINTER(u32), C.POINTER(C.POINTER(C.c_uint8))]
+        L.pt_set_accel_builder.argtypes = [C.c_int]
+        L.pt_scene_accel_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.pt_aov_name.argtypes = [C.c_int]
         L.pt_aov_name.restype = C.c_char_p
         L.pt_debug_textures.argtypes = [vp, u32, u32, vp, C.POINTER(u64)]
@@ -86,6 +88,17 @@ def _check(rc):
 
 def device_count():
     return lib().pt_device_count()
+
+
+ACCEL_SAH, ACCEL_LBVH, ACCEL_AUTO = 0, 1, 2
+
+
+def set_accel_builder(accel):
+    """Acceleration-structure builder of the scenes created from now on: "sah" (host binned SAH, default), "lbvh"
+    (GPU Morton/radix-sort LBVH) or "auto".  Replaces KDTree::build (scene/internal/model.rs:96, internal/mod.rs:42)."""
+    if isinstance(accel, str):
+        accel = {"sah": ACCEL_SAH, "lbvh": ACCEL_LBVH, "auto": ACCEL_AUTO}[accel]
+    _check(lib().pt_set_accel_builder(accel))
 
 
 class Profile:
@@ -165,6 +178,11 @@ class Scene:
         a, b, c, d = C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_uint64()
         _check(lib().pt_scene_info(self.h, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
         return dict(n_tris=a.value, n_prims=b.value, n_nodes=c.value, device_bytes=d.value)
+
+    def accel_info(self):
+        a, ms, d = C.c_int(), C.c_double(), C.c_int()
+        _check(lib().pt_scene_accel_info(self.h, C.byref(a), C.byref(ms), C.byref(d)))
+        return dict(accel=("sah", "lbvh")[a.value], build_ms=ms.value, max_depth=d.value)
 
     def arrays(self):
         """Host copy of the flat scene as a SceneArrays (used to hand the same scene to a checker)."""

@@ -64,6 +64,7 @@ struct DevScene {
   const uint8_t *texels;
   const DevLight *lights;
   const float *tri_pos9;  // original-order positions; only uploaded when a normal map exists
+  const float *srgb_lut;  // 256 entries: powf(i / 255, 2.2), the sRGB -> linear step of material.rs:132-146
   uint32_t n_tris, n_spheres, n_lights, n_nodes;
   uint32_t root_is_valid;
   uint32_t any_alpha;  // some material may be non-opaque
@@ -90,6 +91,7 @@ struct WaveState {
   float4 *thr[2];     // xyz throughput
   float4 *hit;        // (dist, u, v, HitRec.idx bits; idx < 0 = miss)
   float4 *radiance;   // per slot: xyz sum of this path's contributions (zeroed by raygen, atomically added to)
+  uint32_t *hitq;     // queue positions whose ray hit a surface, appended by k_extend: the work list of k_shade
   // shadow queue (one entry per light per shaded hit with a non-zero unshadowed contribution)
   float4 *sh_o;       // xyz origin, w = point-light distance (or -1 for directional)
   float4 *sh_d;       // xyz direction, w = slot
@@ -111,6 +113,8 @@ enum {
   CTR_SHADOW1 = 3,  // shadow rays emitted with buffer 1  }
   CTR_WORK_EXTEND = 4,  // persistent work-fetch cursors
   CTR_WORK_SHADOW = 5,
+  CTR_HITS0 = 6,    // entries of hitq written by k_extend(bounce) for bounce even / odd: k_extend(b) fills
+  CTR_HITS1 = 7,    // CTR_HITS(b & 1) and clears the other one, which k_shade(b - 1) has finished reading
   CTR_STAT_EXTEND = 8,  // 64-bit statistics start here (pairs)
   CTR_STAT_SHADOW = 10,
   CTR_STAT_RECAST = 12,
@@ -118,6 +122,7 @@ enum {
 };
 #define CTR_QUEUE(b) (2u * (b))
 #define CTR_SHADOW(b) (2u * (b) + 1u)
+#define CTR_HITS(b) (6u + (b))
 
 struct WaveParams {
   uint32_t width, height;

@@ -21,6 +21,15 @@
 #ifndef PTB_SHADOW_MINB
 #define PTB_SHADOW_MINB 1
 #endif
+// 1: k_extend finishes missed paths itself (background term) and hands k_shade a compact list of the queue positions
+// that hit something, so that every lane of k_shade has a surface to shade (mod.rs:184-186 leaves the loop on a miss).
+#ifndef PTB_HITQ
+#define PTB_HITQ 0
+#endif
+// 1: wave-state loads/stores use the streaming (evict-first) cache policy so that they do not displace BVH nodes.
+#ifndef PTB_STREAM
+#define PTB_STREAM 0
+#endif
 
 namespace ptb {
 
@@ -97,6 +106,7 @@ __global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene
   if (slot == 0) {
     W.counters[CTR_QUEUE(0)] = P.n_paths;
     W.counters[CTR_WORK_EXTEND] = 0;
+    W.counters[CTR_HITS(0)] = 0;
   }
   if (slot >= P.n_paths) return;
   Ray r = generate_ray(S, P, make_key(P, slot));
@@ -122,8 +132,37 @@ __device__ __forceinline__ uint32_t refill(uint32_t *cursor, bool idle, uint32_t
   return idx < n ? idx : 0xFFFFFFFFu;
 }
 
-constexpr int REFILL_THRESHOLD = 24;  // refill when fewer lanes than this still own a ray
-constexpr int LEAF_THRESHOLD = 12;    // run the (divergent) primitive test once this many lanes wait at a leaf
+__device__ __forceinline__ void add_radiance(float4 *radiance, uint32_t slot, V3 c) {
+  float *dst = reinterpret_cast<float *>(radiance + slot);
+  if (c.x != 0.0f) atomicAdd(dst + 0, c.x);
+  if (c.y != 0.0f) atomicAdd(dst + 1, c.y);
+  if (c.z != 0.0f) atomicAdd(dst + 2, c.z);
+}
+
+// wave-state accesses: plain, or streaming (PTB_STREAM)
+__device__ __forceinline__ float4 ld_wave(const float4 *p) {
+#if PTB_STREAM
+  return __ldcs(p);
+#else
+  return *p;
+#endif
+}
+__device__ __forceinline__ void st_wave(float4 *p, float4 v) {
+#if PTB_STREAM
+  __stcs(p, v);
+#else
+  *p = v;
+#endif
+}
+
+#ifndef PTB_REFILL_T
+#define PTB_REFILL_T 24
+#endif
+#ifndef PTB_LEAF_T
+#define PTB_LEAF_T 12
+#endif
+constexpr int REFILL_THRESHOLD = PTB_REFILL_T;  // refill when fewer lanes than this still own a ray
+constexpr int LEAF_THRESHOLD = PTB_LEAF_T;      // run the (divergent) primitive test once this many lanes wait at a leaf
 
 // extend: closest accepted hit (alpha walk included) of every queued ray.  Persistent warps with lane-level ray
 // replacement; inside a warp, lanes that reach a leaf wait until LEAF_THRESHOLD lanes have one (or nobody is at an
@@ -136,14 +175,18 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
     W.counters[CTR_QUEUE(outb)] = 0;  // the queues k_shade(bounce) appends to
     W.counters[CTR_SHADOW(outb)] = 0;
     W.counters[CTR_WORK_SHADOW] = 0;
+    W.counters[CTR_HITS(outb)] = 0;
     stat_add(W.counters, CTR_STAT_EXTEND, n);
   }
+#if PTB_HITQ
+  const V3 bg = mk3(S.background[0], S.background[1], S.background[2]);
+  const bool bg_lit = bg.x != 0.0f || bg.y != 0.0f || bg.z != 0.0f;
+#endif
   constexpr uint32_t NONE = 0xFFFFFFFFu;
   uint32_t recasts = 0;
   ClosestTrav tv;
   NodeOrder no{};
-  float stk_t[PTB_STACK];
-  uint32_t stk_r[PTB_STACK];
+  ClosestStack stk;
   uint32_t q = NONE, slot = 0, alpha_j = 0;
   bool drained = false, recorded = false;
   tv.cur = ClosestTrav::DONE;
@@ -151,7 +194,7 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
     uint32_t nq = refill(&W.counters[CTR_WORK_EXTEND], q == NONE, n, drained);
     if (nq != NONE) {
       q = nq;
-      float4 o4 = W.ray_o[in][q], d4 = W.ray_d[in][q];
+      float4 o4 = ld_wave(&W.ray_o[in][q]), d4 = ld_wave(&W.ray_d[in][q]);
       Ray r;
       r.o = mk3(o4.x, o4.y, o4.z);
       r.d = mk3(d4.x, d4.y, d4.z);
@@ -164,16 +207,20 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
     if (__ballot_sync(0xffffffffu, q != NONE) == 0) break;
     for (;;) {
       const bool has = q != NONE;
-      if (has && tv.at_inner()) tv.node_step(S, no, stk_t, stk_r);
+#if PTB_HITQ
+      bool fin_hit = false;
+      uint32_t q_fin = 0;
+#endif
+      if (has && tv.at_inner()) tv.node_step(S, no, stk);
       const bool leaf = has && tv.at_leaf();
       const uint32_t m_leaf = __ballot_sync(0xffffffffu, leaf);
       const uint32_t m_inner = __ballot_sync(0xffffffffu, has && tv.at_inner());
-      if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) tv.leaf_step(S, stk_t, stk_r);
+      if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) tv.leaf_step(S, stk);
       if (has && tv.cur == ClosestTrav::DONE) {
         bool done = true;
         if (tv.st.idx >= 0) {
           // record the examined hit: it is shaded unless a later hit of the alpha walk replaces it (mod.rs:188-205)
-          W.hit[q] = make_float4(tv.st.best_t, tv.st.u, tv.st.v, __int_as_float(tv.st.idx));
+          st_wave(&W.hit[q], make_float4(tv.st.best_t, tv.st.u, tv.st.v, __int_as_float(tv.st.idx)));
           recorded = true;
           if (S.any_alpha && (tv.st.flags & TRI_FLAG_ALPHA)) {
             float op = hit_opacity(S, tv.st.idx, tv.st.u, tv.st.v);
@@ -187,10 +234,32 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
           }
         }
         if (done) {
-          if (!recorded) W.hit[q] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));  // miss
+#if PTB_HITQ
+          if (recorded) {
+            fin_hit = true;
+            q_fin = q;
+          } else if (bg_lit) {  // miss: color + throughput * background, and the path ends (mod.rs:184-186)
+            const float4 t4 = W.thr[in][q];
+            add_radiance(W.radiance, slot, mul_el(mk3(t4.x, t4.y, t4.z), bg));
+          }
+#else
+          if (!recorded) st_wave(&W.hit[q], make_float4(0.f, 0.f, 0.f, __int_as_float(-1)));  // miss
+#endif
           q = NONE;
         }
       }
+#if PTB_HITQ
+      {  // warp-aggregated append of the rays that ended on a surface in this iteration
+        const uint32_t mh = __ballot_sync(0xffffffffu, fin_hit);
+        if (mh) {
+          const int leader = __ffs(mh) - 1;
+          uint32_t base = 0;
+          if ((int)lane_id() == leader) base = atomicAdd(&W.counters[CTR_HITS(in)], (uint32_t)__popc(mh));
+          base = __shfl_sync(0xffffffffu, base, leader);
+          if (fin_hit) W.hitq[base + (uint32_t)__popc(mh & lanemask_lt())] = q_fin;
+        }
+      }
+#endif
       const uint32_t busy = __ballot_sync(0xffffffffu, q != NONE);
       if (busy == 0 || (!drained && __popc(busy) < REFILL_THRESHOLD)) break;
     }
@@ -215,13 +284,6 @@ __device__ __forceinline__ void warp_append2(uint32_t *pair, bool want_path, boo
   pos_shadow = (uint32_t)(base >> 32) + (uint32_t)__popc(ms & lanemask_lt());
 }
 
-__device__ __forceinline__ void add_radiance(float4 *radiance, uint32_t slot, V3 c) {
-  float *dst = reinterpret_cast<float *>(radiance + slot);
-  if (c.x != 0.0f) atomicAdd(dst + 0, c.x);
-  if (c.y != 0.0f) atomicAdd(dst + 1, c.y);
-  if (c.z != 0.0f) atomicAdd(dst + 2, c.z);
-}
-
 // shade: miss/background, emissive, next-event setup (shadow queue), GGX sample, throughput, cutoff, RR,
 // and compaction of the surviving paths into the other queue buffer.  Queue positions are assigned statically
 // (warp-strided): no work-fetch atomic; the last light's shadow entry and the next ray share one reservation atomic.
@@ -229,19 +291,28 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
                                                                const __grid_constant__ WaveParams P, WaveState W,
                                                                uint32_t bounce) {
   const uint32_t in = bounce & 1u, outb = in ^ 1u;
+#if PTB_HITQ
+  const uint32_t n = W.counters[CTR_HITS(in)];
+#else
   const uint32_t n = W.counters[CTR_QUEUE(in)];
+#endif
   if (blockIdx.x == 0 && threadIdx.x == 0) W.counters[CTR_WORK_EXTEND] = 0;
   uint32_t *pair = &W.counters[CTR_QUEUE(outb)];
   const uint32_t warps = gridDim.x * (blockDim.x >> 5), warp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   for (uint32_t base = warp * 32u; base < n; base += warps * 32u) {
+#if PTB_HITQ
+    const bool active = base + lane_id() < n;
+    const uint32_t q = active ? W.hitq[base + lane_id()] : 0u;
+#else
     const uint32_t q = base + lane_id();
     const bool active = q < n;
+#endif
     Ray r{};
     V3 thr{}, rad = mk3(0.f, 0.f, 0.f);
     ShadeCtx ctx{};
     uint32_t slot = 0;
     if (active) {
-      float4 o4 = W.ray_o[in][q], d4 = W.ray_d[in][q], t4 = W.thr[in][q], h4 = W.hit[q];
+      float4 o4 = ld_wave(&W.ray_o[in][q]), d4 = ld_wave(&W.ray_d[in][q]), t4 = ld_wave(&W.thr[in][q]), h4 = ld_wave(&W.hit[q]);
       slot = (uint32_t)__float_as_int(d4.w);
       r.o = mk3(o4.x, o4.y, o4.z);
       r.d = mk3(d4.x, d4.y, d4.z);
@@ -262,10 +333,10 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
       uint32_t pp, ps;
       warp_append2(pair, false, want, pp, ps);
       if (want && ps < W.shadow_capacity) {
-        W.sh_o[ps] = make_float4(so.x, so.y, so.z, limit);
-        W.sh_d[ps] = make_float4(sd.x, sd.y, sd.z, __int_as_float((int)slot));
-        W.sh_c[ps] = make_float4(c.x, c.y, c.z, ctx.sf.is_sphere ? __int_as_float(0x7fc00000) : ctx.sf.tu);
-        W.sh_p[ps] = make_float4(ctx.sf.position.x, ctx.sf.position.y, ctx.sf.position.z, ctx.sf.tv);
+        st_wave(&W.sh_o[ps], make_float4(so.x, so.y, so.z, limit));
+        st_wave(&W.sh_d[ps], make_float4(sd.x, sd.y, sd.z, __int_as_float((int)slot)));
+        st_wave(&W.sh_c[ps], make_float4(c.x, c.y, c.z, ctx.sf.is_sphere ? __int_as_float(0x7fc00000) : ctx.sf.tu));
+        st_wave(&W.sh_p[ps], make_float4(ctx.sf.position.x, ctx.sf.position.y, ctx.sf.position.z, ctx.sf.tv));
       }
     }
     const float pu = ctx.sf.is_sphere ? __int_as_float(0x7fc00000) : ctx.sf.tu, pv = ctx.sf.tv;
@@ -276,15 +347,15 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
     uint32_t pp, ps;
     warp_append2(pair, alive, want, pp, ps);
     if (want && ps < W.shadow_capacity) {
-      W.sh_o[ps] = make_float4(so.x, so.y, so.z, limit);
-      W.sh_d[ps] = make_float4(sd.x, sd.y, sd.z, __int_as_float((int)slot));
-      W.sh_c[ps] = make_float4(c.x, c.y, c.z, pu);
-      W.sh_p[ps] = make_float4(ppos.x, ppos.y, ppos.z, pv);
+      st_wave(&W.sh_o[ps], make_float4(so.x, so.y, so.z, limit));
+      st_wave(&W.sh_d[ps], make_float4(sd.x, sd.y, sd.z, __int_as_float((int)slot)));
+      st_wave(&W.sh_c[ps], make_float4(c.x, c.y, c.z, pu));
+      st_wave(&W.sh_p[ps], make_float4(ppos.x, ppos.y, ppos.z, pv));
     }
     if (alive) {
-      W.ray_o[outb][pp] = make_float4(next.o.x, next.o.y, next.o.z, 0.f);
-      W.ray_d[outb][pp] = make_float4(next.d.x, next.d.y, next.d.z, __int_as_float((int)slot));
-      W.thr[outb][pp] = make_float4(thr.x, thr.y, thr.z, 0.f);
+      st_wave(&W.ray_o[outb][pp], make_float4(next.o.x, next.o.y, next.o.z, 0.f));
+      st_wave(&W.ray_d[outb][pp], make_float4(next.d.x, next.d.y, next.d.z, __int_as_float((int)slot)));
+      st_wave(&W.thr[outb][pp], make_float4(thr.x, thr.y, thr.z, 0.f));
     }
   }
 }
@@ -432,7 +503,7 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
     uint32_t nq = refill(&W.counters[CTR_WORK_SHADOW], q == NONE, n, drained);
     if (nq != NONE) {
       q = nq;
-      float4 o4 = W.sh_o[q], d4 = W.sh_d[q], c4 = W.sh_c[q], p4 = W.sh_p[q];
+      float4 o4 = ld_wave(&W.sh_o[q]), d4 = ld_wave(&W.sh_d[q]), c4 = ld_wave(&W.sh_c[q]), p4 = ld_wave(&W.sh_p[q]);
       Ray r;
       r.o = mk3(o4.x, o4.y, o4.z);
       r.d = mk3(d4.x, d4.y, d4.z);
@@ -490,6 +561,9 @@ __global__ void __launch_bounds__(256) k_tonemap(const float *__restrict__ accum
   rgb8[i] = to_u8(powf(t, 1.0f / 2.2f) * 255.0f);
 }
 
+// sRGB -> linear table: the albedo texel conversion of material.rs:132-146, evaluated once per texel value.
+__global__ void k_init_srgb_lut(float *lut) { lut[threadIdx.x] = powf((float)threadIdx.x / 255.0f, 2.2f); }
+
 // ------------------------------------------------------------------------------------------------
 // host-side launchers
 static int g_sm_count = 0;
@@ -530,6 +604,7 @@ void launch_triangle_intersect(const float *rays, const float *tris, uint32_t n,
 void launch_debug_aov(const DevScene &S, uint32_t width, uint32_t height, uint8_t *planes, uint32_t *n_hit, cudaStream_t st) {
   k_debug_aov<<<(width * height + 127) / 128, 128, 0, st>>>(S, width, height, planes, n_hit);
 }
+void launch_init_srgb_lut(float *lut, cudaStream_t st) { k_init_srgb_lut<<<1, 256, 0, st>>>(lut); }
 void launch_raygen(const DevScene &S, const WaveParams &P, const WaveState &W, cudaStream_t st) {
   k_raygen<<<(P.n_paths + 255) / 256, 256, 0, st>>>(S, P, W);
 }

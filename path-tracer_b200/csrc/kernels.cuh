@@ -10,6 +10,7 @@ void launch_trace_paths(const DevScene &S, const WaveParams &P, const uint32_t *
                         uint32_t *counts, cudaStream_t st);
 void launch_triangle_intersect(const float *rays, const float *tris, uint32_t n, pt_hit *out, cudaStream_t st);
 void launch_debug_aov(const DevScene &S, uint32_t width, uint32_t height, uint8_t *planes, uint32_t *n_hit, cudaStream_t st);
+void launch_init_srgb_lut(float *lut, cudaStream_t st);
 void launch_raygen(const DevScene &S, const WaveParams &P, const WaveState &W, cudaStream_t st);
 void launch_extend(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st);
 void launch_shade(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st);

@@ -1,0 +1,594 @@
+// lbvh.cu — GPU acceleration-structure build for large meshes: Morton codes, a hand-written LSD radix sort, the
+// Karras 2012 radix-tree hierarchy, a bottom-up box fit and a level-by-level collapse into the same 128-byte 4-wide
+// nodes the host SAH builder emits (bvh_build.cpp).  Replaces KDTree::build of the reference's third-party kdtree-ray
+// crate (call sites scene/internal/model.rs:96, scene/internal/mod.rs:42) when PT_ACCEL_LBVH is selected.
+// The tree is only a conservative candidate filter (results equal brute force; tests/test_gpu_parity.py), so the two
+// builders are interchangeable: SAH gives faster traversal, LBVH builds a 20 M-triangle scene in tens of milliseconds.
+#include <cuda_runtime.h>
+
+#include <math_constants.h>
+
+#include <cfloat>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "host_api.hpp"
+
+namespace ptb {
+namespace {
+
+#define LB_TRY(expr)                                                                                \
+  do {                                                                                              \
+    cudaError_t _e = (expr);                                                                        \
+    if (_e != cudaSuccess) {                                                                        \
+      set_error("CUDA error %s at %s:%d (%s)", cudaGetErrorString(_e), __FILE__, __LINE__, #expr);  \
+      return PT_ERR_CUDA;                                                                           \
+    }                                                                                               \
+  } while (0)
+
+struct DevBuf {  // frees every temporary on scope exit
+  std::vector<void *> ptrs;
+  ~DevBuf() {
+    for (void *p : ptrs) cudaFree(p);
+  }
+  template <typename T>
+  cudaError_t alloc(T **out, size_t count) {
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, (count ? count : 1) * sizeof(T));
+    if (e == cudaSuccess) ptrs.push_back(p);
+    *out = reinterpret_cast<T *>(p);
+    return e;
+  }
+};
+
+// ---- order-preserving float <-> uint for atomicMin/Max on bounds ----
+__device__ __forceinline__ uint32_t f2o(float f) {
+  uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float o2f(uint32_t o) {
+  uint32_t u = (o & 0x80000000u) ? (o & 0x7FFFFFFFu) : ~o;
+#ifdef __CUDA_ARCH__
+  return __uint_as_float(u);
+#else
+  float f;
+  memcpy(&f, &u, 4);
+  return f;
+#endif
+}
+
+// ---- 1. primitive boxes (triangles then spheres) + centroid bounds ----
+__global__ void __launch_bounds__(256) k_prim_boxes(const float *__restrict__ pos9, uint32_t nt,
+                                                    const float4 *__restrict__ spheres, uint32_t ns,
+                                                    float4 *__restrict__ blo, float4 *__restrict__ bhi,
+                                                    uint32_t *__restrict__ cbounds /* 6 ordered uints */) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x, n = nt + ns;
+  float c[3] = {0, 0, 0};
+  const bool live = i < n;
+  if (live) {
+    float lo[3], hi[3];
+    if (i < nt) {
+      const float *p = pos9 + (size_t)i * 9;
+      for (int k = 0; k < 3; ++k) {
+        lo[k] = fminf(fminf(p[k], p[3 + k]), p[6 + k]);
+        hi[k] = fmaxf(fmaxf(p[k], p[3 + k]), p[6 + k]);
+      }
+    } else {
+      const float4 s = spheres[i - nt];
+      const float r = fabsf(s.w) * 1.0001f + 1e-6f;  // same margin as bvh_build.cpp
+      lo[0] = s.x - r; lo[1] = s.y - r; lo[2] = s.z - r;
+      hi[0] = s.x + r; hi[1] = s.y + r; hi[2] = s.z + r;
+    }
+    blo[i] = make_float4(lo[0], lo[1], lo[2], 0.f);
+    bhi[i] = make_float4(hi[0], hi[1], hi[2], 0.f);
+    for (int k = 0; k < 3; ++k) c[k] = 0.5f * (lo[k] + hi[k]);
+  }
+  // warp-reduce the centroid bounds, then one atomic pair per warp and axis
+  for (int k = 0; k < 3; ++k) {
+    float mn = live ? c[k] : FLT_MAX, mx = live ? c[k] : -FLT_MAX;
+    for (int o = 16; o; o >>= 1) {
+      mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    if ((threadIdx.x & 31) == 0 && mn <= mx) {
+      atomicMin(&cbounds[k], f2o(mn));
+      atomicMax(&cbounds[3 + k], f2o(mx));
+    }
+  }
+}
+
+__device__ __forceinline__ uint32_t expand10(uint32_t v) {  // 10 bits -> every third bit
+  v = (v * 0x00010001u) & 0xFF0000FFu;
+  v = (v * 0x00000101u) & 0x0F00F00Fu;
+  v = (v * 0x00000011u) & 0xC30C30C3u;
+  v = (v * 0x00000005u) & 0x49249249u;
+  return v;
+}
+
+// ---- 2. 30-bit Morton code of the box centroid ----
+__global__ void __launch_bounds__(256) k_morton(const float4 *__restrict__ blo, const float4 *__restrict__ bhi, uint32_t n,
+                                                const uint32_t *__restrict__ cbounds, uint32_t *__restrict__ keys,
+                                                uint32_t *__restrict__ vals) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 lo = blo[i], hi = bhi[i];
+  const float c[3] = {0.5f * (lo.x + hi.x), 0.5f * (lo.y + hi.y), 0.5f * (lo.z + hi.z)};
+  uint32_t q[3];
+  for (int k = 0; k < 3; ++k) {
+    const float mn = o2f(cbounds[k]), mx = o2f(cbounds[3 + k]);
+    const float ext = mx - mn;
+    float t = ext > 0.f ? (c[k] - mn) / ext : 0.f;
+    t = fminf(fmaxf(t * 1024.f, 0.f), 1023.f);
+    q[k] = (uint32_t)t;
+  }
+  keys[i] = (expand10(q[0]) << 2) | (expand10(q[1]) << 1) | expand10(q[2]);
+  vals[i] = i;
+}
+
+// ---- 3. LSD radix sort of (key, value) pairs, 8 bits per pass ----
+constexpr int RS_THREADS = 256, RS_ITEMS = 16, RS_TILE = RS_THREADS * RS_ITEMS;
+
+__global__ void __launch_bounds__(RS_THREADS) k_radix_hist(const uint32_t *__restrict__ keys, uint32_t n, int shift,
+                                                          uint32_t *__restrict__ counts /* [256][blocks] */) {
+  __shared__ uint32_t h[256];
+  h[threadIdx.x] = 0;
+  __syncthreads();
+  const uint32_t base = blockIdx.x * RS_TILE;
+  for (int k = 0; k < RS_ITEMS; ++k) {
+    const uint32_t i = base + k * RS_THREADS + threadIdx.x;
+    if (i < n) atomicAdd(&h[(keys[i] >> shift) & 255u], 1u);
+  }
+  __syncthreads();
+  counts[threadIdx.x * gridDim.x + blockIdx.x] = h[threadIdx.x];
+}
+
+// Stable scatter: the tile is processed in rounds of 256 keys in input order; within a round a key's rank among the
+// equal digits is (keys of earlier warps) + (earlier lanes of its own warp, via __match_any_sync).
+__global__ void __launch_bounds__(RS_THREADS) k_radix_scatter(const uint32_t *__restrict__ keys_in,
+                                                             const uint32_t *__restrict__ vals_in, uint32_t n, int shift,
+                                                             const uint32_t *__restrict__ offsets /* scanned counts */,
+                                                             uint32_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out) {
+  __shared__ uint32_t running[256];              // next output position of each digit for this block
+  __shared__ uint32_t wcount[RS_THREADS / 32][256];  // per warp, per digit: keys of this round
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+  running[threadIdx.x] = offsets[threadIdx.x * gridDim.x + blockIdx.x];
+  const uint32_t base = blockIdx.x * RS_TILE;
+  for (int k = 0; k < RS_ITEMS; ++k) {
+    for (int w = 0; w < RS_THREADS / 32; ++w) wcount[w][threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t i = base + k * RS_THREADS + threadIdx.x;
+    const bool live = i < n;
+    uint32_t key = 0, val = 0, digit = 256 + lane;  // dead lanes match nobody
+    if (live) {
+      key = keys_in[i];
+      val = vals_in[i];
+      digit = (key >> shift) & 255u;
+    }
+    const uint32_t peers = __match_any_sync(0xffffffffu, digit);
+    const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
+    if (live && rank == 0) wcount[warp][digit] = __popc(peers);
+    __syncthreads();
+    if (live) {
+      uint32_t pos = running[digit] + rank;
+      for (uint32_t w = 0; w < warp; ++w) pos += wcount[w][digit];
+      keys_out[pos] = key;
+      vals_out[pos] = val;
+    }
+    __syncthreads();
+    uint32_t tot = 0;
+    for (int w = 0; w < RS_THREADS / 32; ++w) tot += wcount[w][threadIdx.x];
+    running[threadIdx.x] += tot;
+    __syncthreads();
+  }
+}
+
+// ---- exclusive scan of a uint32 array (three phases; the block sums are scanned by one block) ----
+constexpr int SC_THREADS = 256, SC_ITEMS = 8, SC_TILE = SC_THREADS * SC_ITEMS;
+
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t *total) {  // 256 threads
+  __shared__ uint32_t wsum[SC_THREADS / 32];
+  __shared__ uint32_t tot;
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  uint32_t inc = v;
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+    if ((int)lane >= o) inc += t;
+  }
+  if (lane == 31) wsum[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t s = lane < SC_THREADS / 32 ? wsum[lane] : 0;
+    uint32_t si = s;
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t t = __shfl_up_sync(0xffffffffu, si, o);
+      if ((int)lane >= o) si += t;
+    }
+    if (lane < SC_THREADS / 32) wsum[lane] = si - s;
+    if (lane == 31) tot = si;
+  }
+  __syncthreads();
+  const uint32_t r = wsum[warp] + inc - v;
+  if (total) *total = tot;
+  __syncthreads();
+  return r;
+}
+
+__global__ void __launch_bounds__(SC_THREADS) k_scan_tiles(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
+                                                          uint32_t n, uint32_t *__restrict__ tile_sums) {
+  const uint32_t base = blockIdx.x * SC_TILE + threadIdx.x * SC_ITEMS;
+  uint32_t v[SC_ITEMS], s = 0;
+  for (int k = 0; k < SC_ITEMS; ++k) {
+    v[k] = base + k < n ? in[base + k] : 0u;
+    s += v[k];
+  }
+  uint32_t total;
+  uint32_t ex = block_exclusive_scan(s, &total);
+  for (int k = 0; k < SC_ITEMS; ++k) {
+    if (base + k < n) out[base + k] = ex;
+    ex += v[k];
+  }
+  if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+__global__ void __launch_bounds__(SC_THREADS) k_scan_sums(uint32_t *sums, uint32_t n, uint32_t *grand_total) {
+  uint32_t carry = 0;  // one block walks the tile sums
+  for (uint32_t base = 0; base < n; base += SC_THREADS) {
+    const uint32_t i = base + threadIdx.x;
+    const uint32_t v = i < n ? sums[i] : 0u;
+    uint32_t total;
+    const uint32_t ex = block_exclusive_scan(v, &total);
+    if (i < n) sums[i] = carry + ex;
+    carry += total;
+  }
+  if (threadIdx.x == 0 && grand_total) *grand_total = carry;
+}
+__global__ void __launch_bounds__(SC_THREADS) k_scan_add(uint32_t *out, uint32_t n, const uint32_t *__restrict__ tile_sums) {
+  const uint32_t base = blockIdx.x * SC_TILE + threadIdx.x * SC_ITEMS;
+  const uint32_t add = tile_sums[blockIdx.x];
+  for (int k = 0; k < SC_ITEMS; ++k)
+    if (base + k < n) out[base + k] += add;
+}
+
+// out[i] = sum of in[0..i); out may alias in.  tmp: at least ceil(n / SC_TILE) + 1 uints; grand total -> tmp[tiles].
+int exclusive_scan_u32(const uint32_t *in, uint32_t *out, uint32_t n, uint32_t *tmp, cudaStream_t st) {
+  if (n == 0) return PT_OK;
+  const uint32_t tiles = (n + SC_TILE - 1) / SC_TILE;
+  k_scan_tiles<<<tiles, SC_THREADS, 0, st>>>(in, out, n, tmp);
+  k_scan_sums<<<1, SC_THREADS, 0, st>>>(tmp, tiles, tmp + tiles);
+  k_scan_add<<<tiles, SC_THREADS, 0, st>>>(out, n, tmp);
+  LB_TRY(cudaGetLastError());
+  return PT_OK;
+}
+
+int radix_sort_pairs(uint32_t *keys, uint32_t *vals, uint32_t *keys_alt, uint32_t *vals_alt, uint32_t n, int bits,
+                     uint32_t *counts, uint32_t *scan_tmp, cudaStream_t st) {
+  const uint32_t blocks = (n + RS_TILE - 1) / RS_TILE;
+  uint32_t *ki = keys, *vi = vals, *ko = keys_alt, *vo = vals_alt;
+  int passes = 0;
+  for (int shift = 0; shift < bits; shift += 8, ++passes) {
+    k_radix_hist<<<blocks, RS_THREADS, 0, st>>>(ki, n, shift, counts);
+    int rc = exclusive_scan_u32(counts, counts, 256u * blocks, scan_tmp, st);
+    if (rc) return rc;
+    k_radix_scatter<<<blocks, RS_THREADS, 0, st>>>(ki, vi, n, shift, counts, ko, vo);
+    std::swap(ki, ko);
+    std::swap(vi, vo);
+  }
+  LB_TRY(cudaGetLastError());
+  if (passes & 1) {  // result must end in keys/vals
+    LB_TRY(cudaMemcpyAsync(keys, ki, n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+    LB_TRY(cudaMemcpyAsync(vals, vi, n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+  }
+  return PT_OK;
+}
+
+// ---- 4. Karras 2012: radix tree over the sorted codes (ties broken by position) ----
+// Node references: bit31 = 1 -> sorted primitive position (a radix-tree leaf); else internal node index.
+constexpr uint32_t PRIM = 0x80000000u;
+
+__device__ __forceinline__ int delta(const uint32_t *__restrict__ keys, int n, int i, int j) {
+  if (j < 0 || j >= n) return -1;
+  const uint32_t a = keys[i], b = keys[j];
+  if (a == b) return 32 + __clz((uint32_t)i ^ (uint32_t)j);
+  return __clz(a ^ b);
+}
+
+__global__ void __launch_bounds__(256) k_radix_tree(const uint32_t *__restrict__ keys, int n, uint32_t *__restrict__ left,
+                                                    uint32_t *__restrict__ right, uint32_t *__restrict__ rlo,
+                                                    uint32_t *__restrict__ rhi, uint32_t *__restrict__ parent_int,
+                                                    uint32_t *__restrict__ parent_prim) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n - 1) return;
+  const int d = delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1) >= 0 ? 1 : -1;
+  const int dmin = delta(keys, n, i, i - d);
+  int lmax = 2;
+  while (delta(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+  int l = 0;
+  for (int t = lmax >> 1; t >= 1; t >>= 1)
+    if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+  const int j = i + l * d;
+  const int dnode = delta(keys, n, i, j);
+  int s = 0;
+  for (int t = (l + 1) >> 1;; t = (t + 1) >> 1) {
+    if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    if (t == 1) break;
+  }
+  const int gamma = i + s * d + min(d, 0);
+  const int lo = min(i, j), hi = max(i, j);
+  const uint32_t lref = lo == gamma ? (PRIM | (uint32_t)gamma) : (uint32_t)gamma;
+  const uint32_t rref = hi == gamma + 1 ? (PRIM | (uint32_t)(gamma + 1)) : (uint32_t)(gamma + 1);
+  left[i] = lref;
+  right[i] = rref;
+  rlo[i] = (uint32_t)lo;
+  rhi[i] = (uint32_t)hi;
+  if (lref & PRIM) parent_prim[gamma] = (uint32_t)i; else parent_int[gamma] = (uint32_t)i;
+  if (rref & PRIM) parent_prim[gamma + 1] = (uint32_t)i; else parent_int[gamma + 1] = (uint32_t)i;
+  if (i == 0) parent_int[0] = 0xFFFFFFFFu;
+}
+
+// ---- 5. bottom-up box fit: the second thread to reach a node merges its children ----
+__global__ void __launch_bounds__(256) k_fit(int n, const uint32_t *__restrict__ sorted_prim, const float4 *__restrict__ blo,
+                                             const float4 *__restrict__ bhi, const uint32_t *__restrict__ left,
+                                             const uint32_t *__restrict__ right, const uint32_t *__restrict__ parent_int,
+                                             const uint32_t *__restrict__ parent_prim, float4 *__restrict__ nlo,
+                                             float4 *__restrict__ nhi, uint32_t *__restrict__ visits) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t node = parent_prim[i];
+  while (node != 0xFFFFFFFFu) {
+    if (atomicAdd(&visits[node], 1u) == 0) return;  // first arrival: the sibling subtree is not finished yet
+    __threadfence();
+    float4 lo[2], hi[2];
+    const uint32_t ch[2] = {left[node], right[node]};
+    for (int k = 0; k < 2; ++k) {
+      if (ch[k] & PRIM) {
+        const uint32_t p = sorted_prim[ch[k] & ~PRIM];
+        lo[k] = blo[p];
+        hi[k] = bhi[p];
+      } else {
+        lo[k] = __ldcg(&nlo[ch[k]]);
+        hi[k] = __ldcg(&nhi[ch[k]]);
+      }
+    }
+    __stcg(&nlo[node], make_float4(fminf(lo[0].x, lo[1].x), fminf(lo[0].y, lo[1].y), fminf(lo[0].z, lo[1].z), 0.f));
+    __stcg(&nhi[node], make_float4(fmaxf(hi[0].x, hi[1].x), fmaxf(hi[0].y, hi[1].y), fmaxf(hi[0].z, hi[1].z), 0.f));
+    __threadfence();
+    node = parent_int[node];
+  }
+}
+
+// ---- 6. collapse to 4-wide nodes, one tree level per launch ----
+struct CollapseArgs {
+  const uint32_t *left, *right, *rlo, *rhi;
+  const float4 *nlo, *nhi;       // internal boxes
+  const float4 *blo, *bhi;       // primitive boxes (original primitive order)
+  const uint32_t *sorted_prim;   // sorted position -> primitive (triangles < nt <= spheres)
+  const uint32_t *tri_rank;      // sorted position -> number of triangles before it (n + 1 entries)
+  uint32_t nt;
+  Bvh4Node *nodes;
+  uint32_t *node_count;
+  uint32_t node_cap;
+};
+
+// A radix-tree node is emitted as one leaf when it holds <= 4 primitives, all triangles (spheres sit alone).
+__device__ __forceinline__ bool is_leaf_ref(const CollapseArgs &A, uint32_t ref) {
+  if (ref & PRIM) return true;
+  const uint32_t lo = A.rlo[ref], hi = A.rhi[ref], cnt = hi - lo + 1;
+  return cnt <= 4 && A.tri_rank[hi + 1] - A.tri_rank[lo] == cnt;
+}
+__device__ __forceinline__ void ref_box(const CollapseArgs &A, uint32_t ref, float4 &lo, float4 &hi) {
+  if (ref & PRIM) {
+    const uint32_t p = A.sorted_prim[ref & ~PRIM];
+    lo = A.blo[p];
+    hi = A.bhi[p];
+  } else {
+    lo = A.nlo[ref];
+    hi = A.nhi[ref];
+  }
+}
+__device__ __forceinline__ float half_area(float4 lo, float4 hi) {
+  const float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
+  return dx * dy + dy * dz + dz * dx;
+}
+__device__ __forceinline__ uint32_t leaf_child(const CollapseArgs &A, uint32_t ref) {
+  uint32_t lo, cnt;
+  if (ref & PRIM) {
+    lo = ref & ~PRIM;
+    cnt = 1;
+    const uint32_t p = A.sorted_prim[lo];
+    if (p >= A.nt) return BVH_LEAF | BVH_SPHERE | (p - A.nt);
+  } else {
+    lo = A.rlo[ref];
+    cnt = A.rhi[ref] - lo + 1;
+  }
+  return BVH_LEAF | (A.tri_rank[lo] << 3) | (cnt - 1);
+}
+
+__global__ void __launch_bounds__(128) k_collapse(const CollapseArgs A, const uint2 *__restrict__ work_in, uint32_t n_in,
+                                                  uint2 *__restrict__ work_out, uint32_t *__restrict__ n_out) {
+  const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= n_in) return;
+  const uint2 item = work_in[w];  // x = radix-tree node (internal, not a leaf), y = 4-wide node index
+  uint32_t kids[4];
+  int nk = 2;
+  kids[0] = A.left[item.x];
+  kids[1] = A.right[item.x];
+  while (nk < 4) {  // open the inner child with the largest box, as the host builder does
+    int best = -1;
+    float ba = -1.f;
+    for (int k = 0; k < nk; ++k) {
+      if (is_leaf_ref(A, kids[k])) continue;
+      float4 lo, hi;
+      ref_box(A, kids[k], lo, hi);
+      const float a = half_area(lo, hi);
+      if (a > ba) { ba = a; best = k; }
+    }
+    if (best < 0) break;
+    const uint32_t c = kids[best];
+    kids[best] = A.left[c];
+    kids[nk++] = A.right[c];
+  }
+  Bvh4Node nd;
+  for (int k = 0; k < 4; ++k) {
+    nd.lo_x[k] = nd.lo_y[k] = nd.lo_z[k] = CUDART_INF_F;
+    nd.hi_x[k] = nd.hi_y[k] = nd.hi_z[k] = -CUDART_INF_F;
+    nd.child[k] = BVH_EMPTY;
+    nd.pad[k] = 0;
+  }
+  for (int k = 0; k < nk; ++k) {
+    float4 lo, hi;
+    ref_box(A, kids[k], lo, hi);
+    // conservative inflation, identical to bvh_build.cpp: a box cull may never drop a primitive Moller-Trumbore accepts
+    const float ex = fmaxf(fabsf(lo.x), fabsf(hi.x)) * 4e-6f + 1e-7f;
+    const float ey = fmaxf(fabsf(lo.y), fabsf(hi.y)) * 4e-6f + 1e-7f;
+    const float ez = fmaxf(fabsf(lo.z), fabsf(hi.z)) * 4e-6f + 1e-7f;
+    nd.lo_x[k] = lo.x - ex; nd.hi_x[k] = hi.x + ex;
+    nd.lo_y[k] = lo.y - ey; nd.hi_y[k] = hi.y + ey;
+    nd.lo_z[k] = lo.z - ez; nd.hi_z[k] = hi.z + ez;
+    if (is_leaf_ref(A, kids[k])) {
+      nd.child[k] = leaf_child(A, kids[k]);
+    } else {
+      const uint32_t id4 = atomicAdd(A.node_count, 1u);
+      nd.child[k] = id4;
+      if (id4 < A.node_cap) work_out[atomicAdd(n_out, 1u)] = make_uint2(kids[k], id4);
+    }
+  }
+  A.nodes[item.y] = nd;
+}
+
+__global__ void __launch_bounds__(256) k_leaf_order(uint32_t n, uint32_t nt, const uint32_t *__restrict__ sorted_prim,
+                                                    const uint32_t *__restrict__ tri_rank, uint32_t *__restrict__ leaf_tris,
+                                                    uint32_t *__restrict__ is_tri) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (is_tri) {
+    is_tri[i] = sorted_prim[i] < nt ? 1u : 0u;
+    return;
+  }
+  const uint32_t p = sorted_prim[i];
+  if (p < nt) leaf_tris[tri_rank[i]] = p;
+}
+
+}  // namespace
+
+// Builds `out` for scene `s` on the current CUDA device.  Returns PT_OK, or PT_ERR_INVALID with *too_deep = 1 when the
+// radix tree is deeper than the traversal stack allows (the caller then falls back to the host SAH build).
+int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_deep) {
+  if (too_deep) *too_deep = 0;
+  const uint32_t nt = (uint32_t)s.n_tris(), ns = (uint32_t)s.sphere_models.size(), n = nt + ns;
+  if (n < 8) {
+    set_error("LBVH build needs at least 8 primitives");
+    return PT_ERR_INVALID;
+  }
+  cudaStream_t st = nullptr;
+  DevBuf B;
+  float *d_pos = nullptr;
+  float4 *d_sph = nullptr, *blo = nullptr, *bhi = nullptr, *nlo = nullptr, *nhi = nullptr;
+  uint32_t *cb = nullptr, *keys = nullptr, *vals = nullptr, *keys2 = nullptr, *vals2 = nullptr, *counts = nullptr;
+  uint32_t *scan_tmp = nullptr, *left = nullptr, *right = nullptr, *rlo = nullptr, *rhi = nullptr, *par_i = nullptr;
+  uint32_t *par_p = nullptr, *visits = nullptr, *tri_rank = nullptr, *leaf_tris = nullptr, *ctr = nullptr;
+  uint2 *work[2] = {nullptr, nullptr};
+  Bvh4Node *nodes = nullptr;
+  const uint32_t rs_blocks = (n + RS_TILE - 1) / RS_TILE;
+  const uint32_t node_cap = n;  // every 4-wide node has >= 2 children, so there are fewer nodes than leaves
+  LB_TRY(B.alloc(&d_pos, (size_t)nt * 9));
+  LB_TRY(B.alloc(&d_sph, ns));
+  LB_TRY(B.alloc(&blo, n));
+  LB_TRY(B.alloc(&bhi, n));
+  LB_TRY(B.alloc(&nlo, n));
+  LB_TRY(B.alloc(&nhi, n));
+  LB_TRY(B.alloc(&cb, 8));
+  LB_TRY(B.alloc(&keys, n));
+  LB_TRY(B.alloc(&vals, n));
+  LB_TRY(B.alloc(&keys2, n));
+  LB_TRY(B.alloc(&vals2, n));
+  LB_TRY(B.alloc(&counts, 256 * (size_t)rs_blocks));
+  LB_TRY(B.alloc(&scan_tmp, (256 * (size_t)rs_blocks + n) / SC_TILE + 16));
+  LB_TRY(B.alloc(&left, n));
+  LB_TRY(B.alloc(&right, n));
+  LB_TRY(B.alloc(&rlo, n));
+  LB_TRY(B.alloc(&rhi, n));
+  LB_TRY(B.alloc(&par_i, n));
+  LB_TRY(B.alloc(&par_p, n));
+  LB_TRY(B.alloc(&visits, n));
+  LB_TRY(B.alloc(&tri_rank, (size_t)n + 1));
+  LB_TRY(B.alloc(&leaf_tris, nt));
+  LB_TRY(B.alloc(&ctr, 8));
+  LB_TRY(B.alloc(&work[0], n));
+  LB_TRY(B.alloc(&work[1], n));
+  LB_TRY(B.alloc(&nodes, node_cap));
+  LB_TRY(cudaMemcpyAsync(d_pos, s.pos.data(), (size_t)nt * 9 * sizeof(float), cudaMemcpyHostToDevice, st));
+  if (ns) {
+    std::vector<float4> sph(ns);
+    for (uint32_t k = 0; k < ns; ++k) {
+      const pt_model &m = s.models[s.sphere_models[k]];
+      sph[k] = make_float4(m.center[0], m.center[1], m.center[2], m.radius);
+    }
+    LB_TRY(cudaMemcpy(d_sph, sph.data(), ns * sizeof(float4), cudaMemcpyHostToDevice));
+  }
+  cudaEvent_t e0, e1;
+  LB_TRY(cudaEventCreate(&e0));
+  LB_TRY(cudaEventCreate(&e1));
+  LB_TRY(cudaEventRecord(e0, st));
+  const uint32_t init_cb[6] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u};
+  LB_TRY(cudaMemcpyAsync(cb, init_cb, sizeof init_cb, cudaMemcpyHostToDevice, st));
+  const uint32_t g256 = (n + 255) / 256;
+  k_prim_boxes<<<g256, 256, 0, st>>>(d_pos, nt, d_sph, ns, blo, bhi, cb);
+  k_morton<<<g256, 256, 0, st>>>(blo, bhi, n, cb, keys, vals);
+  int rc = radix_sort_pairs(keys, vals, keys2, vals2, n, 32, counts, scan_tmp, st);
+  if (rc) return rc;
+  // triangle ranks in sorted order (n + 1 entries: the last one is the triangle count)
+  k_leaf_order<<<g256, 256, 0, st>>>(n, nt, vals, nullptr, nullptr, tri_rank);
+  LB_TRY(cudaMemsetAsync(tri_rank + n, 0, sizeof(uint32_t), st));
+  if ((rc = exclusive_scan_u32(tri_rank, tri_rank, n + 1, scan_tmp, st))) return rc;
+  k_leaf_order<<<g256, 256, 0, st>>>(n, nt, vals, tri_rank, leaf_tris, nullptr);
+  k_radix_tree<<<g256, 256, 0, st>>>(keys, (int)n, left, right, rlo, rhi, par_i, par_p);
+  LB_TRY(cudaMemsetAsync(visits, 0, (size_t)n * sizeof(uint32_t), st));
+  k_fit<<<g256, 256, 0, st>>>((int)n, vals, blo, bhi, left, right, par_i, par_p, nlo, nhi, visits);
+  LB_TRY(cudaGetLastError());
+  // level-by-level collapse; the root of the radix tree (internal node 0) becomes 4-wide node 0
+  CollapseArgs A{left, right, rlo, rhi, nlo, nhi, blo, bhi, vals, tri_rank, nt, nodes, ctr, node_cap};
+  const uint32_t one = 1;
+  LB_TRY(cudaMemcpyAsync(ctr, &one, sizeof one, cudaMemcpyHostToDevice, st));  // node_count = 1 (the root)
+  const uint2 root_item = make_uint2(0u, 0u);
+  LB_TRY(cudaMemcpyAsync(work[0], &root_item, sizeof root_item, cudaMemcpyHostToDevice, st));
+  uint32_t n_in = 1;
+  int depth = 0;
+  // A root that is itself one leaf (<= 4 triangles) cannot occur: n >= 8.
+  while (n_in) {
+    ++depth;
+    if (depth * 3 + 4 > 96) {  // traversal stack bound (PTB_STACK)
+      if (too_deep) *too_deep = 1;
+      set_error("LBVH too deep for the traversal stack");
+      cudaEventDestroy(e0);
+      cudaEventDestroy(e1);
+      return PT_ERR_INVALID;
+    }
+    LB_TRY(cudaMemsetAsync(ctr + 1, 0, sizeof(uint32_t), st));
+    k_collapse<<<(n_in + 127) / 128, 128, 0, st>>>(A, work[0], n_in, work[1], ctr + 1);
+    LB_TRY(cudaMemcpyAsync(&n_in, ctr + 1, sizeof n_in, cudaMemcpyDeviceToHost, st));
+    LB_TRY(cudaStreamSynchronize(st));
+    std::swap(work[0], work[1]);
+  }
+  LB_TRY(cudaEventRecord(e1, st));
+  LB_TRY(cudaEventSynchronize(e1));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (build_ms) *build_ms = ms;
+  uint32_t n_nodes = 0;
+  LB_TRY(cudaMemcpy(&n_nodes, ctr, sizeof n_nodes, cudaMemcpyDeviceToHost));
+  if (n_nodes > node_cap) {
+    set_error("LBVH node pool overflow");
+    return PT_ERR_INVALID;
+  }
+  out.nodes.resize(n_nodes);
+  out.leaf_tris.resize(nt);
+  LB_TRY(cudaMemcpy(out.nodes.data(), nodes, (size_t)n_nodes * sizeof(Bvh4Node), cudaMemcpyDeviceToHost));
+  LB_TRY(cudaMemcpy(out.leaf_tris.data(), leaf_tris, (size_t)nt * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  out.max_depth = depth;
+  return PT_OK;
+}
+
+}  // namespace ptb

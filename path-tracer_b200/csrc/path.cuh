@@ -208,7 +208,7 @@ __device__ __forceinline__ bool shade_finish(const WaveParams &P, const RngKey &
   if (more) {  // mod.rs:265-275
     next.o = c.sf.position + c.sf.normal * NORMAL_BIAS;
     next.d = brdf_sample(c.brdf, c.sf.shading_n, c.view, u32_to_unit(rb.x), u32_to_unit(rb.y));
-    V3 w = eval_indirect(c.brdf, c.sf.shading_n, c.view, next.d) / 1.0f;
+    V3 w = eval_indirect(c.brdf, c.sf.shading_n, c.view, next.d);  // `/ brdf.pdf()` with pdf() == 1: x / 1.0 == x exactly
     thr = mul_el(thr, w);
   }
   if (dot3(thr, thr) < 0.00001f) return false;  // mod.rs:219-221

@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -69,6 +70,7 @@ struct pt_scene {
   std::vector<cudaEvent_t> events;  // pool for per-kernel timing (pt_set_kernel_timing)
   uint64_t device_bytes = 0;
   double build_ms = 0;
+  int accel = PT_ACCEL_SAH;
   // wave buffers, grown lazily and reused between renders (guarded: one render at a time per scene)
   std::mutex mu;
   WaveState wave{};
@@ -98,10 +100,42 @@ int upload(pt_scene *sc, const std::vector<T> &v, const T **out) {
 
 bool material_may_be_transparent(const pt_material &m) { return !(m.opacity_tex < 0 && m.opacity >= 1.0f); }
 
+int g_accel = -1;  // -1: not set through the API -> $PT_B200_ACCEL or SAH
+int accel_choice() {
+  if (g_accel >= 0) return g_accel;
+  if (const char *e = std::getenv("PT_B200_ACCEL")) {
+    if (!std::strcmp(e, "lbvh")) return PT_ACCEL_LBVH;
+    if (!std::strcmp(e, "auto")) return PT_ACCEL_AUTO;
+  }
+  return PT_ACCEL_SAH;
+}
+
 int build_device_scene(pt_scene *sc) {
   HostScene &h = sc->host;
   unsigned hw = std::max(1u, std::thread::hardware_concurrency());
-  build_bvh4(h, sc->bvh, (int)std::min(hw, 32u));
+  int accel = accel_choice();
+  const uint64_t n_prims_geom = h.n_tris() + h.sphere_models.size();
+  if (accel == PT_ACCEL_AUTO) accel = n_prims_geom >= (4ull << 20) ? PT_ACCEL_LBVH : PT_ACCEL_SAH;
+  if (n_prims_geom < 8) accel = PT_ACCEL_SAH;
+  sc->accel = PT_ACCEL_SAH;
+  bool built = false;
+  if (accel == PT_ACCEL_LBVH) {
+    float ms = 0;
+    int too_deep = 0;
+    int rc = build_bvh4_lbvh(h, sc->bvh, &ms, &too_deep);
+    if (rc == PT_OK) {
+      built = true;
+      sc->accel = PT_ACCEL_LBVH;
+      sc->build_ms = ms;
+    } else if (!too_deep) {
+      return rc;
+    }  // too deep for the traversal stack (pathological duplicates): fall through to the SAH builder
+  }
+  if (!built) {
+    auto t0 = std::chrono::steady_clock::now();
+    build_bvh4(h, sc->bvh, (int)std::min(hw, 32u));
+    sc->build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  }
   if (sc->bvh.max_depth * 3 + 4 > 96) {
     set_error("acceleration structure too deep (%d levels) for the traversal stack", sc->bvh.max_depth);
     return PT_ERR_INVALID;
@@ -177,6 +211,14 @@ int build_device_scene(pt_scene *sc) {
   D.tri_pos9 = nullptr;
   if (any_normal_map)
     if ((rc = upload(sc, h.pos, &D.tri_pos9))) return rc;
+  {
+    float *lut = nullptr;
+    CUDA_TRY(cudaMalloc(&lut, 256 * sizeof(float)));
+    sc->allocs.push_back(lut);
+    launch_init_srgb_lut(lut, nullptr);
+    CUDA_TRY(cudaGetLastError());
+    D.srgb_lut = lut;
+  }
   D.n_tris = nt;
   D.n_spheres = (uint32_t)spheres.size();
   D.n_lights = (uint32_t)lights.size();
@@ -222,6 +264,7 @@ int ensure_wave(pt_scene *sc, uint32_t n_paths) {
   }
   if ((rc = wave_alloc(sc, &W.hit, n_paths))) return rc;
   if ((rc = wave_alloc(sc, &W.radiance, n_paths))) return rc;
+  if ((rc = wave_alloc(sc, &W.hitq, n_paths))) return rc;
   if ((rc = wave_alloc(sc, &W.sh_o, shadow_cap))) return rc;
   if ((rc = wave_alloc(sc, &W.sh_d, shadow_cap))) return rc;
   if ((rc = wave_alloc(sc, &W.sh_c, shadow_cap))) return rc;
@@ -357,6 +400,23 @@ void pt_set_kernel_timing(int on) { g_kernel_timing = on; }
 int pt_scene_get_desc(const pt_scene *sc, pt_scene_desc *out) {
   if (!sc || !out) return PT_ERR_INVALID;
   sc->host.to_desc(*out);
+  return PT_OK;
+}
+
+int pt_set_accel_builder(int accel) {
+  if (accel < PT_ACCEL_SAH || accel > PT_ACCEL_AUTO) {
+    set_error("unknown acceleration-structure builder %d", accel);
+    return PT_ERR_INVALID;
+  }
+  g_accel = accel;
+  return PT_OK;
+}
+
+int pt_scene_accel_info(const pt_scene *sc, int *accel, double *build_ms, int *max_depth) {
+  if (!sc) return PT_ERR_INVALID;
+  if (accel) *accel = sc->accel;
+  if (build_ms) *build_ms = sc->build_ms;
+  if (max_depth) *max_depth = sc->bvh.max_depth;
   return PT_OK;
 }
 

@@ -63,4 +63,9 @@ struct Bvh4 {
 // conservatively so a box cull can never drop a primitive Möller–Trumbore would accept.
 void build_bvh4(const HostScene &s, Bvh4 &out, int threads);
 
+// GPU LBVH build (lbvh.cu) on the current CUDA device: Morton codes + radix sort + Karras hierarchy + bottom-up fit,
+// collapsed to the same 4-wide nodes.  *build_ms = device time of the build (CUDA events, upload excluded).
+// Returns PT_ERR_INVALID with *too_deep = 1 when the tree exceeds the traversal stack (caller falls back to SAH).
+int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_deep);
+
 }  // namespace ptb

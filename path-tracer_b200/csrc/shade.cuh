@@ -87,8 +87,8 @@ __device__ __forceinline__ MatSample material_sample(const DevScene &S, int mode
     if (m.roughness_tex >= 0) rough = (float)get_pixel(S, m.roughness_tex, u, v)[0] / 255.0f * m.roughness;
     if (m.albedo_tex >= 0) {
       const uint8_t *p = get_pixel(S, m.albedo_tex, u, v);
-      r.albedo = mul_el(mk3(powf((float)p[0] / 255.0f, 2.2f), powf((float)p[1] / 255.0f, 2.2f),
-                            powf((float)p[2] / 255.0f, 2.2f)), af);
+      // powf(texel / 255, 2.2) through a 256-entry table filled by k_init_srgb_lut with the very same expression
+      r.albedo = mul_el(mk3(__ldg(S.srgb_lut + p[0]), __ldg(S.srgb_lut + p[1]), __ldg(S.srgb_lut + p[2])), af);
     }
     if (m.opacity_tex >= 0) r.opacity = (float)get_pixel(S, m.opacity_tex, u, v)[0] / 255.0f * m.opacity;
     if (m.emissive_tex >= 0) {

@@ -7,7 +7,31 @@
 #pragma once
 #include "path.cuh"
 
+#ifndef PTB_STK64
+#define PTB_STK64 0
+#endif
+
 namespace ptb {
+
+// The lane's closest-hit traversal stack (local memory): (entry distance, child reference) pairs, kept outside the
+// traversal struct so that the scalar state stays in registers.  PTB_STK64 packs a pair into one 64-bit word
+// (one STL.64 / LDL.64 per push / pop instead of two 32-bit accesses).
+struct ClosestStack {
+#if PTB_STK64
+  uint2 e[PTB_STACK];
+  __device__ __forceinline__ void put(int i, float t, uint32_t r) { e[i] = make_uint2(__float_as_uint(t), r); }
+  __device__ __forceinline__ void get(int i, float &t, uint32_t &r) const {
+    const uint2 v = e[i];
+    t = __uint_as_float(v.x);
+    r = v.y;
+  }
+#else
+  float t_[PTB_STACK];
+  uint32_t r_[PTB_STACK];
+  __device__ __forceinline__ void put(int i, float t, uint32_t r) { t_[i] = t; r_[i] = r; }
+  __device__ __forceinline__ void get(int i, float &t, uint32_t &r) const { t = t_[i]; r = r_[i]; }
+#endif
+};
 
 struct ClosestTrav {
   Ray r;
@@ -49,17 +73,18 @@ struct ClosestTrav {
   __device__ __forceinline__ bool at_inner() const { return !(cur & 0x80000000u); }
   __device__ __forceinline__ bool at_leaf() const { return (cur & 0x80000000u) && cur != DONE; }
 
-  // stk_t / stk_r: the lane's traversal stack (PTB_STACK entries each), kept outside the struct so that the
-  // scalar state stays in registers.
-  __device__ __forceinline__ void pop(const float *stk_t, const uint32_t *stk_r) {
+  __device__ __forceinline__ void pop(const ClosestStack &stk) {
     while (sp > 0) {
       --sp;
-      if (stk_t[sp] <= t_prune) { cur = stk_r[sp]; return; }
+      float t;
+      uint32_t ref;
+      stk.get(sp, t, ref);
+      if (t <= t_prune) { cur = ref; return; }
     }
     cur = DONE;
   }
   // Precondition: at_inner().  Visits one node: cur becomes the nearest child hit, or the next stack entry.
-  __device__ __forceinline__ void node_step(const DevScene &S, const NodeOrder &no, float *stk_t, uint32_t *stk_r) {
+  __device__ __forceinline__ void node_step(const DevScene &S, const NodeOrder &no, ClosestStack &stk) {
     const NodeData nd = load_node(S.nodes, cur);
     const uint4 ch = nd.ch;
     float t0 = slab_fma(nd.lo_x.x, nd.lo_y.x, nd.lo_z.x, nd.hi_x.x, nd.hi_y.x, nd.hi_z.x, pre, no, t_prune, ch.x);
@@ -69,23 +94,23 @@ struct ClosestTrav {
     uint32_t r0 = ch.x, r1 = ch.y, r2 = ch.z, r3 = ch.w;
     PTB_CSWAP(t0, r0, t1, r1) PTB_CSWAP(t2, r2, t3, r3) PTB_CSWAP(t0, r0, t2, r2) PTB_CSWAP(t1, r1, t3, r3)
     PTB_CSWAP(t1, r1, t2, r2)
-    if (t3 < CUDART_INF_F) { stk_t[sp] = t3; stk_r[sp] = r3; ++sp; }
-    if (t2 < CUDART_INF_F) { stk_t[sp] = t2; stk_r[sp] = r2; ++sp; }
-    if (t1 < CUDART_INF_F) { stk_t[sp] = t1; stk_r[sp] = r1; ++sp; }
+    if (t3 < CUDART_INF_F) stk.put(sp++, t3, r3);
+    if (t2 < CUDART_INF_F) stk.put(sp++, t2, r2);
+    if (t1 < CUDART_INF_F) stk.put(sp++, t1, r1);
     if (t0 < CUDART_INF_F) cur = r0;
-    else pop(stk_t, stk_r);
+    else pop(stk);
   }
   // Precondition: at_leaf().  Tests ONE primitive of the leaf (uniform cost per step); a triangle leaf with more
   // primitives left stays current (first+1, count-1 == ref + 7).
-  __device__ __forceinline__ void leaf_step(const DevScene &S, const float *stk_t, const uint32_t *stk_r) {
+  __device__ __forceinline__ void leaf_step(const DevScene &S, const ClosestStack &stk) {
     if (cur & 0x40000000u) {
       leaf_closest(S, cur, r, t_lo, id_lo, st, t_prune, pre);
-      pop(stk_t, stk_r);
+      pop(stk);
       return;
     }
     leaf_closest(S, cur & ~7u, r, t_lo, id_lo, st, t_prune, pre);  // count-1 = 0: the first primitive only
     if (cur & 7u) cur += 7u;
-    else pop(stk_t, stk_r);
+    else pop(stk);
   }
 };
 

@@ -127,6 +127,16 @@ def test_png_roundtrip(tmp_path):
     assert np.array_equal(pt.read_png(ref, 3), np.asarray(Image.open(ref).convert("RGB")))
 
 
+def test_accel_builder_selection_host_only():
+    pt.set_accel_builder("lbvh")
+    pt.set_accel_builder("auto")
+    pt.set_accel_builder("sah")
+    with pytest.raises(pt.PtError):
+        pt.set_accel_builder(7)
+    sc = pt.Scene.synthetic("soup", 1000, seed=1, device=-1)
+    assert sc.accel_info()["accel"] == "sah"  # host-only scenes build no tree
+
+
 def test_synthetic_scenes_host_only():
     for recipe, n in (("console", 20000), ("foliage", 20000), ("city", 20000), ("soup", 5000)):
         sc = pt.Scene.synthetic(recipe, n, seed=3, device=-1)
