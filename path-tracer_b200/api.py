@@ -21,7 +21,7 @@ _LIB = None
 EXPORTS = ["pt_last_error", "pt_device_count", "pt_profile_default", "pt_profile_load_yaml", "pt_scene_load_isf",
            "pt_scene_create", "pt_scene_synthetic", "pt_scene_destroy", "pt_set_accel_builder", "pt_scene_accel_info", "pt_scene_upload", "pt_set_kernel_timing", "pt_scene_get_desc", "pt_scene_info",
            "pt_trace_closest", "pt_trace_closest_device", "pt_trace_transmittance", "pt_triangle_intersect",
-           "pt_trace_paths", "pt_render_accum_device", "pt_aov_name", "pt_debug_textures", "pt_render_progressive",
+           "pt_trace_paths", "pt_render_accum_device", "pt_aov_name", "pt_debug_textures", "pt_render_progressive", "pt_convert_gltf",
            "pt_tonemap_device", "pt_render", "pt_write_png", "pt_read_png", "pt_free"]
 
 
@@ -71,6 +71,7 @@ def lib():
         L.pt_read_png.argtypes = [C.c_char_p, u32, C.POINTER(u32), C.POINTER(u32), C.POINTER(C.POINTER(C.c_uint8))]
         L.pt_set_accel_builder.argtypes = [C.c_int]
         L.pt_scene_accel_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_int)]
+        L.pt_convert_gltf.argtypes = [C.c_char_p, C.c_char_p]
         L.pt_aov_name.argtypes = [C.c_int]
         L.pt_aov_name.restype = C.c_char_p
         L.pt_debug_textures.argtypes = [vp, u32, u32, vp, C.POINTER(u64)]
@@ -246,6 +247,11 @@ def triangle_intersect(rays, tris, device=0):
     out = np.zeros(len(rays), HIT_DTYPE)
     _check(lib().pt_triangle_intersect(None, device, rays.ctypes.data, tris.ctypes.data, len(rays), out.ctypes.data))
     return out
+
+
+def convert_gltf_to_isf(input_path, output_dir):
+    """scene::convert_gltf_to_isf (src/scene/gltf.rs:146-204): writes output_dir/scene.isf + texture PNGs."""
+    _check(lib().pt_convert_gltf(os.fsencode(input_path), os.fsencode(output_dir)))
 
 
 def load_internal(path, device=0):

@@ -4,8 +4,8 @@
 // --stats, --snapshot-every.  The SFML viewer (renderer/viewer.rs) needs a window + GL: unavailable on this box; -v
 // delivers the same feed headless instead: the running mean image is written over <OUTPUT> after every
 // --snapshot-every samples per pixel (default 16).  --debug-textures writes the seven AOV PNGs of
-// renderer/debug_renderer.rs into the working directory.  `convert` (glTF -> isf, scene/gltf.rs) is outside the
-// accelerated path.
+// renderer/debug_renderer.rs into the working directory.  `convert <INPUT> <OUTPUT>` (glTF -> isf, scene/gltf.rs) is
+// host code (gltf_convert.cpp).
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -21,7 +21,7 @@ static int usage(const char *msg) {
                "Path-trace awesome things\n\nUsage: path-tracer <COMMAND>\n\nCommands:\n"
                "  render   <INPUT> [-o, --output <OUTPUT>] [-q, --quiet] [-v, --viewer] [--debug-textures]\n"
                "           [-p, --profile <PROFILE>] [--seed <N>] [--stats <FILE>] [--snapshot-every <SPP>]\n"
-               "  convert  <INPUT> <OUTPUT>   (not part of the B200 build)\n");
+               "  convert  <INPUT> <OUTPUT>   glTF 2.0 (.gltf / .glb) -> <OUTPUT>/scene.isf + texture PNGs\n");
   return 2;
 }
 
@@ -32,9 +32,24 @@ int main(int argc, char **argv) {
     usage(nullptr);
     return 0;
   }
-  if (cmd == "convert") {
-    std::fprintf(stderr, "convert: the glTF -> isf converter is not part of the B200 render path\n");
-    return 2;
+  if (cmd == "convert") {  // config/mod.rs:44-52 + main.rs:54-57
+    std::vector<std::string> pos;
+    for (int i = 2; i < argc; ++i) {
+      std::string a = argv[i];
+      if (a == "-h" || a == "--help") {
+        usage(nullptr);
+        return 0;
+      }
+      if (!a.empty() && a[0] == '-') return usage(("unexpected argument '" + a + "'").c_str());
+      pos.push_back(a);
+    }
+    if (pos.size() < 2) return usage("the following required arguments were not provided: <INPUT> <OUTPUT>");
+    if (pos.size() > 2) return usage(("unexpected argument '" + pos[2] + "'").c_str());
+    if (pt_convert_gltf(pos[0].c_str(), pos[1].c_str()) != PT_OK) {
+      std::fprintf(stderr, "%s\n", pt_last_error());
+      return 2;
+    }
+    return 0;
   }
   if (cmd != "render") return usage(("unrecognized subcommand '" + cmd + "'").c_str());
 

@@ -91,7 +91,6 @@ struct WaveState {
   float4 *thr[2];     // xyz throughput
   float4 *hit;        // (dist, u, v, HitRec.idx bits; idx < 0 = miss)
   float4 *radiance;   // per slot: xyz sum of this path's contributions (zeroed by raygen, atomically added to)
-  uint32_t *hitq;     // queue positions whose ray hit a surface, appended by k_extend: the work list of k_shade
   // shadow queue (one entry per light per shaded hit with a non-zero unshadowed contribution)
   float4 *sh_o;       // xyz origin, w = point-light distance (or -1 for directional)
   float4 *sh_d;       // xyz direction, w = slot
@@ -113,8 +112,6 @@ enum {
   CTR_SHADOW1 = 3,  // shadow rays emitted with buffer 1  }
   CTR_WORK_EXTEND = 4,  // persistent work-fetch cursors
   CTR_WORK_SHADOW = 5,
-  CTR_HITS0 = 6,    // entries of hitq written by k_extend(bounce) for bounce even / odd: k_extend(b) fills
-  CTR_HITS1 = 7,    // CTR_HITS(b & 1) and clears the other one, which k_shade(b - 1) has finished reading
   CTR_STAT_EXTEND = 8,  // 64-bit statistics start here (pairs)
   CTR_STAT_SHADOW = 10,
   CTR_STAT_RECAST = 12,
@@ -122,7 +119,6 @@ enum {
 };
 #define CTR_QUEUE(b) (2u * (b))
 #define CTR_SHADOW(b) (2u * (b) + 1u)
-#define CTR_HITS(b) (6u + (b))
 
 struct WaveParams {
   uint32_t width, height;

@@ -12,7 +12,12 @@ int scene_from_host(HostScene &&host, int device, pt_scene **out);
 int load_isf_file(const char *path, HostScene &out);
 // png.cpp
 int png_read(const char *path, uint32_t channels_out, uint32_t *w, uint32_t *h, std::vector<uint8_t> &data);
+int png_decode(const uint8_t *bytes, size_t size, const char *name, uint32_t channels_out, uint32_t *w, uint32_t *h,
+               std::vector<uint8_t> &data);
 int png_write(const char *path, const uint8_t *rgb8, uint32_t w, uint32_t h);
+int png_write_ch(const char *path, const uint8_t *pixels, uint32_t w, uint32_t h, uint32_t channels);
+// gltf_convert.cpp: scene::convert_gltf_to_isf (src/scene/gltf.rs:146-204)
+int convert_gltf_to_isf(const char *input, const char *output_dir);
 // synth.cpp
 int make_synthetic(const char *recipe, uint64_t n_tris, uint64_t seed, HostScene &out);
 }  // namespace ptb

@@ -19,16 +19,16 @@
 #define PTB_SHADE_MINB 6
 #endif
 #ifndef PTB_SHADOW_MINB
-#define PTB_SHADOW_MINB 1
+#define PTB_SHADOW_MINB 6  // 72 registers, 6 CTAs per SM: k_shadow -2 % (console) ... -18 % (foliage) against 90 registers
 #endif
-// 1: k_extend finishes missed paths itself (background term) and hands k_shade a compact list of the queue positions
-// that hit something, so that every lane of k_shade has a surface to shade (mod.rs:184-186 leaves the loop on a miss).
-#ifndef PTB_HITQ
-#define PTB_HITQ 0
+// 1: wave-state loads/stores use the streaming (evict-first) cache policy so that they do not displace BVH nodes
+// (measured: k_shade -10 %, k_extend -2 % on the console workload).
+// 1: k_shade packs the rays that hit a surface onto its lanes (see k_shade).
+#ifndef PTB_SHADE_COMPACT
+#define PTB_SHADE_COMPACT 1
 #endif
-// 1: wave-state loads/stores use the streaming (evict-first) cache policy so that they do not displace BVH nodes.
 #ifndef PTB_STREAM
-#define PTB_STREAM 0
+#define PTB_STREAM 1
 #endif
 
 namespace ptb {
@@ -106,7 +106,6 @@ __global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene
   if (slot == 0) {
     W.counters[CTR_QUEUE(0)] = P.n_paths;
     W.counters[CTR_WORK_EXTEND] = 0;
-    W.counters[CTR_HITS(0)] = 0;
   }
   if (slot >= P.n_paths) return;
   Ray r = generate_ray(S, P, make_key(P, slot));
@@ -175,13 +174,8 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
     W.counters[CTR_QUEUE(outb)] = 0;  // the queues k_shade(bounce) appends to
     W.counters[CTR_SHADOW(outb)] = 0;
     W.counters[CTR_WORK_SHADOW] = 0;
-    W.counters[CTR_HITS(outb)] = 0;
     stat_add(W.counters, CTR_STAT_EXTEND, n);
   }
-#if PTB_HITQ
-  const V3 bg = mk3(S.background[0], S.background[1], S.background[2]);
-  const bool bg_lit = bg.x != 0.0f || bg.y != 0.0f || bg.z != 0.0f;
-#endif
   constexpr uint32_t NONE = 0xFFFFFFFFu;
   uint32_t recasts = 0;
   ClosestTrav tv;
@@ -207,10 +201,6 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
     if (__ballot_sync(0xffffffffu, q != NONE) == 0) break;
     for (;;) {
       const bool has = q != NONE;
-#if PTB_HITQ
-      bool fin_hit = false;
-      uint32_t q_fin = 0;
-#endif
       if (has && tv.at_inner()) tv.node_step(S, no, stk);
       const bool leaf = has && tv.at_leaf();
       const uint32_t m_leaf = __ballot_sync(0xffffffffu, leaf);
@@ -234,32 +224,10 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
           }
         }
         if (done) {
-#if PTB_HITQ
-          if (recorded) {
-            fin_hit = true;
-            q_fin = q;
-          } else if (bg_lit) {  // miss: color + throughput * background, and the path ends (mod.rs:184-186)
-            const float4 t4 = W.thr[in][q];
-            add_radiance(W.radiance, slot, mul_el(mk3(t4.x, t4.y, t4.z), bg));
-          }
-#else
           if (!recorded) st_wave(&W.hit[q], make_float4(0.f, 0.f, 0.f, __int_as_float(-1)));  // miss
-#endif
           q = NONE;
         }
       }
-#if PTB_HITQ
-      {  // warp-aggregated append of the rays that ended on a surface in this iteration
-        const uint32_t mh = __ballot_sync(0xffffffffu, fin_hit);
-        if (mh) {
-          const int leader = __ffs(mh) - 1;
-          uint32_t base = 0;
-          if ((int)lane_id() == leader) base = atomicAdd(&W.counters[CTR_HITS(in)], (uint32_t)__popc(mh));
-          base = __shfl_sync(0xffffffffu, base, leader);
-          if (fin_hit) W.hitq[base + (uint32_t)__popc(mh & lanemask_lt())] = q_fin;
-        }
-      }
-#endif
       const uint32_t busy = __ballot_sync(0xffffffffu, q != NONE);
       if (busy == 0 || (!drained && __popc(busy) < REFILL_THRESHOLD)) break;
     }
@@ -291,19 +259,43 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
                                                                const __grid_constant__ WaveParams P, WaveState W,
                                                                uint32_t bounce) {
   const uint32_t in = bounce & 1u, outb = in ^ 1u;
-#if PTB_HITQ
-  const uint32_t n = W.counters[CTR_HITS(in)];
-#else
   const uint32_t n = W.counters[CTR_QUEUE(in)];
-#endif
   if (blockIdx.x == 0 && threadIdx.x == 0) W.counters[CTR_WORK_EXTEND] = 0;
   uint32_t *pair = &W.counters[CTR_QUEUE(outb)];
   const uint32_t warps = gridDim.x * (blockDim.x >> 5), warp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  for (uint32_t base = warp * 32u; base < n; base += warps * 32u) {
-#if PTB_HITQ
-    const bool active = base + lane_id() < n;
-    const uint32_t q = active ? W.hitq[base + lane_id()] : 0u;
+#if PTB_SHADE_COMPACT
+  // A warp takes 64 consecutive queue positions, finishes the missed ones on the spot (mod.rs:184-186: background term,
+  // the path ends) and packs the hits, in queue order, onto its lanes: after the first bounce about half of the rays
+  // miss, and the ~1200-instruction surface shader below would otherwise run with half of its lanes idle.  Keeping
+  // the queue order keeps neighbouring paths together, which the next extend / shadow launch relies on.
+  const V3 bg = mk3(S.background[0], S.background[1], S.background[2]);
+  const bool bg_lit = bg.x != 0.0f || bg.y != 0.0f || bg.z != 0.0f;
+  for (uint32_t base = warp * 64u; base < n; base += warps * 64u) {
+    bool hit_a = false, hit_b = false;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const uint32_t qq = base + 32u * half + lane_id();
+      bool h = false;
+      if (qq < n) {
+        h = __float_as_int(W.hit[qq].w) >= 0;
+        if (!h && bg_lit) {
+          const float4 t4 = ld_wave(&W.thr[in][qq]);
+          const uint32_t sl = (uint32_t)__float_as_int(W.ray_d[in][qq].w);
+          add_radiance(W.radiance, sl, mul_el(mk3(t4.x, t4.y, t4.z), bg));
+        }
+      }
+      if (half == 0) hit_a = h; else hit_b = h;
+    }
+    const uint32_t m_a = __ballot_sync(0xffffffffu, hit_a), m_b = __ballot_sync(0xffffffffu, hit_b);
+    const uint32_t n_a = (uint32_t)__popc(m_a), n_hit = n_a + (uint32_t)__popc(m_b);
+    for (uint32_t done = 0; done < n_hit; done += 32u) {
+    const uint32_t k = done + lane_id();
+    const bool active = k < n_hit;
+    uint32_t q = 0;
+    if (active) q = k < n_a ? base + __fns(m_a, 0, (int)k + 1) : base + 32u + __fns(m_b, 0, (int)(k - n_a) + 1);
 #else
+  for (uint32_t base = warp * 32u; base < n; base += warps * 32u) {
+    {
     const uint32_t q = base + lane_id();
     const bool active = q < n;
 #endif
@@ -356,6 +348,7 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
       st_wave(&W.ray_o[outb][pp], make_float4(next.o.x, next.o.y, next.o.z, 0.f));
       st_wave(&W.ray_d[outb][pp], make_float4(next.d.x, next.d.y, next.d.z, __int_as_float((int)slot)));
       st_wave(&W.thr[outb][pp], make_float4(thr.x, thr.y, thr.z, 0.f));
+    }
     }
   }
 }

@@ -33,6 +33,19 @@ int png_read(const char *path, uint32_t channels_out, uint32_t *w_out, uint32_t 
   size_t n;
   while ((n = std::fread(buf, 1, sizeof buf, f)) > 0) file.insert(file.end(), buf, buf + n);
   std::fclose(f);
+  return png_decode(file.data(), file.size(), path, channels_out, w_out, h_out, out);
+}
+
+// channels_out: 1 (into_luma8), 3 (into_rgb8) or 4 (into_rgba8; alpha 255 when the file has none).
+int png_decode(const uint8_t *bytes, size_t size, const char *path, uint32_t channels_out, uint32_t *w_out,
+               uint32_t *h_out, std::vector<uint8_t> &out) {
+  struct View {  // keeps the body below identical for file and in-memory sources
+    const uint8_t *p;
+    size_t n;
+    size_t size() const { return n; }
+    const uint8_t *data() const { return p; }
+    const uint8_t &operator[](size_t i) const { return p[i]; }
+  } file{bytes, size};
   static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', 0x0D, 0x0A, 0x1A, 0x0A};
   if (file.size() < 8 || std::memcmp(file.data(), sig, 8) != 0) {
     set_error("%s: not a PNG file", path);
@@ -133,6 +146,9 @@ int png_read(const char *path, uint32_t channels_out, uint32_t *w_out, uint32_t 
       uint8_t *o = &out[((size_t)y * w + x) * channels_out];
       if (channels_out == 3) {
         o[0] = r; o[1] = g; o[2] = b;
+      } else if (channels_out == 4) {
+        o[0] = r; o[1] = g; o[2] = b;
+        o[3] = ctype == 6 ? s[3] : ctype == 4 ? s[1] : 255;
       } else {
         // image crate rgb_to_luma for u8: (2126 r + 7152 g + 722 b) / 10000; gray sources pass through
         o[0] = gray_src ? r : (uint8_t)((2126u * r + 7152u * g + 722u * b) / 10000u);
@@ -144,11 +160,15 @@ int png_read(const char *path, uint32_t channels_out, uint32_t *w_out, uint32_t 
   return PT_OK;
 }
 
-int png_write(const char *path, const uint8_t *rgb8, uint32_t w, uint32_t h) {
-  std::vector<uint8_t> raw(((size_t)w * 3 + 1) * h);
+int png_write(const char *path, const uint8_t *rgb8, uint32_t w, uint32_t h) { return png_write_ch(path, rgb8, w, h, 3); }
+
+// 8-bit RGB (channels 3) or grayscale (channels 1) PNG.
+int png_write_ch(const char *path, const uint8_t *rgb8, uint32_t w, uint32_t h, uint32_t channels) {
+  const size_t row = (size_t)w * channels;
+  std::vector<uint8_t> raw((row + 1) * h);
   for (uint32_t y = 0; y < h; ++y) {
-    raw[((size_t)w * 3 + 1) * y] = 0;
-    std::memcpy(&raw[((size_t)w * 3 + 1) * y + 1], rgb8 + (size_t)y * w * 3, (size_t)w * 3);
+    raw[(row + 1) * y] = 0;
+    std::memcpy(&raw[(row + 1) * y + 1], rgb8 + (size_t)y * row, row);
   }
   uLongf clen = compressBound((uLong)raw.size());
   std::vector<uint8_t> comp(clen);
@@ -174,7 +194,8 @@ int png_write(const char *path, const uint8_t *rgb8, uint32_t w, uint32_t h) {
   static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', 0x0D, 0x0A, 0x1A, 0x0A};
   std::fwrite(sig, 1, 8, f);
   uint8_t ihdr[13] = {(uint8_t)(w >> 24), (uint8_t)(w >> 16), (uint8_t)(w >> 8), (uint8_t)w,
-                      (uint8_t)(h >> 24), (uint8_t)(h >> 16), (uint8_t)(h >> 8), (uint8_t)h, 8, 2, 0, 0, 0};
+                      (uint8_t)(h >> 24), (uint8_t)(h >> 16), (uint8_t)(h >> 8), (uint8_t)h, 8,
+                      (uint8_t)(channels == 1 ? 0 : 2), 0, 0, 0};
   chunk("IHDR", ihdr, 13);
   chunk("IDAT", comp.data(), (uint32_t)clen);
   chunk("IEND", nullptr, 0);

@@ -264,7 +264,6 @@ int ensure_wave(pt_scene *sc, uint32_t n_paths) {
   }
   if ((rc = wave_alloc(sc, &W.hit, n_paths))) return rc;
   if ((rc = wave_alloc(sc, &W.radiance, n_paths))) return rc;
-  if ((rc = wave_alloc(sc, &W.hitq, n_paths))) return rc;
   if ((rc = wave_alloc(sc, &W.sh_o, shadow_cap))) return rc;
   if ((rc = wave_alloc(sc, &W.sh_d, shadow_cap))) return rc;
   if ((rc = wave_alloc(sc, &W.sh_c, shadow_cap))) return rc;
