@@ -273,6 +273,10 @@ def run_ours(args, wl):
     peak, peak_src = peaks()
     canon = canonical_counts(args.workload)
     roof = None
+    props = torch.cuda.get_device_properties(local)
+    sm_count = props.multi_processor_count
+    sm_mhz = clocks.get("sm_max_mhz") or 1965.0
+    fp32_peak = sm_count * 128 * sm_mhz * 1e6 / 1e12  # T f32 instructions / s (x2 flops only if every op were an FMA)
     if canon:
         b_ext = ray_bytes(canon["n_node_closest"], canon["n_tri_closest"])
         b_sh = ray_bytes(canon["n_node_any"], canon["n_tri_any"])
@@ -293,6 +297,15 @@ def run_ours(args, wl):
                 "algorithmic_bytes_per_launch": ext_bytes / max(1, st["extend_launches"]),
                 "kernel_ms_per_step": {"extend": st["ms_extend"], "shade": st["ms_shade"], "shadow": st["ms_shadow"],
                                        "other": st["ms_other"], "total": st["ms_total"]},
+                # second roofline of SURVEY 8(d): canonical f32 operations per ray (30 per node visit, 52 per triangle test)
+                # against the FP32 issue peak SMs x 128 lanes x max SM clock; the scene being L2-resident or not, this is
+                # the bound the kernel is actually nearest to (see profiles/: issue slots and L1 wavefronts co-limit)
+                "fp32": {"flops_per_ray": canon.get("flops_per_ray_closest"),
+                         "achieved_tflops": (canon.get("flops_per_ray_closest", 0.0) * st["extend_rays"] / (st["ms_extend"] * 1e-3) / 1e12)
+                         if st["ms_extend"] > 0 else None,
+                         "peak_tinstr": fp32_peak, "sm_count": sm_count, "sm_max_mhz": sm_mhz,
+                         "frac": (canon.get("flops_per_ray_closest", 0.0) * st["extend_rays"] / (st["ms_extend"] * 1e-3) / 1e12 / fp32_peak)
+                         if st["ms_extend"] > 0 and fp32_peak else None},
                 "shadow_kernel": {"bytes_per_ray": b_sh,
                                   "achieved": b_sh * st["shadow_rays"] / (st["ms_shadow"] * 1e-3) / 1e9 if st["ms_shadow"] > 0 else None}}
     launches = (st["kernel_launches"] + 1) * args.steps  # + tonemap

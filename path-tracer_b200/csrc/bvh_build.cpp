@@ -194,8 +194,8 @@ void build_bvh4(const HostScene &s, Bvh4 &out, int threads) {
   if (rn.right & LEAF2) {  // whole scene in one leaf: wrap it in a single node
     Bvh4Node nd{};
     for (int k = 0; k < 4; ++k) {
-      nd.lo_x[k] = nd.lo_y[k] = nd.lo_z[k] = INFINITY;
-      nd.hi_x[k] = nd.hi_y[k] = nd.hi_z[k] = -INFINITY;
+      nd.lo_x[k] = nd.lo_y[k] = nd.lo_z[k] = NAN;  // empty slot: NaN planes fail every slab test (isect.cuh slab_fma)
+      nd.hi_x[k] = nd.hi_y[k] = nd.hi_z[k] = NAN;
       nd.child[k] = BVH_EMPTY;
     }
     Box b = inflate(rn.box);
@@ -234,8 +234,8 @@ void build_bvh4(const HostScene &s, Bvh4 &out, int threads) {
     }
     Bvh4Node nd{};
     for (int k = 0; k < 4; ++k) {
-      nd.lo_x[k] = nd.lo_y[k] = nd.lo_z[k] = INFINITY;
-      nd.hi_x[k] = nd.hi_y[k] = nd.hi_z[k] = -INFINITY;
+      nd.lo_x[k] = nd.lo_y[k] = nd.lo_z[k] = NAN;  // empty slot: NaN planes fail every slab test (isect.cuh slab_fma)
+      nd.hi_x[k] = nd.hi_y[k] = nd.hi_z[k] = NAN;
       nd.child[k] = BVH_EMPTY;
     }
     for (int k = 0; k < nk; ++k) {

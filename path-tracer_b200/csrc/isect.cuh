@@ -153,7 +153,10 @@ __device__ __forceinline__ float slab_fma(float lox, float loy, float loz, float
   float t0z = __fmaf_rn(loz, p.iz, n.oiz), t1z = __fmaf_rn(hiz, p.iz, n.oiz);
   float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.0f));
   float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
-  bool hit = child != 0xFFFFFFFFu && tn <= __fmaf_rn(tf, 1.000002f, 1e-7f) && tn <= t_max;
+  // Empty child slots carry NaN planes (bvh_build.cpp, lbvh.cu): every t is NaN, fminf/fmaxf then leave tf = NaN and the
+  // first comparison is false, so no test of `child` against the empty marker is needed.
+  (void)child;
+  bool hit = tn <= __fmaf_rn(tf, 1.000002f, 1e-7f) && tn <= t_max;
   return hit ? tn : CUDART_INF_F;
 }
 

@@ -23,10 +23,6 @@
 #endif
 // 1: wave-state loads/stores use the streaming (evict-first) cache policy so that they do not displace BVH nodes
 // (measured: k_shade -10 %, k_extend -2 % on the console workload).
-// 1: k_shade packs the rays that hit a surface onto its lanes (see k_shade).
-#ifndef PTB_SHADE_COMPACT
-#define PTB_SHADE_COMPACT 1
-#endif
 #ifndef PTB_STREAM
 #define PTB_STREAM 1
 #endif
@@ -115,8 +111,82 @@ __global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene
   W.radiance[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
-// Lane-level work fetch: every idle lane of the warp takes the next queue position (one atomic per refill).
-// `drained` becomes true (warp-uniformly) once the cursor has passed n.
+// Lane-level work fetch: every idle lane of the warp takes the next queue position.  A warp reserves queue positions
+// CHUNK at a time and always has ONE reservation in flight: the atomic that reserves the following chunk is issued
+// when the current chunk is opened and its result is only read when that chunk runs out, so its round trip to L2
+// (the largest single stall of k_shadow and 5 % of k_extend's in profiles/r01) overlaps with traversal work; as soon
+// as the following chunk's base has arrived, the ray records it covers are prefetched into L2.
+// `drained` becomes true (warp-uniformly) once the reservations have passed n.
+// Measured (console / city / foliage, profiles/r02): k_shadow -26 % / +5 % / +1 %, k_extend +19 % / +6 % / +7 % (its
+// 72-register budget spills in the loop), so the shadow kernel fetches ahead and the extend kernel does not.
+#ifndef PTB_FETCH_AHEAD_EXTEND
+#define PTB_FETCH_AHEAD_EXTEND 0
+#endif
+#ifndef PTB_FETCH_AHEAD_SHADOW
+#define PTB_FETCH_AHEAD_SHADOW 1
+#endif
+#ifndef PTB_PF_L1
+#define PTB_PF_L1 0
+#endif
+__device__ __forceinline__ void prefetch_l2(const void *p) {
+#if PTB_PF_L1
+  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+#else
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#endif
+}
+
+struct WorkFetch {
+  static constexpr uint32_t CHUNK = 64u;  // queue positions per reservation (two refills of a whole warp)
+  uint32_t next, avail;  // unconsumed part of the current reservation (warp-uniform)
+  uint32_t ahead;        // lane 0: first position of the reservation requested last
+  bool ahead_fresh;      // the records of the `ahead` reservation have not been prefetched yet
+  bool drained;
+
+  __device__ __forceinline__ void init(uint32_t *cursor) {
+    next = avail = 0;
+    ahead = 0;
+    drained = false;
+    ahead_fresh = true;
+    if (lane_id() == 0) ahead = atomicAdd(cursor, CHUNK);
+  }
+  // pf(position) prefetches the records of one queue position.
+  template <typename Prefetch>
+  __device__ __forceinline__ uint32_t refill(uint32_t *cursor, bool idle, uint32_t n, Prefetch pf) {
+    const uint32_t m = __ballot_sync(0xffffffffu, idle);
+    uint32_t idx = 0xFFFFFFFFu;
+    if (m && !drained) {
+      const uint32_t cnt = (uint32_t)__popc(m), rank = (uint32_t)__popc(m & lanemask_lt());
+      if (cnt < avail) {
+        if (idle) idx = next + rank;
+        next += cnt;
+        avail -= cnt;
+        if (next >= n) drained = true;  // every later position, reserved or not, is past the queue
+        else if (ahead_fresh) {  // the reservation requested at the last switch has arrived by now: warm its records
+          const uint32_t nb = __shfl_sync(0xffffffffu, ahead, 0);
+#pragma unroll
+          for (uint32_t k = 0; k < CHUNK; k += 32u)
+            if (nb + k + lane_id() < n) pf(nb + k + lane_id());
+          ahead_fresh = false;
+        }
+      } else {  // the current reservation runs out: continue in the one requested earlier, request another
+        const uint32_t nb = __shfl_sync(0xffffffffu, ahead, 0);
+        if (idle) idx = rank < avail ? next + rank : nb + (rank - avail);
+        next = nb + (cnt - avail);
+        avail = CHUNK - (cnt - avail);
+        if (nb >= n) {
+          drained = true;
+        } else {
+          if (lane_id() == 0) ahead = atomicAdd(cursor, CHUNK);
+          ahead_fresh = true;
+        }
+      }
+    }
+    return idx < n ? idx : 0xFFFFFFFFu;
+  }
+};
+
+// Synchronous variant: one atomic per refill, its result needed at once.
 __device__ __forceinline__ uint32_t refill(uint32_t *cursor, bool idle, uint32_t n, bool &drained) {
   uint32_t m = __ballot_sync(0xffffffffu, idle);
   uint32_t idx = 0xFFFFFFFFu;
@@ -182,10 +252,25 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
   NodeOrder no{};
   ClosestStack stk;
   uint32_t q = NONE, slot = 0, alpha_j = 0;
-  bool drained = false, recorded = false;
+  bool recorded = false;
   tv.cur = ClosestTrav::DONE;
+#if PTB_FETCH_AHEAD_EXTEND
+  WorkFetch wf;
+  wf.init(&W.counters[CTR_WORK_EXTEND]);
+  const float4 *pf_o = W.ray_o[in], *pf_d = W.ray_d[in];
+#define drained wf.drained
+#else
+  bool drained = false;
+#endif
   for (;;) {
+#if PTB_FETCH_AHEAD_EXTEND
+    uint32_t nq = wf.refill(&W.counters[CTR_WORK_EXTEND], q == NONE, n, [&](uint32_t p) {
+      prefetch_l2(pf_o + p);
+      prefetch_l2(pf_d + p);
+    });
+#else
     uint32_t nq = refill(&W.counters[CTR_WORK_EXTEND], q == NONE, n, drained);
+#endif
     if (nq != NONE) {
       q = nq;
       float4 o4 = ld_wave(&W.ray_o[in][q]), d4 = ld_wave(&W.ray_d[in][q]);
@@ -232,6 +317,7 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
       if (busy == 0 || (!drained && __popc(busy) < REFILL_THRESHOLD)) break;
     }
   }
+#undef drained
   recasts = __reduce_add_sync(0xffffffffu, recasts);
   if (lane_id() == 0 && recasts) stat_add(W.counters, CTR_STAT_RECAST, recasts);
 }
@@ -263,42 +349,9 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
   if (blockIdx.x == 0 && threadIdx.x == 0) W.counters[CTR_WORK_EXTEND] = 0;
   uint32_t *pair = &W.counters[CTR_QUEUE(outb)];
   const uint32_t warps = gridDim.x * (blockDim.x >> 5), warp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-#if PTB_SHADE_COMPACT
-  // A warp takes 64 consecutive queue positions, finishes the missed ones on the spot (mod.rs:184-186: background term,
-  // the path ends) and packs the hits, in queue order, onto its lanes: after the first bounce about half of the rays
-  // miss, and the ~1200-instruction surface shader below would otherwise run with half of its lanes idle.  Keeping
-  // the queue order keeps neighbouring paths together, which the next extend / shadow launch relies on.
-  const V3 bg = mk3(S.background[0], S.background[1], S.background[2]);
-  const bool bg_lit = bg.x != 0.0f || bg.y != 0.0f || bg.z != 0.0f;
-  for (uint32_t base = warp * 64u; base < n; base += warps * 64u) {
-    bool hit_a = false, hit_b = false;
-#pragma unroll
-    for (int half = 0; half < 2; ++half) {
-      const uint32_t qq = base + 32u * half + lane_id();
-      bool h = false;
-      if (qq < n) {
-        h = __float_as_int(W.hit[qq].w) >= 0;
-        if (!h && bg_lit) {
-          const float4 t4 = ld_wave(&W.thr[in][qq]);
-          const uint32_t sl = (uint32_t)__float_as_int(W.ray_d[in][qq].w);
-          add_radiance(W.radiance, sl, mul_el(mk3(t4.x, t4.y, t4.z), bg));
-        }
-      }
-      if (half == 0) hit_a = h; else hit_b = h;
-    }
-    const uint32_t m_a = __ballot_sync(0xffffffffu, hit_a), m_b = __ballot_sync(0xffffffffu, hit_b);
-    const uint32_t n_a = (uint32_t)__popc(m_a), n_hit = n_a + (uint32_t)__popc(m_b);
-    for (uint32_t done = 0; done < n_hit; done += 32u) {
-    const uint32_t k = done + lane_id();
-    const bool active = k < n_hit;
-    uint32_t q = 0;
-    if (active) q = k < n_a ? base + __fns(m_a, 0, (int)k + 1) : base + 32u + __fns(m_b, 0, (int)(k - n_a) + 1);
-#else
   for (uint32_t base = warp * 32u; base < n; base += warps * 32u) {
-    {
     const uint32_t q = base + lane_id();
     const bool active = q < n;
-#endif
     Ray r{};
     V3 thr{}, rad = mk3(0.f, 0.f, 0.f);
     ShadeCtx ctx{};
@@ -348,7 +401,6 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
       st_wave(&W.ray_o[outb][pp], make_float4(next.o.x, next.o.y, next.o.z, 0.f));
       st_wave(&W.ray_d[outb][pp], make_float4(next.d.x, next.d.y, next.d.z, __int_as_float((int)slot)));
       st_wave(&W.thr[outb][pp], make_float4(thr.x, thr.y, thr.z, 0.f));
-    }
     }
   }
 }
@@ -490,10 +542,25 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
   uint32_t stk[PTB_STACK];
   uint32_t q = NONE, slot = 0;
   V3 c{};
-  bool drained = false;
   tv.cur = ShadowTrav::DONE;
+#if PTB_FETCH_AHEAD_SHADOW
+  WorkFetch wf;
+  wf.init(&W.counters[CTR_WORK_SHADOW]);
+#define drained wf.drained
+#else
+  bool drained = false;
+#endif
   for (;;) {
+#if PTB_FETCH_AHEAD_SHADOW
+    uint32_t nq = wf.refill(&W.counters[CTR_WORK_SHADOW], q == NONE, n, [&](uint32_t p) {
+      prefetch_l2(W.sh_o + p);
+      prefetch_l2(W.sh_d + p);
+      prefetch_l2(W.sh_c + p);
+      prefetch_l2(W.sh_p + p);
+    });
+#else
     uint32_t nq = refill(&W.counters[CTR_WORK_SHADOW], q == NONE, n, drained);
+#endif
     if (nq != NONE) {
       q = nq;
       float4 o4 = ld_wave(&W.sh_o[q]), d4 = ld_wave(&W.sh_d[q]), c4 = ld_wave(&W.sh_c[q]), p4 = ld_wave(&W.sh_p[q]);
@@ -527,6 +594,8 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
     }
   }
 }
+
+#undef drained
 
 // resolve: *pixel += color (mod.rs:130) for the wave's samples of each pixel, in sample order.
 __global__ void __launch_bounds__(256) k_resolve(const __grid_constant__ WaveParams P, WaveState W, float *__restrict__ accum) {

@@ -430,8 +430,8 @@ __global__ void __launch_bounds__(128) k_collapse(const CollapseArgs A, const ui
   }
   Bvh4Node nd;
   for (int k = 0; k < 4; ++k) {
-    nd.lo_x[k] = nd.lo_y[k] = nd.lo_z[k] = CUDART_INF_F;
-    nd.hi_x[k] = nd.hi_y[k] = nd.hi_z[k] = -CUDART_INF_F;
+    nd.lo_x[k] = nd.lo_y[k] = nd.lo_z[k] = CUDART_NAN_F;  // empty slot: NaN planes fail every slab test
+    nd.hi_x[k] = nd.hi_y[k] = nd.hi_z[k] = CUDART_NAN_F;
     nd.child[k] = BVH_EMPTY;
     nd.pad[k] = 0;
   }

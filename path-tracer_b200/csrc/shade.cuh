@@ -49,15 +49,28 @@ __device__ __forceinline__ float rng_alpha(const RngKey &k, uint32_t bounce, uin
 
 // ---------------- textures / materials ----------------
 // material.rs:115-130: nearest texel, repeat, truncation toward zero (Rust `as i64` saturates).
+// `(c as i64).rem_euclid(n)` (material.rs:121-128): `as i64` truncates toward zero, saturates and maps NaN to 0.
+// Coordinates that fit 32 bits (all but absurd uvs) take a 32-bit remainder; the 64-bit one is kept out of line.
+__device__ __noinline__ uint32_t texel_index_wide(float c, uint32_t n) {
+  long long i = __float2ll_rz(c);  // saturates like `as i64`
+  long long r = i % (long long)n;
+  if (r < 0) r += (long long)n;
+  return (uint32_t)r;
+}
+__device__ __forceinline__ uint32_t texel_index(float c, uint32_t n) {
+  if (c != c) return 0u;
+  if (fabsf(c) < 2147483520.0f) {
+    const int i = __float2int_rz(c);
+    int r = i % (int)n;  // n < 2^31 (a texture side)
+    if (r < 0) r += (int)n;
+    return (uint32_t)r;
+  }
+  return texel_index_wide(c, n);
+}
 __device__ __forceinline__ const uint8_t *get_pixel(const DevScene &S, int tex, float u, float v) {
   const DevTexture t = S.textures[tex];
   float cx = u * (float)t.width, cy = v * (float)t.height;
-  long long ix = (cx != cx) ? 0 : __float2ll_rz(cx);  // __float2ll_rz saturates like `as i64`
-  long long iy = (cy != cy) ? 0 : __float2ll_rz(cy);
-  long long w = t.width, h = t.height;
-  long long x = ix % w, y = iy % h;
-  if (x < 0) x += w;
-  if (y < 0) y += h;
+  const uint32_t x = texel_index(cx, t.width), y = texel_index(cy, t.height);
   return S.texels + t.offset + ((size_t)y * t.width + (size_t)x) * t.channels;
 }
 
