@@ -112,13 +112,14 @@ __global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene
 }
 
 // Lane-level work fetch: every idle lane of the warp takes the next queue position.  A warp reserves queue positions
-// CHUNK at a time and always has ONE reservation in flight: the atomic that reserves the following chunk is issued
+// `chunk` at a time and always has ONE reservation in flight: the atomic that reserves the following chunk is issued
 // when the current chunk is opened and its result is only read when that chunk runs out, so its round trip to L2
 // (the largest single stall of k_shadow and 5 % of k_extend's in profiles/r01) overlaps with traversal work; as soon
 // as the following chunk's base has arrived, the ray records it covers are prefetched into L2.
 // `drained` becomes true (warp-uniformly) once the reservations have passed n.
-// Measured (console / city / foliage, profiles/r02): k_shadow -26 % / +5 % / +1 %, k_extend +19 % / +6 % / +7 % (its
-// 72-register budget spills in the loop), so the shadow kernel fetches ahead and the extend kernel does not.
+// Measured (console / city / foliage, profiles/r02): k_shadow -26 % / +5 % / +1 %, k_extend +19 % / +6 % / +7 % (with or
+// without spills: per-warp reservations widen the window of queue positions in flight across the GPU fourfold, and
+// closest-hit traversal loses node locality in L1/L2), so the shadow kernel fetches ahead and the extend kernel does not.
 #ifndef PTB_FETCH_AHEAD_EXTEND
 #define PTB_FETCH_AHEAD_EXTEND 0
 #endif
@@ -137,18 +138,20 @@ __device__ __forceinline__ void prefetch_l2(const void *p) {
 }
 
 struct WorkFetch {
-  static constexpr uint32_t CHUNK = 64u;  // queue positions per reservation (two refills of a whole warp)
-  uint32_t next, avail;  // unconsumed part of the current reservation (warp-uniform)
-  uint32_t ahead;        // lane 0: first position of the reservation requested last
-  bool ahead_fresh;      // the records of the `ahead` reservation have not been prefetched yet
+  uint32_t next, end;  // unconsumed part of the current reservation (warp-uniform)
+  uint32_t ahead;      // lane 0: first position of the reservation requested last
+  uint32_t chunk;      // queue positions per reservation
+  bool ahead_fresh;    // the records of the `ahead` reservation have not been prefetched yet
   bool drained;
 
-  __device__ __forceinline__ void init(uint32_t *cursor) {
-    next = avail = 0;
+  __device__ __forceinline__ void init(uint32_t *cursor, uint32_t n) {
+    const uint32_t total_warps = gridDim.x * (blockDim.x >> 5);
+    chunk = n >= total_warps * 256u ? 64u : 32u;  // short queues: small chunks, so that every SM gets some work
+    next = end = 0;
     ahead = 0;
     drained = false;
     ahead_fresh = true;
-    if (lane_id() == 0) ahead = atomicAdd(cursor, CHUNK);
+    if (lane_id() == 0) ahead = atomicAdd(cursor, chunk);
   }
   // pf(position) prefetches the records of one queue position.
   template <typename Prefetch>
@@ -156,28 +159,26 @@ struct WorkFetch {
     const uint32_t m = __ballot_sync(0xffffffffu, idle);
     uint32_t idx = 0xFFFFFFFFu;
     if (m && !drained) {
-      const uint32_t cnt = (uint32_t)__popc(m), rank = (uint32_t)__popc(m & lanemask_lt());
+      const uint32_t cnt = (uint32_t)__popc(m), rank = (uint32_t)__popc(m & lanemask_lt()), avail = end - next;
       if (cnt < avail) {
         if (idle) idx = next + rank;
         next += cnt;
-        avail -= cnt;
         if (next >= n) drained = true;  // every later position, reserved or not, is past the queue
         else if (ahead_fresh) {  // the reservation requested at the last switch has arrived by now: warm its records
           const uint32_t nb = __shfl_sync(0xffffffffu, ahead, 0);
-#pragma unroll
-          for (uint32_t k = 0; k < CHUNK; k += 32u)
-            if (nb + k + lane_id() < n) pf(nb + k + lane_id());
+          for (uint32_t k = lane_id(); k < chunk; k += 32u)
+            if (nb + k < n) pf(nb + k);
           ahead_fresh = false;
         }
       } else {  // the current reservation runs out: continue in the one requested earlier, request another
         const uint32_t nb = __shfl_sync(0xffffffffu, ahead, 0);
         if (idle) idx = rank < avail ? next + rank : nb + (rank - avail);
         next = nb + (cnt - avail);
-        avail = CHUNK - (cnt - avail);
+        end = nb + chunk;
         if (nb >= n) {
           drained = true;
         } else {
-          if (lane_id() == 0) ahead = atomicAdd(cursor, CHUNK);
+          if (lane_id() == 0) ahead = atomicAdd(cursor, chunk);
           ahead_fresh = true;
         }
       }
@@ -256,7 +257,7 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
   tv.cur = ClosestTrav::DONE;
 #if PTB_FETCH_AHEAD_EXTEND
   WorkFetch wf;
-  wf.init(&W.counters[CTR_WORK_EXTEND]);
+  wf.init(&W.counters[CTR_WORK_EXTEND], n);
   const float4 *pf_o = W.ray_o[in], *pf_d = W.ray_d[in];
 #define drained wf.drained
 #else
@@ -545,7 +546,7 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
   tv.cur = ShadowTrav::DONE;
 #if PTB_FETCH_AHEAD_SHADOW
   WorkFetch wf;
-  wf.init(&W.counters[CTR_WORK_SHADOW]);
+  wf.init(&W.counters[CTR_WORK_SHADOW], n);
 #define drained wf.drained
 #else
   bool drained = false;
