@@ -23,10 +23,6 @@
 #endif
 // 1: wave-state loads/stores use the streaming (evict-first) cache policy so that they do not displace BVH nodes
 // (measured: k_shade -10 %, k_extend -2 % on the console workload).
-// 1: k_shade prefetches the next chunk's path records and shading records (see k_shade).
-#ifndef PTB_SHADE_PREFETCH
-#define PTB_SHADE_PREFETCH 0
-#endif
 #ifndef PTB_STREAM
 #define PTB_STREAM 1
 #endif
@@ -357,19 +353,6 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
   for (uint32_t base = warp * 32u; base < n; base += warps * 32u) {
     const uint32_t q = base + lane_id();
     const bool active = q < n;
-#if PTB_SHADE_PREFETCH
-    // software pipeline over the warp's next chunk: its path records are pulled into L2 now, its hit index is loaded
-    // now and used at the END of this iteration to pull the shading record of the triangle it hit (the head of the
-    // dependent chain hit -> shading record -> material -> texel that this kernel's long-scoreboard stalls sit on)
-    const uint32_t qn = q + warps * 32u;
-    int idx_next = -1;
-    if (qn < n) {
-      idx_next = __float_as_int(W.hit[qn].w);
-      prefetch_l2(&W.ray_o[in][qn]);
-      prefetch_l2(&W.ray_d[in][qn]);
-      prefetch_l2(&W.thr[in][qn]);
-    }
-#endif
     Ray r{};
     V3 thr{}, rad = mk3(0.f, 0.f, 0.f);
     ShadeCtx ctx{};
@@ -420,15 +403,6 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
       st_wave(&W.ray_d[outb][pp], make_float4(next.d.x, next.d.y, next.d.z, __int_as_float((int)slot)));
       st_wave(&W.thr[outb][pp], make_float4(thr.x, thr.y, thr.z, 0.f));
     }
-#if PTB_SHADE_PREFETCH
-    if (idx_next >= 0) {
-      const uint32_t i = (uint32_t)(idx_next & HIT_INDEX_MASK);
-      if (i < S.n_tris) {
-        prefetch_l2(S.shade + i);
-        prefetch_l2(reinterpret_cast<const char *>(S.shade + i) + 32);
-      }
-    }
-#endif
   }
 }
 
