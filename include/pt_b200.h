@@ -247,12 +247,13 @@ int pt_render_progressive(const pt_scene *scene, const pt_profile *profile, uint
 /* ---- convert_gltf_to_isf (scene/gltf.rs:146-204): `path-tracer convert <input> <output_dir>` ---- */
 /* Reads a glTF 2.0 file (.gltf with external / base64 buffers, or .glb), writes <output_dir>/scene.isf and the
  * texture PNGs next to it (albedo_tex_N / alpha_tex_N / gray_tex_N / vec_tex_N, gltf.rs:47-77).  Host code only (no
- * GPU).  PNG images only: the image crate's JPEG decoder has no counterpart in this build. */
+ * GPU).  Images: PNG and baseline JPEG (progressive JPEG is rejected). */
 int pt_convert_gltf(const char *input, const char *output_dir);
 
 /* ---- image output: RgbImage::save (main.rs:50) ---- */
 int pt_write_png(const char *path, const uint8_t *rgb8, uint32_t width, uint32_t height);
-/* 8-bit PNG decode used by the texture bank (texture_bank.rs:33,49); channels_out in {1,3}.
+/* Texture decode used by the texture bank (texture_bank.rs:33,49): PNG or baseline JPEG, chosen by the file's
+ * signature as image::open does; channels_out in {1,3}.
  * *data_out is malloc'ed; free with pt_free. */
 int pt_read_png(const char *path, uint32_t channels_out, uint32_t *width, uint32_t *height,
                 uint8_t **data_out);

@@ -7,6 +7,7 @@
 #include <atomic>
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 #include <thread>
 
 #include "scene_host.hpp"
@@ -48,6 +49,7 @@ struct Builder {
   std::atomic<uint32_t> next{0};
   std::atomic<int> live_threads{1};
   int max_threads;
+  uint32_t max_leaf = bvh_max_leaf_tris();
 
   Builder(const HostScene &sc, int threads) : s(sc), nt((uint32_t)sc.n_tris()), max_threads(std::max(1, threads)) {}
 
@@ -74,7 +76,7 @@ struct Builder {
     }
     Node2 n;
     n.box = box;
-    if (count == 1 || (count <= 4 && !has_sphere)) {
+    if (count == 1 || (count <= max_leaf && !has_sphere)) {
       n.left = first;
       n.right = count | LEAF2;
       nodes[idx] = n;
@@ -142,6 +144,18 @@ struct Builder {
     return idx;
   }
 };
+
+}  // namespace
+
+// Triangles per leaf.  Measured on B200 (profiles/r02, k_extend ms at 16 / 4 / 8 spp on console / city / foliage):
+// 8: 6.75 / 24.7 / 48.5, 4: 5.92 / 19.1 / 40.4, 3: 5.24 / 16.4 / 38.3, 2: 5.22 / 16.5 / 36.6 — the traversal tests one
+// primitive per step, so a large leaf only trades cheap box tests for Moller-Trumbore tests that mostly miss.
+uint32_t bvh_max_leaf_tris() {
+  if (const char *e = std::getenv("PT_B200_LEAF_TRIS")) return (uint32_t)std::min(8, std::max(1, std::atoi(e)));
+  return 2;
+}
+
+namespace {
 
 inline Box inflate(const Box &b) {
   Box r;

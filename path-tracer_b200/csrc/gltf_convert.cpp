@@ -11,8 +11,9 @@
 //     colour * intensity.
 // The reference delegates parsing to the easy-gltf crate (^1.1.4, source not vendored): what that crate does is
 // restated from the glTF 2.0 specification.  Not on the accelerated path: plain host C++.
-// Limits (an error, exit code 2): JPEG / non-PNG images (no decoder in this build), sparse accessors, non-triangle
-// primitive modes, orthographic cameras, scenes without a camera (the reference panics there).
+// Images: PNG (png.cpp) and baseline JPEG (jpeg.cpp).  Limits (an error, exit code 2): progressive JPEG and other
+// image formats, sparse accessors, non-triangle primitive modes, orthographic cameras, scenes without a camera (the
+// reference panics there).
 #include <sys/stat.h>
 
 #include <cerrno>
@@ -287,12 +288,9 @@ struct TextureBank {  // ReverseTextureBank, gltf.rs:18-77: one counter per text
     if (it != rgba_cache.end()) return it->second;
     std::string name;
     std::vector<uint8_t> bytes = doc->image_bytes(image, name);
-    static const uint8_t png_sig[4] = {0x89, 'P', 'N', 'G'};
-    if (bytes.size() < 4 || std::memcmp(bytes.data(), png_sig, 4) != 0)
-      fail(name + ": only PNG images can be converted (no JPEG decoder in this build); re-encode the texture as PNG");
     uint32_t w = 0, h = 0;
     std::vector<uint8_t> px;
-    if (png_decode(bytes.data(), bytes.size(), name.c_str(), 4, &w, &h, px) != PT_OK) fail(pt_last_error());
+    if (image_decode(bytes.data(), bytes.size(), name.c_str(), 4, &w, &h, px) != PT_OK) fail(pt_last_error());
     dims[image] = {w, h};
     return rgba_cache[image] = std::move(px);
   }

@@ -14,6 +14,11 @@ int load_isf_file(const char *path, HostScene &out);
 int png_read(const char *path, uint32_t channels_out, uint32_t *w, uint32_t *h, std::vector<uint8_t> &data);
 int png_decode(const uint8_t *bytes, size_t size, const char *name, uint32_t channels_out, uint32_t *w, uint32_t *h,
                std::vector<uint8_t> &data);
+// jpeg.cpp: baseline JPEG; image_decode picks PNG or JPEG from the signature (like image::open)
+int jpeg_decode(const uint8_t *bytes, size_t size, const char *name, uint32_t channels_out, uint32_t *w, uint32_t *h,
+                std::vector<uint8_t> &data);
+int image_decode(const uint8_t *bytes, size_t size, const char *name, uint32_t channels_out, uint32_t *w, uint32_t *h,
+                 std::vector<uint8_t> &data);
 int png_write(const char *path, const uint8_t *rgb8, uint32_t w, uint32_t h);
 int png_write_ch(const char *path, const uint8_t *pixels, uint32_t w, uint32_t h, uint32_t channels);
 // gltf_convert.cpp: scene::convert_gltf_to_isf (src/scene/gltf.rs:146-204)

@@ -365,16 +365,17 @@ struct CollapseArgs {
   const uint32_t *sorted_prim;   // sorted position -> primitive (triangles < nt <= spheres)
   const uint32_t *tri_rank;      // sorted position -> number of triangles before it (n + 1 entries)
   uint32_t nt;
+  uint32_t max_leaf;             // triangles per leaf (bvh_max_leaf_tris)
   Bvh4Node *nodes;
   uint32_t *node_count;
   uint32_t node_cap;
 };
 
-// A radix-tree node is emitted as one leaf when it holds <= 4 primitives, all triangles (spheres sit alone).
+// A radix-tree node is emitted as one leaf when it holds <= max_leaf primitives, all triangles (spheres sit alone).
 __device__ __forceinline__ bool is_leaf_ref(const CollapseArgs &A, uint32_t ref) {
   if (ref & PRIM) return true;
   const uint32_t lo = A.rlo[ref], hi = A.rhi[ref], cnt = hi - lo + 1;
-  return cnt <= 4 && A.tri_rank[hi + 1] - A.tri_rank[lo] == cnt;
+  return cnt <= A.max_leaf && A.tri_rank[hi + 1] - A.tri_rank[lo] == cnt;
 }
 __device__ __forceinline__ void ref_box(const CollapseArgs &A, uint32_t ref, float4 &lo, float4 &hi) {
   if (ref & PRIM) {
@@ -476,8 +477,8 @@ __global__ void __launch_bounds__(256) k_leaf_order(uint32_t n, uint32_t nt, con
 int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_deep) {
   if (too_deep) *too_deep = 0;
   const uint32_t nt = (uint32_t)s.n_tris(), ns = (uint32_t)s.sphere_models.size(), n = nt + ns;
-  if (n < 8) {
-    set_error("LBVH build needs at least 8 primitives");
+  if (n < 16) {
+    set_error("LBVH build needs at least 16 primitives");
     return PT_ERR_INVALID;
   }
   cudaStream_t st = nullptr;
@@ -547,7 +548,7 @@ int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_dee
   k_fit<<<g256, 256, 0, st>>>((int)n, vals, blo, bhi, left, right, par_i, par_p, nlo, nhi, visits);
   LB_TRY(cudaGetLastError());
   // level-by-level collapse; the root of the radix tree (internal node 0) becomes 4-wide node 0
-  CollapseArgs A{left, right, rlo, rhi, nlo, nhi, blo, bhi, vals, tri_rank, nt, nodes, ctr, node_cap};
+  CollapseArgs A{left, right, rlo, rhi, nlo, nhi, blo, bhi, vals, tri_rank, nt, bvh_max_leaf_tris(), nodes, ctr, node_cap};
   const uint32_t one = 1;
   LB_TRY(cudaMemcpyAsync(ctr, &one, sizeof one, cudaMemcpyHostToDevice, st));  // node_count = 1 (the root)
   const uint2 root_item = make_uint2(0u, 0u);

@@ -33,7 +33,7 @@ int png_read(const char *path, uint32_t channels_out, uint32_t *w_out, uint32_t 
   size_t n;
   while ((n = std::fread(buf, 1, sizeof buf, f)) > 0) file.insert(file.end(), buf, buf + n);
   std::fclose(f);
-  return png_decode(file.data(), file.size(), path, channels_out, w_out, h_out, out);
+  return image_decode(file.data(), file.size(), path, channels_out, w_out, h_out, out);  // PNG, or JPEG by signature
 }
 
 // channels_out: 1 (into_luma8), 3 (into_rgb8) or 4 (into_rgba8; alpha 255 when the file has none).

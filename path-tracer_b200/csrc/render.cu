@@ -116,7 +116,7 @@ int build_device_scene(pt_scene *sc) {
   int accel = accel_choice();
   const uint64_t n_prims_geom = h.n_tris() + h.sphere_models.size();
   if (accel == PT_ACCEL_AUTO) accel = n_prims_geom >= (4ull << 20) ? PT_ACCEL_LBVH : PT_ACCEL_SAH;
-  if (n_prims_geom < 8) accel = PT_ACCEL_SAH;
+  if (n_prims_geom < 16) accel = PT_ACCEL_SAH;  // the LBVH root must not be a single leaf (leaves hold <= 8 triangles)
   sc->accel = PT_ACCEL_SAH;
   bool built = false;
   if (accel == PT_ACCEL_LBVH) {

@@ -62,6 +62,8 @@ struct Bvh4 {
 // Binned-SAH BVH2 build over triangles + spheres, collapsed to 4-wide.  Boxes are inflated
 // conservatively so a box cull can never drop a primitive Möller–Trumbore would accept.
 void build_bvh4(const HostScene &s, Bvh4 &out, int threads);
+// Largest number of triangles either builder puts into one leaf (default 2; $PT_B200_LEAF_TRIS in 1..8 for A/B runs).
+uint32_t bvh_max_leaf_tris();
 
 // GPU LBVH build (lbvh.cu) on the current CUDA device: Morton codes + radix sort + Karras hierarchy + bottom-up fit,
 // collapsed to the same 4-wide nodes.  *build_ms = device time of the build (CUDA events, upload excluded).

@@ -212,21 +212,91 @@ def test_convert_api_and_errors(tmp_path):
     path, exp = build_gltf(tmp_path)
     pt.convert_gltf_to_isf(str(path), str(tmp_path / "o2"))
     check_scene(tmp_path / "o2", exp)
-    # output exists but is a file (gltf.rs:153-155), missing input, no camera, JPEG texture: all exit code 2 (main.rs:14-21)
+    # output exists but is a file (gltf.rs:153-155), missing input, no camera, progressive JPEG: all exit code 2 (main.rs:14-21)
     (tmp_path / "afile").write_text("x")
     doc = json.loads(path.read_text())
     doc["nodes"][3].pop("camera")
     (tmp_path / "nocam.gltf").write_text(json.dumps(doc))
     doc = json.loads(path.read_text())
-    (tmp_path / "fake.jpg").write_bytes(b"\xff\xd8\xff\xe0" + b"\0" * 32)
-    doc["images"][0] = {"uri": "fake.jpg"}
+    Image.fromarray(np.zeros((16, 16, 3), np.uint8), "RGB").save(tmp_path / "prog.jpg", progressive=True)
+    doc["images"][0] = {"uri": "prog.jpg"}
     (tmp_path / "jpeg.gltf").write_text(json.dumps(doc))
     for args, needle in (([str(path), str(tmp_path / "afile")], b"is not a directory"),
                          ([str(tmp_path / "missing.gltf"), str(tmp_path / "o3")], b"cannot open"),
                          ([str(tmp_path / "nocam.gltf"), str(tmp_path / "o4")], b"No camera found"),
-                         ([str(tmp_path / "jpeg.gltf"), str(tmp_path / "o5")], b"PNG"),
+                         ([str(tmp_path / "jpeg.gltf"), str(tmp_path / "o5")], b"progressive"),
                          ([str(path)], b"required arguments")):
         r = subprocess.run([EXE, "convert"] + args, capture_output=True)
         assert r.returncode == 2 and needle in r.stderr, (args, r.stderr)
     with pytest.raises(pt.PtError):
         pt.convert_gltf_to_isf(str(tmp_path / "missing.gltf"), str(tmp_path / "o6"))
+
+
+def smooth_image(h, w, seed):
+    rng = np.random.default_rng(seed)
+    y, x = np.mgrid[0:h, 0:w]
+    img = np.stack([127 + 120 * np.sin(x / 9.0 + seed), 127 + 120 * np.cos(y / 7.0), 127 + 100 * np.sin((x + y) / 11.0)], -1)
+    return np.clip(img + rng.normal(0, 4, img.shape), 0, 255).astype(np.uint8)
+
+
+@pytest.mark.parametrize("subsampling,quality,size", [(0, 95, (40, 56)), (1, 90, (33, 47)), (2, 85, (50, 37)), (2, 60, (16, 16))])
+def test_jpeg_decode_matches_pil(tmp_path, subsampling, quality, size):
+    """Baseline JPEG textures (image::open accepts them in texture_bank.rs:33,49): decoded pixels agree with libjpeg's
+    to within IDCT / chroma-upsampling differences."""
+    h, w = size
+    img = smooth_image(h, w, subsampling + quality)
+    p = tmp_path / "t.jpg"
+    Image.fromarray(img, "RGB").save(p, quality=quality, subsampling=subsampling)
+    got = pt.read_png(str(p), 3).astype(np.int16)
+    want = np.asarray(Image.open(p).convert("RGB")).astype(np.int16)
+    assert got.shape == want.shape
+    d = np.abs(got - want)
+    if subsampling == 0:
+        assert d.max() <= 2 and d.mean() < 0.5, (d.max(), d.mean())
+    else:  # linear vs libjpeg's integer "fancy" chroma upsampling
+        assert d.mean() < 1.0 and d.max() <= 6, (d.mean(), d.max())
+    gray = pt.read_png(str(p), 1)[:, :, 0].astype(np.int16)
+    g32 = got.astype(np.int64)
+    luma = (2126 * g32[:, :, 0] + 7152 * g32[:, :, 1] + 722 * g32[:, :, 2]) // 10000
+    assert np.array_equal(gray, luma)
+
+
+def test_jpeg_gray_restart_and_errors(tmp_path):
+    g = smooth_image(45, 61, 3)[:, :, 0]
+    p = tmp_path / "g.jpg"
+    Image.fromarray(g, "L").save(p, quality=92)
+    got = pt.read_png(str(p), 1)[:, :, 0].astype(np.int16)
+    want = np.asarray(Image.open(p)).astype(np.int16)
+    assert np.abs(got - want).max() <= 2
+    rgb = pt.read_png(str(p), 3)
+    assert (rgb[:, :, 0] == rgb[:, :, 1]).all() and (rgb[:, :, 1] == rgb[:, :, 2]).all()
+    # restart intervals (DRI/RSTn): same pixels as the file without them
+    img = smooth_image(48, 64, 9)
+    a, b = tmp_path / "a.jpg", tmp_path / "b.jpg"
+    Image.fromarray(img, "RGB").save(a, quality=90, subsampling=2)
+    Image.fromarray(img, "RGB").save(b, quality=90, subsampling=2, restart_marker_blocks=2)
+    assert b.read_bytes().count(b"\xff\xdd") >= 1
+    assert np.array_equal(pt.read_png(str(a), 3), pt.read_png(str(b), 3))
+    prog = tmp_path / "p.jpg"
+    Image.fromarray(img, "RGB").save(prog, progressive=True)
+    with pytest.raises(pt.PtError) as e:
+        pt.read_png(str(prog), 3)
+    assert "progressive" in str(e.value)
+    trunc = tmp_path / "t.jpg"
+    trunc.write_bytes(a.read_bytes()[:40])
+    with pytest.raises(pt.PtError):
+        pt.read_png(str(trunc), 3)
+
+
+def test_convert_with_jpeg_texture(tmp_path):
+    path, exp = build_gltf(tmp_path)
+    doc = json.loads(path.read_text())
+    Image.fromarray(smooth_image(24, 32, 1), "RGB").save(tmp_path / "base.jpg", quality=95, subsampling=0)
+    doc["images"][0] = {"uri": "base.jpg"}
+    (tmp_path / "j.gltf").write_text(json.dumps(doc))
+    out = tmp_path / "oj"
+    pt.convert_gltf_to_isf(str(tmp_path / "j.gltf"), str(out))
+    alb = np.asarray(Image.open(out / "albedo_tex_0.png")).astype(np.int16)
+    want = np.asarray(Image.open(tmp_path / "base.jpg").convert("RGB")).astype(np.int16)
+    assert alb.shape == want.shape and np.abs(alb - want).max() <= 3 and np.abs(alb - want).mean() < 0.5
+    assert (np.asarray(Image.open(out / "alpha_tex_0.png")) == 255).all()  # a JPEG has no alpha: opaque
