@@ -250,6 +250,14 @@ int pt_render_progressive(const pt_scene *scene, const pt_profile *profile, uint
  * GPU).  Images: PNG and baseline JPEG (progressive JPEG is rejected). */
 int pt_convert_gltf(const char *input, const char *output_dir);
 
+/* ---- binary side-car of an isf scene ("isfb"; no reference counterpart: scene/isf.rs is JSON only) ---- */
+/* Writes the flat scene of `scene` (decoded textures included) as raw little-endian arrays; with_accel != 0 also
+ * stores the scene's 4-wide BVH (a host-only scene, device -1, gets the host SAH tree built for the purpose).
+ * pt_scene_load_isf recognises such a file by its magic, checks a stored tree against the scene (every reference in
+ * range, leaves partition the triangles, child boxes contain their contents) and skips the build.  Layout:
+ * path-tracer_b200/csrc/isf_binary.cpp. */
+int pt_scene_save_binary(const pt_scene *scene, const char *path, int with_accel);
+
 /* ---- image output: RgbImage::save (main.rs:50) ---- */
 int pt_write_png(const char *path, const uint8_t *rgb8, uint32_t width, uint32_t height);
 /* Texture decode used by the texture bank (texture_bank.rs:33,49): PNG or baseline JPEG, chosen by the file's

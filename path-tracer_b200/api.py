@@ -21,7 +21,7 @@ _LIB = None
 EXPORTS = ["pt_last_error", "pt_device_count", "pt_profile_default", "pt_profile_load_yaml", "pt_scene_load_isf",
            "pt_scene_create", "pt_scene_synthetic", "pt_scene_destroy", "pt_set_accel_builder", "pt_scene_accel_info", "pt_scene_upload", "pt_set_kernel_timing", "pt_scene_get_desc", "pt_scene_info",
            "pt_trace_closest", "pt_trace_closest_device", "pt_trace_transmittance", "pt_triangle_intersect",
-           "pt_trace_paths", "pt_render_accum_device", "pt_aov_name", "pt_debug_textures", "pt_render_progressive", "pt_convert_gltf",
+           "pt_trace_paths", "pt_render_accum_device", "pt_aov_name", "pt_debug_textures", "pt_render_progressive", "pt_convert_gltf", "pt_scene_save_binary",
            "pt_tonemap_device", "pt_render", "pt_write_png", "pt_read_png", "pt_free"]
 
 
@@ -72,6 +72,7 @@ def lib():
         L.pt_set_accel_builder.argtypes = [C.c_int]
         L.pt_scene_accel_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.pt_convert_gltf.argtypes = [C.c_char_p, C.c_char_p]
+        L.pt_scene_save_binary.argtypes = [vp, C.c_char_p, C.c_int]
         L.pt_aov_name.argtypes = [C.c_int]
         L.pt_aov_name.restype = C.c_char_p
         L.pt_debug_textures.argtypes = [vp, u32, u32, vp, C.POINTER(u64)]
@@ -184,6 +185,10 @@ class Scene:
         a, ms, d = C.c_int(), C.c_double(), C.c_int()
         _check(lib().pt_scene_accel_info(self.h, C.byref(a), C.byref(ms), C.byref(d)))
         return dict(accel=("sah", "lbvh")[a.value], build_ms=ms.value, max_depth=d.value)
+
+    def save_binary(self, path, with_accel=True):
+        """Write the scene as an isfb file (raw arrays, optionally with its BVH); Scene.load reads it back."""
+        _check(lib().pt_scene_save_binary(self.h, os.fsencode(path), 1 if with_accel else 0))
 
     def arrays(self):
         """Host copy of the flat scene as a SceneArrays (used to hand the same scene to a checker)."""

@@ -157,10 +157,10 @@ uint32_t bvh_max_leaf_tris() {
 
 namespace {
 
-inline Box inflate(const Box &b) {
+inline Box inflate(const Box &b, float S) {
   Box r;
   for (int k = 0; k < 3; ++k) {
-    float e = std::max(std::fabs(b.lo[k]), std::fabs(b.hi[k])) * 4e-6f + 1e-7f;
+    float e = plane_pad(b.lo[k], b.hi[k], S);
     r.lo[k] = b.lo[k] - e;
     r.hi[k] = b.hi[k] + e;
   }
@@ -174,18 +174,34 @@ void build_bvh4(const HostScene &s, Bvh4 &out, int threads) {
   const uint32_t nt = B.nt, ns = (uint32_t)s.sphere_models.size();
   const uint32_t n = nt + ns;
   B.pbox.resize(n);
+  Box scene;
+  scene.reset();
   for (uint32_t t = 0; t < nt; ++t) {
     Box b;
     b.reset();
     for (int k = 0; k < 3; ++k) b.grow_pt(&s.pos[(size_t)t * 9 + k * 3]);
     B.pbox[t] = b;
+    scene.grow(b);
   }
   for (uint32_t k = 0; k < ns; ++k) {
     const pt_model &m = s.models[s.sphere_models[k]];
-    float r = std::fabs(m.radius) * 1.0001f + 1e-6f;
+    float r = std::fabs(m.radius);
     Box b;
     for (int a = 0; a < 3; ++a) { b.lo[a] = m.center[a] - r; b.hi[a] = m.center[a] + r; }
     B.pbox[nt + k] = b;
+    scene.grow(b);
+  }
+  // margins (scene_host.hpp): primitive boxes grow by what the f32 intersection arithmetic can leak
+  const float *cam = &s.camera[12];
+  const float D = ray_distance_scale(scene.lo, scene.hi, cam), S = coordinate_scale(scene.lo, scene.hi, cam);
+  for (uint32_t t = 0; t < nt; ++t) {
+    const float e = triangle_leak_pad(&s.pos[(size_t)t * 9], D);
+    for (int a = 0; a < 3; ++a) { B.pbox[t].lo[a] -= e; B.pbox[t].hi[a] += e; }
+  }
+  for (uint32_t k = 0; k < ns; ++k) {
+    const pt_model &m = s.models[s.sphere_models[k]];
+    const float r = sphere_box_radius(m.radius, D);
+    for (int a = 0; a < 3; ++a) { B.pbox[nt + k].lo[a] = m.center[a] - r; B.pbox[nt + k].hi[a] = m.center[a] + r; }
   }
   B.order.resize(n);
   for (uint32_t i = 0; i < n; ++i) B.order[i] = i;
@@ -212,7 +228,7 @@ void build_bvh4(const HostScene &s, Bvh4 &out, int threads) {
       nd.hi_x[k] = nd.hi_y[k] = nd.hi_z[k] = NAN;
       nd.child[k] = BVH_EMPTY;
     }
-    Box b = inflate(rn.box);
+    Box b = inflate(rn.box, S);
     nd.lo_x[0] = b.lo[0]; nd.lo_y[0] = b.lo[1]; nd.lo_z[0] = b.lo[2];
     nd.hi_x[0] = b.hi[0]; nd.hi_y[0] = b.hi[1]; nd.hi_z[0] = b.hi[2];
     nd.child[0] = leaf_ref(rn);
@@ -254,7 +270,7 @@ void build_bvh4(const HostScene &s, Bvh4 &out, int threads) {
     }
     for (int k = 0; k < nk; ++k) {
       const Node2 &c = B.nodes[kids[k]];
-      Box b = inflate(c.box);
+      Box b = inflate(c.box, S);
       nd.lo_x[k] = b.lo[0]; nd.lo_y[k] = b.lo[1]; nd.lo_z[k] = b.lo[2];
       nd.hi_x[k] = b.hi[0]; nd.hi_y[k] = b.hi[1]; nd.hi_z[k] = b.hi[2];
       if (c.right & LEAF2) {

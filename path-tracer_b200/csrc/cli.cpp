@@ -5,7 +5,9 @@
 // delivers the same feed headless instead: the running mean image is written over <OUTPUT> after every
 // --snapshot-every samples per pixel (default 16).  --debug-textures writes the seven AOV PNGs of
 // renderer/debug_renderer.rs into the working directory.  `convert <INPUT> <OUTPUT>` (glTF -> isf, scene/gltf.rs) is
-// host code (gltf_convert.cpp).
+// host code (gltf_convert.cpp); `convert --binary` also writes <OUTPUT>/scene.isfb, and `pack <INPUT> <OUTPUT.isfb>`
+// turns any isf / isfb scene into the binary side-car (raw arrays + the host SAH tree unless --no-accel;
+// isf_binary.cpp), which `render` accepts wherever it accepts scene.isf.
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -21,7 +23,9 @@ static int usage(const char *msg) {
                "Path-trace awesome things\n\nUsage: path-tracer <COMMAND>\n\nCommands:\n"
                "  render   <INPUT> [-o, --output <OUTPUT>] [-q, --quiet] [-v, --viewer] [--debug-textures]\n"
                "           [-p, --profile <PROFILE>] [--seed <N>] [--stats <FILE>] [--snapshot-every <SPP>]\n"
-               "  convert  <INPUT> <OUTPUT>   glTF 2.0 (.gltf / .glb) -> <OUTPUT>/scene.isf + texture PNGs\n");
+               "  convert  <INPUT> <OUTPUT> [--binary]   glTF 2.0 (.gltf / .glb) -> <OUTPUT>/scene.isf + texture PNGs\n"
+               "           (--binary: also <OUTPUT>/scene.isfb)\n"
+               "  pack     <INPUT> <OUTPUT.isfb> [--no-accel]   isf scene -> binary side-car with its BVH\n");
   return 2;
 }
 
@@ -32,24 +36,38 @@ int main(int argc, char **argv) {
     usage(nullptr);
     return 0;
   }
-  if (cmd == "convert") {  // config/mod.rs:44-52 + main.rs:54-57
+  if (cmd == "convert" || cmd == "pack") {  // config/mod.rs:44-52 + main.rs:54-57
     std::vector<std::string> pos;
+    bool binary = false, accel = true;
     for (int i = 2; i < argc; ++i) {
       std::string a = argv[i];
       if (a == "-h" || a == "--help") {
         usage(nullptr);
         return 0;
       }
+      if (cmd == "convert" && a == "--binary") { binary = true; continue; }
+      if (cmd == "pack" && a == "--no-accel") { accel = false; continue; }
       if (!a.empty() && a[0] == '-') return usage(("unexpected argument '" + a + "'").c_str());
       pos.push_back(a);
     }
     if (pos.size() < 2) return usage("the following required arguments were not provided: <INPUT> <OUTPUT>");
     if (pos.size() > 2) return usage(("unexpected argument '" + pos[2] + "'").c_str());
-    if (pt_convert_gltf(pos[0].c_str(), pos[1].c_str()) != PT_OK) {
+    auto fail = [] {
       std::fprintf(stderr, "%s\n", pt_last_error());
       return 2;
+    };
+    std::string isf = pos[0], isfb = pos[1];
+    if (cmd == "convert") {
+      if (pt_convert_gltf(pos[0].c_str(), pos[1].c_str()) != PT_OK) return fail();
+      if (!binary) return 0;
+      isf = pos[1] + "/scene.isf";
+      isfb = pos[1] + "/scene.isfb";
     }
-    return 0;
+    pt_scene *host_scene = nullptr;  // device -1: parsed and finalised on the host, nothing uploaded
+    if (pt_scene_load_isf(isf.c_str(), -1, &host_scene) != PT_OK) return fail();
+    int rc = pt_scene_save_binary(host_scene, isfb.c_str(), accel ? 1 : 0);
+    pt_scene_destroy(host_scene);
+    return rc == PT_OK ? 0 : fail();
   }
   if (cmd != "render") return usage(("unrecognized subcommand '" + cmd + "'").c_str());
 

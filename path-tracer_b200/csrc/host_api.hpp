@@ -6,8 +6,9 @@
 
 namespace ptb {
 void set_error(const char *fmt, ...);
-// Finalises `host`, builds the BVH, uploads to `device`.  Takes ownership of host.
-int scene_from_host(HostScene &&host, int device, pt_scene **out);
+// Finalises `host`, builds the BVH, uploads to `device`.  Takes ownership of host.  With `accel` (read from an isfb
+// file, kind = PT_ACCEL_*) the tree is validated against the scene and used instead of building one.
+int scene_from_host(HostScene &&host, int device, pt_scene **out, Bvh4 *accel = nullptr, int accel_kind = -1);
 // isf_loader.cpp: scene/mod.rs:16-22 + isf.rs serde schema.  Returns PT_OK or an error (message set).
 int load_isf_file(const char *path, HostScene &out);
 // png.cpp

@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(256) k_prim_boxes(const float *__restrict__ po
                                                     float4 *__restrict__ blo, float4 *__restrict__ bhi,
                                                     uint32_t *__restrict__ cbounds /* 6 ordered uints */) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x, n = nt + ns;
-  float c[3] = {0, 0, 0};
+  float c[3] = {0, 0, 0}, b[6] = {0, 0, 0, 0, 0, 0};
   const bool live = i < n;
   if (live) {
     float lo[3], hi[3];
@@ -77,25 +77,66 @@ __global__ void __launch_bounds__(256) k_prim_boxes(const float *__restrict__ po
       }
     } else {
       const float4 s = spheres[i - nt];
-      const float r = fabsf(s.w) * 1.0001f + 1e-6f;  // same margin as bvh_build.cpp
+      const float r = fabsf(s.w);  // exact extent; the margins are added by k_pad_boxes once the scene box is known
       lo[0] = s.x - r; lo[1] = s.y - r; lo[2] = s.z - r;
       hi[0] = s.x + r; hi[1] = s.y + r; hi[2] = s.z + r;
     }
     blo[i] = make_float4(lo[0], lo[1], lo[2], 0.f);
     bhi[i] = make_float4(hi[0], hi[1], hi[2], 0.f);
-    for (int k = 0; k < 3; ++k) c[k] = 0.5f * (lo[k] + hi[k]);
+    for (int k = 0; k < 3; ++k) {
+      c[k] = 0.5f * (lo[k] + hi[k]);
+      b[k] = lo[k];
+      b[3 + k] = hi[k];
+    }
   }
-  // warp-reduce the centroid bounds, then one atomic pair per warp and axis
+  // warp-reduce the centroid bounds (Morton normalisation) and the scene box (margins), then one atomic pair per
+  // warp and axis for each
   for (int k = 0; k < 3; ++k) {
     float mn = live ? c[k] : FLT_MAX, mx = live ? c[k] : -FLT_MAX;
+    float bn = live ? b[k] : FLT_MAX, bx = live ? b[3 + k] : -FLT_MAX;
     for (int o = 16; o; o >>= 1) {
       mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
       mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      bn = fminf(bn, __shfl_xor_sync(0xffffffffu, bn, o));
+      bx = fmaxf(bx, __shfl_xor_sync(0xffffffffu, bx, o));
     }
     if ((threadIdx.x & 31) == 0 && mn <= mx) {
       atomicMin(&cbounds[k], f2o(mn));
       atomicMax(&cbounds[3 + k], f2o(mx));
+      atomicMin(&cbounds[8 + k], f2o(bn));
+      atomicMax(&cbounds[11 + k], f2o(bx));
     }
+  }
+}
+
+struct SceneScale { float D, S; };
+__device__ __forceinline__ SceneScale scene_scale(const uint32_t *__restrict__ cbounds, float3 cam) {
+  const float lo[3] = {o2f(cbounds[8]), o2f(cbounds[9]), o2f(cbounds[10])};
+  const float hi[3] = {o2f(cbounds[11]), o2f(cbounds[12]), o2f(cbounds[13])};
+  const float c[3] = {cam.x, cam.y, cam.z};
+  return SceneScale{ray_distance_scale(lo, hi, c), coordinate_scale(lo, hi, c)};
+}
+
+// ---- 1b. margins of the primitive boxes (scene_host.hpp): what the f32 intersection arithmetic can leak ----
+__global__ void __launch_bounds__(256) k_pad_boxes(const float *__restrict__ pos9, uint32_t nt,
+                                                   const float4 *__restrict__ spheres, uint32_t ns,
+                                                   float4 *__restrict__ blo, float4 *__restrict__ bhi,
+                                                   const uint32_t *__restrict__ cbounds, float3 cam) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nt + ns) return;
+  const float D = scene_scale(cbounds, cam).D;
+  if (i < nt) {
+    float p[9];
+    for (int k = 0; k < 9; ++k) p[k] = pos9[(size_t)i * 9 + k];
+    const float e = triangle_leak_pad(p, D);
+    float4 lo = blo[i], hi = bhi[i];
+    blo[i] = make_float4(lo.x - e, lo.y - e, lo.z - e, 0.f);
+    bhi[i] = make_float4(hi.x + e, hi.y + e, hi.z + e, 0.f);
+  } else {
+    const float4 s = spheres[i - nt];
+    const float r = sphere_box_radius(s.w, D);
+    blo[i] = make_float4(s.x - r, s.y - r, s.z - r, 0.f);
+    bhi[i] = make_float4(s.x + r, s.y + r, s.z + r, 0.f);
   }
 }
 
@@ -369,6 +410,8 @@ struct CollapseArgs {
   Bvh4Node *nodes;
   uint32_t *node_count;
   uint32_t node_cap;
+  const uint32_t *cbounds;       // scene box (k_prim_boxes) for the slab-plane margin
+  float3 cam;
 };
 
 // A radix-tree node is emitted as one leaf when it holds <= max_leaf primitives, all triangles (spheres sit alone).
@@ -410,6 +453,7 @@ __global__ void __launch_bounds__(128) k_collapse(const CollapseArgs A, const ui
   const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
   if (w >= n_in) return;
   const uint2 item = work_in[w];  // x = radix-tree node (internal, not a leaf), y = 4-wide node index
+  const float S = scene_scale(A.cbounds, A.cam).S;
   uint32_t kids[4];
   int nk = 2;
   kids[0] = A.left[item.x];
@@ -439,10 +483,8 @@ __global__ void __launch_bounds__(128) k_collapse(const CollapseArgs A, const ui
   for (int k = 0; k < nk; ++k) {
     float4 lo, hi;
     ref_box(A, kids[k], lo, hi);
-    // conservative inflation, identical to bvh_build.cpp: a box cull may never drop a primitive Moller-Trumbore accepts
-    const float ex = fmaxf(fabsf(lo.x), fabsf(hi.x)) * 4e-6f + 1e-7f;
-    const float ey = fmaxf(fabsf(lo.y), fabsf(hi.y)) * 4e-6f + 1e-7f;
-    const float ez = fmaxf(fabsf(lo.z), fabsf(hi.z)) * 4e-6f + 1e-7f;
+    // slab-plane margin, identical to bvh_build.cpp (scene_host.hpp plane_pad)
+    const float ex = plane_pad(lo.x, hi.x, S), ey = plane_pad(lo.y, hi.y, S), ez = plane_pad(lo.z, hi.z, S);
     nd.lo_x[k] = lo.x - ex; nd.hi_x[k] = hi.x + ex;
     nd.lo_y[k] = lo.y - ey; nd.hi_y[k] = hi.y + ey;
     nd.lo_z[k] = lo.z - ez; nd.hi_z[k] = hi.z + ez;
@@ -498,7 +540,7 @@ int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_dee
   LB_TRY(B.alloc(&bhi, n));
   LB_TRY(B.alloc(&nlo, n));
   LB_TRY(B.alloc(&nhi, n));
-  LB_TRY(B.alloc(&cb, 8));
+  LB_TRY(B.alloc(&cb, 16));
   LB_TRY(B.alloc(&keys, n));
   LB_TRY(B.alloc(&vals, n));
   LB_TRY(B.alloc(&keys2, n));
@@ -531,11 +573,15 @@ int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_dee
   LB_TRY(cudaEventCreate(&e0));
   LB_TRY(cudaEventCreate(&e1));
   LB_TRY(cudaEventRecord(e0, st));
-  const uint32_t init_cb[6] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u};
+  // [0..5] centroid bounds, [8..13] scene box, both as order-preserving uints (min slots start at the maximum)
+  const uint32_t init_cb[16] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u, 0u, 0u,
+                                0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u, 0u, 0u};
+  const float3 cam = make_float3(s.camera[12], s.camera[13], s.camera[14]);
   LB_TRY(cudaMemcpyAsync(cb, init_cb, sizeof init_cb, cudaMemcpyHostToDevice, st));
   const uint32_t g256 = (n + 255) / 256;
   k_prim_boxes<<<g256, 256, 0, st>>>(d_pos, nt, d_sph, ns, blo, bhi, cb);
   k_morton<<<g256, 256, 0, st>>>(blo, bhi, n, cb, keys, vals);
+  k_pad_boxes<<<g256, 256, 0, st>>>(d_pos, nt, d_sph, ns, blo, bhi, cb, cam);  // symmetric: centroids unchanged
   int rc = radix_sort_pairs(keys, vals, keys2, vals2, n, 32, counts, scan_tmp, st);
   if (rc) return rc;
   // triangle ranks in sorted order (n + 1 entries: the last one is the triangle count)
@@ -548,7 +594,7 @@ int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_dee
   k_fit<<<g256, 256, 0, st>>>((int)n, vals, blo, bhi, left, right, par_i, par_p, nlo, nhi, visits);
   LB_TRY(cudaGetLastError());
   // level-by-level collapse; the root of the radix tree (internal node 0) becomes 4-wide node 0
-  CollapseArgs A{left, right, rlo, rhi, nlo, nhi, blo, bhi, vals, tri_rank, nt, bvh_max_leaf_tris(), nodes, ctr, node_cap};
+  CollapseArgs A{left, right, rlo, rhi, nlo, nhi, blo, bhi, vals, tri_rank, nt, bvh_max_leaf_tris(), nodes, ctr, node_cap, cb, cam};
   const uint32_t one = 1;
   LB_TRY(cudaMemcpyAsync(ctr, &one, sizeof one, cudaMemcpyHostToDevice, st));  // node_count = 1 (the root)
   const uint2 root_item = make_uint2(0u, 0u);

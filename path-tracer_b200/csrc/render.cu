@@ -71,6 +71,7 @@ struct pt_scene {
   uint64_t device_bytes = 0;
   double build_ms = 0;
   int accel = PT_ACCEL_SAH;
+  bool accel_preloaded = false;  // bvh came validated from an isfb file: build_device_scene only uploads it
   // wave buffers, grown lazily and reused between renders (guarded: one render at a time per scene)
   std::mutex mu;
   WaveState wave{};
@@ -117,9 +118,9 @@ int build_device_scene(pt_scene *sc) {
   const uint64_t n_prims_geom = h.n_tris() + h.sphere_models.size();
   if (accel == PT_ACCEL_AUTO) accel = n_prims_geom >= (4ull << 20) ? PT_ACCEL_LBVH : PT_ACCEL_SAH;
   if (n_prims_geom < 16) accel = PT_ACCEL_SAH;  // the LBVH root must not be a single leaf (leaves hold <= 8 triangles)
-  sc->accel = PT_ACCEL_SAH;
-  bool built = false;
-  if (accel == PT_ACCEL_LBVH) {
+  bool built = sc->accel_preloaded;
+  if (!built) sc->accel = PT_ACCEL_SAH;
+  if (!built && accel == PT_ACCEL_LBVH) {
     float ms = 0;
     int too_deep = 0;
     int rc = build_bvh4_lbvh(h, sc->bvh, &ms, &too_deep);
@@ -298,7 +299,7 @@ int check_profile(const pt_profile *p) {
 }  // namespace
 
 namespace ptb {
-int scene_from_host(HostScene &&host, int device, pt_scene **out) {
+int scene_from_host(HostScene &&host, int device, pt_scene **out, Bvh4 *accel, int accel_kind) {
   if (!out) return PT_ERR_INVALID;
   *out = nullptr;
   std::string err = host.finalize();
@@ -306,10 +307,25 @@ int scene_from_host(HostScene &&host, int device, pt_scene **out) {
     set_error("%s", err.c_str());
     return PT_ERR_INVALID;
   }
+  if (accel && accel_kind >= 0) {
+    err = validate_bvh4(host, *accel);
+    if (!err.empty()) {
+      set_error("stored acceleration structure rejected: %s", err.c_str());
+      return PT_ERR_PARSE;
+    }
+  }
+  auto adopt = [&](pt_scene *sc) {
+    if (accel && accel_kind >= 0) {
+      sc->bvh = std::move(*accel);
+      sc->accel = accel_kind == PT_ACCEL_LBVH ? PT_ACCEL_LBVH : PT_ACCEL_SAH;
+      sc->accel_preloaded = true;
+    }
+  };
   if (device == -1) {  // host-only scene: loaders / generators / introspection without a GPU
     pt_scene *sc = new pt_scene();
     sc->host = std::move(host);
     sc->device = -1;
+    adopt(sc);
     *out = sc;
     return PT_OK;
   }
@@ -326,6 +342,7 @@ int scene_from_host(HostScene &&host, int device, pt_scene **out) {
   pt_scene *sc = new pt_scene();
   sc->host = std::move(host);
   sc->device = device;
+  adopt(sc);
   int rc = build_device_scene(sc);
   if (rc != PT_OK) {
     pt_scene_destroy(sc);
@@ -417,6 +434,23 @@ int pt_scene_accel_info(const pt_scene *sc, int *accel, double *build_ms, int *m
   if (build_ms) *build_ms = sc->build_ms;
   if (max_depth) *max_depth = sc->bvh.max_depth;
   return PT_OK;
+}
+
+int pt_scene_save_binary(const pt_scene *sc, const char *path, int with_accel) {
+  if (!sc || !path) {
+    set_error("null argument");
+    return PT_ERR_INVALID;
+  }
+  if (!with_accel) return save_isfb_file(path, sc->host, nullptr, -1);
+  if (!sc->bvh.nodes.empty()) return save_isfb_file(path, sc->host, &sc->bvh, sc->accel);
+  // host-only scene (device -1): the SAH builder is host code, so the tree can be written without a GPU
+  Bvh4 bvh;
+  build_bvh4(sc->host, bvh, (int)std::min(std::max(1u, std::thread::hardware_concurrency()), 32u));
+  if (bvh.max_depth * 3 + 4 > 96) {
+    set_error("acceleration structure too deep (%d levels) for the traversal stack", bvh.max_depth);
+    return PT_ERR_INVALID;
+  }
+  return save_isfb_file(path, sc->host, &bvh, PT_ACCEL_SAH);
 }
 
 int pt_scene_info(const pt_scene *sc, uint64_t *n_tris, uint64_t *n_prims, uint64_t *n_nodes, uint64_t *device_bytes) {

@@ -1,6 +1,7 @@
 // scene_host.hpp — host-side flat scene, the replacement of scene::internal::Scene
 // (reference scene/internal/mod.rs:26-51).  Owns copies of everything in a pt_scene_desc.
 #pragma once
+#include <cmath>
 #include <cstdint>
 #include <string>
 #include <vector>
@@ -59,8 +60,63 @@ struct Bvh4 {
   int max_depth = 0;
 };
 
-// Binned-SAH BVH2 build over triangles + spheres, collapsed to 4-wide.  Boxes are inflated
-// conservatively so a box cull can never drop a primitive Möller–Trumbore would accept.
+// ---- box margins shared by both builders (host SAH and device LBVH) --------------------------------------------
+// The contract of the traversal is brute-force semantics: a box cull must never drop a primitive that the reference's
+// f32 arithmetic (triangle.rs:37-82, model.rs:26-64) would accept.  That arithmetic accepts rays that miss the exact
+// primitive by a rounding-sized margin which grows with the distance |o - v0| to the ray origin, so the margins are
+// scaled by the scene, not by the local coordinate:
+//   D = |scene box diagonal| + |camera - box centre|   bounds origin-to-primitive distances (origins are the camera or
+//                                                      points on surfaces)
+//   S = largest |coordinate| of the scene box and the camera
+#if defined(__CUDACC__)
+#define PTB_HD __host__ __device__
+#else
+#define PTB_HD
+#endif
+PTB_HD inline float ray_distance_scale(const float lo[3], const float hi[3], const float cam[3]) {
+  float d2 = 0.f, c2 = 0.f;
+  for (int k = 0; k < 3; ++k) {
+    const float d = hi[k] - lo[k], c = cam[k] - 0.5f * (lo[k] + hi[k]);
+    d2 += d * d;
+    c2 += c * c;
+  }
+  const float D = sqrtf(d2) + sqrtf(c2);
+  return D == D && D < 1e30f ? D : 1.0f;
+}
+PTB_HD inline float coordinate_scale(const float lo[3], const float hi[3], const float cam[3]) {
+  float S = 0.f;
+  for (int k = 0; k < 3; ++k) S = fmaxf(S, fmaxf(fmaxf(fabsf(lo[k]), fabsf(hi[k])), fabsf(cam[k])));
+  return S < 1e30f ? S : 1.0f;
+}
+// Moller-Trumbore's barycentrics carry an error of a few ulp of |o - v0| |d| |e| / det; in space that lets a ray pass
+// a few ulp of D outside the edges through v0, and (|e1| + |e2|) / |e2 - e1| times as much outside the edge opposite
+// v0 (a thin triangle with its sharp corner at v0 leaks most).  p = the 9 position floats of the triangle.
+PTB_HD inline float triangle_leak_pad(const float *p, float D) {
+  float l1 = 0.f, l2 = 0.f, l3 = 0.f;
+  for (int k = 0; k < 3; ++k) {
+    const float a = p[3 + k] - p[k], b = p[6 + k] - p[k], c = b - a;
+    l1 += a * a;
+    l2 += b * b;
+    l3 += c * c;
+  }
+  float ratio = (sqrtf(l1) + sqrtf(l2)) / fmaxf(sqrtf(l3), 1e-30f);
+  ratio = fminf(fmaxf(ratio, 1.0f), 4096.0f);
+  return 2.4e-7f * D * ratio;
+}
+// The sphere test's discriminant carries an error of a few ulp of |o - c|^2: a tangent ray at distance h is accepted
+// while h^2 <= r^2 + that error.
+PTB_HD inline float sphere_box_radius(float radius, float D) {
+  const float r = fabsf(radius);
+  return sqrtf(r * r + 1.2e-7f * D * D) * 1.0001f + 1e-6f;
+}
+// Slab planes of a node box: the fused slab test (isect.cuh slab_fma) rounds at the magnitude of o*inv and plane*inv,
+// i.e. ~1 ulp of max(|plane|, |o|) in space.
+PTB_HD inline float plane_pad(float lo, float hi, float S) {
+  return fmaxf(fmaxf(fabsf(lo), fabsf(hi)), S) * 4e-6f + 1e-7f;
+}
+
+// Binned-SAH BVH2 build over triangles + spheres, collapsed to 4-wide.  Boxes carry the margins above
+// so a box cull can never drop a primitive Möller–Trumbore would accept.
 void build_bvh4(const HostScene &s, Bvh4 &out, int threads);
 // Largest number of triangles either builder puts into one leaf (default 2; $PT_B200_LEAF_TRIS in 1..8 for A/B runs).
 uint32_t bvh_max_leaf_tris();
@@ -69,5 +125,16 @@ uint32_t bvh_max_leaf_tris();
 // collapsed to the same 4-wide nodes.  *build_ms = device time of the build (CUDA events, upload excluded).
 // Returns PT_ERR_INVALID with *too_deep = 1 when the tree exceeds the traversal stack (caller falls back to SAH).
 int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_deep);
+
+// Revision of the box-inflation / node-layout rules both builders follow; an isfb accel section written under another
+// revision is ignored on load (isf_binary.cpp).
+constexpr uint32_t BVH_ACCEL_REV = 2;
+// isf_binary.cpp: the binary side-car of an isf scene, optionally with its BVH.
+bool is_isfb_file(const char *path);
+int save_isfb_file(const char *path, const HostScene &s, const Bvh4 *accel, int accel_kind);
+// *accel_kind = -1 when the file carries no usable accel section; `accel` may be null (scene only).
+int load_isfb_file(const char *path, HostScene &out, Bvh4 *accel, int *accel_kind);
+// "" when `b` is a complete, in-range, box-consistent BVH of `s` (s.finalize() must have run).
+std::string validate_bvh4(const HostScene &s, const Bvh4 &b);
 
 }  // namespace ptb

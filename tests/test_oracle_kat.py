@@ -92,3 +92,16 @@ def test_bvh_filter_equals_brute_force():
         a = sc.trace_closest(rr, brute=False)
         b = sc.trace_closest(rr, brute=True)
         assert np.array_equal(a, b), name
+
+
+def test_bvh_filter_keeps_edge_grazing_hits():
+    """Rays aimed within a few 1e-4 of the edges of thin triangles 150 units away: f32 Moller-Trumbore accepts rays
+    that pass slightly outside such a triangle, and the filter's boxes carry a margin for exactly that
+    (oracle/scene.cpp prim_box).  Without the margin this batch loses hits."""
+    import rays as R
+    sa, targets, cam, rng = R.edge_grazing_scene()
+    rr = R.edge_grazing_rays(targets, cam, rng, 1 << 16)
+    sc = oracle_lib.OracleScene(sa)
+    b = sc.trace_closest(rr, brute=True)
+    assert np.array_equal(sc.trace_closest(rr, brute=False), b)
+    assert 0.3 < float((b["prim_id"] >= 0).mean()) < 0.99

@@ -65,7 +65,7 @@ for accel, leaf in TREES:
         ray = np.concatenate([r["ray_o"], r["ray_d"]]).astype(np.float32)
         same_ray = bool((a["ray_o"] == r["ray_o"]).all() and (a["ray_d"] == r["ray_d"]).all())
         row = dict(path=int(p), bounce=b, same_ray=same_ray, ref=dict(prim=int(r["prim_id"]), t=float(r["t"])),
-                   got=dict(prim=int(a["prim_id"]), t=float(a["t"])), dist_o=float(np.linalg.norm(r["ray_o"])))
+                   got=dict(prim=int(a["prim_id"]), t=float(a["t"])), ray=[float(x).hex() for x in ray])
         for key, pid in (("mt_ref_prim", int(r["prim_id"])), ("mt_got_prim", int(a["prim_id"]))):
             if pid >= 0 and table[pid] >= 0:
                 hit = pkg.triangle_intersect(ray[None, :], pos[table[pid]][None, :])[0]
@@ -73,6 +73,6 @@ for accel, leaf in TREES:
                                 w=float(1.0 - hit["u"] - hit["v"]))
                 tri = pos[table[pid]].reshape(3, 3)
                 row[key]["extent"] = float(np.abs(tri.max(0) - tri.min(0)).max())
-                row[key]["coord"] = float(np.abs(tri).max())
+                row[key]["tri"] = [float(x).hex() for x in pos[table[pid]]]
         print(json.dumps(row), flush=True)
     sc.close()
