@@ -26,26 +26,47 @@ struct Box {
 // Exact extent of a primitive (pad = 0) or its extent plus what the f32 intersection arithmetic can accept beyond
 // it: Moller-Trumbore's barycentrics are a few ulp of |o - v0| off, which in space is a few ulp of the origin
 // distance D outside the edges through v0 and (|e1| + |e2|) / |e2 - e1| times that outside the opposite edge; the
-// sphere discriminant is a few ulp of |o - c|^2 off.  D bounds the distance from any ray origin (camera or surface
-// point) to any primitive.
-Box prim_box(const Scene &s, int32_t prim, float D) {
+// sphere discriminant is a few ulp of |o - c|^2 off.  D = reach(v0 or centre) bounds the distance from any ray origin
+// (the camera or a point on a surface, i.e. inside the scene box `all`) to the primitive; all == nullptr: exact extent.
+static float reach(const float *p, const Box &all, const float *cam) {
+  float f2 = 0, c2 = 0;
+  for (int k = 0; k < 3; ++k) {
+    float f = std::max(std::fabs(p[k] - all.lo[k]), std::fabs(p[k] - all.hi[k])), c = p[k] - cam[k];
+    f2 += f * f;
+    c2 += c * c;
+  }
+  float D = std::sqrt(std::max(f2, c2));
+  return D < 1e30f ? D : 1.0f;
+}
+
+Box prim_box(const Scene &s, int32_t prim, const Box *all) {
   Box b;
   b.reset();
   if (prim >= 0) {
     const float *p = &s.pos[(size_t)prim * 9];
     for (int k = 0; k < 3; ++k) b.grow(p + k * 3);
+    if (!all) return b;
+    const float D = reach(p, *all, &s.camera[12]);
     float l1 = 0, l2 = 0, l3 = 0;
     for (int k = 0; k < 3; ++k) {
       float e1 = p[3 + k] - p[k], e2 = p[6 + k] - p[k], e3 = e2 - e1;
       l1 += e1 * e1; l2 += e2 * e2; l3 += e3 * e3;
     }
-    float ratio = (std::sqrt(l1) + std::sqrt(l2)) / std::max(std::sqrt(l3), 1e-30f);
-    float pad = 2.4e-7f * D * std::min(std::max(ratio, 1.0f), 4096.0f);
+    // a triangle whose doubled area is below 1e-6 / 8 is never accepted (|det| < 1e-6, triangle.rs:49) for |d| <= 8
+    float e1[3] = {p[3] - p[0], p[4] - p[1], p[5] - p[2]}, e2[3] = {p[6] - p[0], p[7] - p[1], p[8] - p[2]};
+    float cx = e1[1] * e2[2] - e1[2] * e2[1], cy = e1[2] * e2[0] - e1[0] * e2[2], cz = e1[0] * e2[1] - e1[1] * e2[0];
+    float ratio = 1.0f;
+    if (std::sqrt(cx * cx + cy * cy + cz * cz) * 8.0f >= 1e-6f)
+      ratio = std::min(std::max((std::sqrt(l1) + std::sqrt(l2)) / std::max(std::sqrt(l3), 1e-30f), 1.0f), 4096.0f);
+    float pad = 2.4e-7f * D * ratio;
     for (int k = 0; k < 3; ++k) { b.lo[k] -= pad; b.hi[k] += pad; }
   } else {
     const pt_model &m = s.models[~prim];
     float r = std::fabs(m.radius);
-    r = std::sqrt(r * r + 1.2e-7f * D * D) * 1.0001f + 1e-6f;
+    if (all) {
+      const float D = reach(m.center, *all, &s.camera[12]);
+      r = std::sqrt(r * r + 1.2e-7f * D * D) * 1.0001f + 1e-6f;
+    }
     for (int k = 0; k < 3; ++k) { b.lo[k] = m.center[k] - r; b.hi[k] = m.center[k] + r; }
   }
   return b;
@@ -135,17 +156,9 @@ void build_bvh(Scene &s) {
   std::vector<float> cent(n * 3);
   Box all;
   all.reset();
-  for (size_t i = 0; i < n; ++i) all.grow(prim_box(s, s.bvh_prims[i], 0.0f));
-  float diag = 0, camd = 0;
-  for (int k = 0; k < 3; ++k) {
-    float e = all.hi[k] - all.lo[k], c = s.camera[12 + k] - 0.5f * (all.lo[k] + all.hi[k]);
-    diag += e * e;
-    camd += c * c;
-  }
-  float D = std::sqrt(diag) + std::sqrt(camd);
-  if (!(D < 1e30f)) D = 1.0f;
+  for (size_t i = 0; i < n; ++i) all.grow(prim_box(s, s.bvh_prims[i], nullptr));
   for (size_t i = 0; i < n; ++i) {
-    boxes[i] = prim_box(s, s.bvh_prims[i], D);
+    boxes[i] = prim_box(s, s.bvh_prims[i], &all);
     for (int k = 0; k < 3; ++k) cent[i * 3 + k] = 0.5f * (boxes[i].lo[k] + boxes[i].hi[k]);
   }
   s.nodes.reserve(n);

@@ -155,6 +155,11 @@ uint32_t bvh_max_leaf_tris() {
   return 2;
 }
 
+float bvh_margin_scale() {
+  if (const char *e = std::getenv("PT_B200_MARGIN_SCALE")) return std::max(0.0f, (float)std::atof(e));
+  return 1.0f;
+}
+
 namespace {
 
 inline Box inflate(const Box &b, float S) {
@@ -193,14 +198,16 @@ void build_bvh4(const HostScene &s, Bvh4 &out, int threads) {
   }
   // margins (scene_host.hpp): primitive boxes grow by what the f32 intersection arithmetic can leak
   const float *cam = &s.camera[12];
-  const float D = ray_distance_scale(scene.lo, scene.hi, cam), S = coordinate_scale(scene.lo, scene.hi, cam);
+  const float ms = bvh_margin_scale();
+  const float S = ms * coordinate_scale(scene.lo, scene.hi, cam);
   for (uint32_t t = 0; t < nt; ++t) {
-    const float e = triangle_leak_pad(&s.pos[(size_t)t * 9], D);
+    const float *p = &s.pos[(size_t)t * 9];
+    const float e = triangle_leak_pad(p, ms * origin_reach(p, scene.lo, scene.hi, cam));
     for (int a = 0; a < 3; ++a) { B.pbox[t].lo[a] -= e; B.pbox[t].hi[a] += e; }
   }
   for (uint32_t k = 0; k < ns; ++k) {
     const pt_model &m = s.models[s.sphere_models[k]];
-    const float r = sphere_box_radius(m.radius, D);
+    const float r = sphere_box_radius(m.radius, ms * origin_reach(m.center, scene.lo, scene.hi, cam));
     for (int a = 0; a < 3; ++a) { B.pbox[nt + k].lo[a] = m.center[a] - r; B.pbox[nt + k].hi[a] = m.center[a] + r; }
   }
   B.order.resize(n);

@@ -109,32 +109,32 @@ __global__ void __launch_bounds__(256) k_prim_boxes(const float *__restrict__ po
   }
 }
 
-struct SceneScale { float D, S; };
-__device__ __forceinline__ SceneScale scene_scale(const uint32_t *__restrict__ cbounds, float3 cam) {
-  const float lo[3] = {o2f(cbounds[8]), o2f(cbounds[9]), o2f(cbounds[10])};
-  const float hi[3] = {o2f(cbounds[11]), o2f(cbounds[12]), o2f(cbounds[13])};
-  const float c[3] = {cam.x, cam.y, cam.z};
-  return SceneScale{ray_distance_scale(lo, hi, c), coordinate_scale(lo, hi, c)};
+struct SceneBox { float lo[3], hi[3], cam[3], scale; };
+__device__ __forceinline__ SceneBox scene_box(const uint32_t *__restrict__ cbounds, float4 cam) {
+  return SceneBox{{o2f(cbounds[8]), o2f(cbounds[9]), o2f(cbounds[10])},
+                  {o2f(cbounds[11]), o2f(cbounds[12]), o2f(cbounds[13])},
+                  {cam.x, cam.y, cam.z}, cam.w};  // w = bvh_margin_scale()
 }
 
 // ---- 1b. margins of the primitive boxes (scene_host.hpp): what the f32 intersection arithmetic can leak ----
 __global__ void __launch_bounds__(256) k_pad_boxes(const float *__restrict__ pos9, uint32_t nt,
                                                    const float4 *__restrict__ spheres, uint32_t ns,
                                                    float4 *__restrict__ blo, float4 *__restrict__ bhi,
-                                                   const uint32_t *__restrict__ cbounds, float3 cam) {
+                                                   const uint32_t *__restrict__ cbounds, float4 cam) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nt + ns) return;
-  const float D = scene_scale(cbounds, cam).D;
+  const SceneBox sb = scene_box(cbounds, cam);
   if (i < nt) {
     float p[9];
     for (int k = 0; k < 9; ++k) p[k] = pos9[(size_t)i * 9 + k];
-    const float e = triangle_leak_pad(p, D);
+    const float e = triangle_leak_pad(p, sb.scale * origin_reach(p, sb.lo, sb.hi, sb.cam));
     float4 lo = blo[i], hi = bhi[i];
     blo[i] = make_float4(lo.x - e, lo.y - e, lo.z - e, 0.f);
     bhi[i] = make_float4(hi.x + e, hi.y + e, hi.z + e, 0.f);
   } else {
     const float4 s = spheres[i - nt];
-    const float r = sphere_box_radius(s.w, D);
+    const float c[3] = {s.x, s.y, s.z};
+    const float r = sphere_box_radius(s.w, sb.scale * origin_reach(c, sb.lo, sb.hi, sb.cam));
     blo[i] = make_float4(s.x - r, s.y - r, s.z - r, 0.f);
     bhi[i] = make_float4(s.x + r, s.y + r, s.z + r, 0.f);
   }
@@ -411,7 +411,7 @@ struct CollapseArgs {
   uint32_t *node_count;
   uint32_t node_cap;
   const uint32_t *cbounds;       // scene box (k_prim_boxes) for the slab-plane margin
-  float3 cam;
+  float4 cam;                    // camera position, w = bvh_margin_scale()
 };
 
 // A radix-tree node is emitted as one leaf when it holds <= max_leaf primitives, all triangles (spheres sit alone).
@@ -453,7 +453,8 @@ __global__ void __launch_bounds__(128) k_collapse(const CollapseArgs A, const ui
   const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
   if (w >= n_in) return;
   const uint2 item = work_in[w];  // x = radix-tree node (internal, not a leaf), y = 4-wide node index
-  const float S = scene_scale(A.cbounds, A.cam).S;
+  const SceneBox sb = scene_box(A.cbounds, A.cam);
+  const float S = sb.scale * coordinate_scale(sb.lo, sb.hi, sb.cam);
   uint32_t kids[4];
   int nk = 2;
   kids[0] = A.left[item.x];
@@ -576,7 +577,7 @@ int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_dee
   // [0..5] centroid bounds, [8..13] scene box, both as order-preserving uints (min slots start at the maximum)
   const uint32_t init_cb[16] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u, 0u, 0u,
                                 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u, 0u, 0u};
-  const float3 cam = make_float3(s.camera[12], s.camera[13], s.camera[14]);
+  const float4 cam = make_float4(s.camera[12], s.camera[13], s.camera[14], bvh_margin_scale());
   LB_TRY(cudaMemcpyAsync(cb, init_cb, sizeof init_cb, cudaMemcpyHostToDevice, st));
   const uint32_t g256 = (n + 255) / 256;
   k_prim_boxes<<<g256, 256, 0, st>>>(d_pos, nt, d_sph, ns, blo, bhi, cb);

@@ -65,22 +65,22 @@ struct Bvh4 {
 // f32 arithmetic (triangle.rs:37-82, model.rs:26-64) would accept.  That arithmetic accepts rays that miss the exact
 // primitive by a rounding-sized margin which grows with the distance |o - v0| to the ray origin, so the margins are
 // scaled by the scene, not by the local coordinate:
-//   D = |scene box diagonal| + |camera - box centre|   bounds origin-to-primitive distances (origins are the camera or
-//                                                      points on surfaces)
+//   D(p) = max(|p - farthest corner of the scene box|, |p - camera|)   bounds |o - p| for every origin the renderer
+//                                                      uses (the camera or a point on a surface), p = v0 / centre
 //   S = largest |coordinate| of the scene box and the camera
 #if defined(__CUDACC__)
 #define PTB_HD __host__ __device__
 #else
 #define PTB_HD
 #endif
-PTB_HD inline float ray_distance_scale(const float lo[3], const float hi[3], const float cam[3]) {
-  float d2 = 0.f, c2 = 0.f;
+PTB_HD inline float origin_reach(const float p[3], const float lo[3], const float hi[3], const float cam[3]) {
+  float f2 = 0.f, c2 = 0.f;
   for (int k = 0; k < 3; ++k) {
-    const float d = hi[k] - lo[k], c = cam[k] - 0.5f * (lo[k] + hi[k]);
-    d2 += d * d;
+    const float f = fmaxf(fabsf(p[k] - lo[k]), fabsf(p[k] - hi[k])), c = p[k] - cam[k];
+    f2 += f * f;
     c2 += c * c;
   }
-  const float D = sqrtf(d2) + sqrtf(c2);
+  const float D = sqrtf(fmaxf(f2, c2));
   return D == D && D < 1e30f ? D : 1.0f;
 }
 PTB_HD inline float coordinate_scale(const float lo[3], const float hi[3], const float cam[3]) {
@@ -92,15 +92,24 @@ PTB_HD inline float coordinate_scale(const float lo[3], const float hi[3], const
 // a few ulp of D outside the edges through v0, and (|e1| + |e2|) / |e2 - e1| times as much outside the edge opposite
 // v0 (a thin triangle with its sharp corner at v0 leaks most).  p = the 9 position floats of the triangle.
 PTB_HD inline float triangle_leak_pad(const float *p, float D) {
-  float l1 = 0.f, l2 = 0.f, l3 = 0.f;
+  float l1 = 0.f, l2 = 0.f, l3 = 0.f, e1[3], e2[3];
   for (int k = 0; k < 3; ++k) {
-    const float a = p[3 + k] - p[k], b = p[6 + k] - p[k], c = b - a;
-    l1 += a * a;
-    l2 += b * b;
+    e1[k] = p[3 + k] - p[k];
+    e2[k] = p[6 + k] - p[k];
+    const float c = e2[k] - e1[k];
+    l1 += e1[k] * e1[k];
+    l2 += e2[k] * e2[k];
     l3 += c * c;
   }
-  float ratio = (sqrtf(l1) + sqrtf(l2)) / fmaxf(sqrtf(l3), 1e-30f);
-  ratio = fminf(fmaxf(ratio, 1.0f), 4096.0f);
+  // |det| = |e1 . (d x e2)| <= |d| |e1 x e2| and triangle.rs:49 rejects |det| < 1e-6: a triangle whose doubled area
+  // is below 1e-6 / 8 cannot be hit by any ray with |d| <= 8 (the renderer's are unit length), so it needs no
+  // leak margin however thin it is (sphere poles and other collapsed triangles would otherwise get the largest one)
+  const float cx = e1[1] * e2[2] - e1[2] * e2[1], cy = e1[2] * e2[0] - e1[0] * e2[2], cz = e1[0] * e2[1] - e1[1] * e2[0];
+  float ratio = 1.0f;
+  if (sqrtf(cx * cx + cy * cy + cz * cz) * 8.0f >= 1e-6f) {
+    ratio = (sqrtf(l1) + sqrtf(l2)) / fmaxf(sqrtf(l3), 1e-30f);
+    ratio = fminf(fmaxf(ratio, 1.0f), 4096.0f);
+  }
   return 2.4e-7f * D * ratio;
 }
 // The sphere test's discriminant carries an error of a few ulp of |o - c|^2: a tangent ray at distance h is accepted
@@ -109,11 +118,15 @@ PTB_HD inline float sphere_box_radius(float radius, float D) {
   const float r = fabsf(radius);
   return sqrtf(r * r + 1.2e-7f * D * D) * 1.0001f + 1e-6f;
 }
-// Slab planes of a node box: the fused slab test (isect.cuh slab_fma) rounds at the magnitude of o*inv and plane*inv,
-// i.e. ~1 ulp of max(|plane|, |o|) in space.
+// Slab planes of a node box: the fused slab test (isect.cuh slab_fma) evaluates fma(plane, inv, -(o * inv)).  The
+// roundings that scale with t are absorbed by the widened exit (tf * 1.000002) and by 4e-6 |plane|; the rounding of
+// the product o * inv is ~1 ulp of |o| in space whatever t is (a wall at x = 0.01 seen from x = 50), hence 8 ulp of S.
 PTB_HD inline float plane_pad(float lo, float hi, float S) {
-  return fmaxf(fmaxf(fabsf(lo), fabsf(hi)), S) * 4e-6f + 1e-7f;
+  return fmaxf(fabsf(lo), fabsf(hi)) * 4e-6f + S * 4.8e-7f + 1e-7f;
 }
+
+// A/B knob: $PT_B200_MARGIN_SCALE multiplies D and S (0 = the coordinate-relative rules of revision 1).
+float bvh_margin_scale();
 
 // Binned-SAH BVH2 build over triangles + spheres, collapsed to 4-wide.  Boxes carry the margins above
 // so a box cull can never drop a primitive Möller–Trumbore would accept.
