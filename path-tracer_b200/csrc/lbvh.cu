@@ -8,6 +8,7 @@
 
 #include <math_constants.h>
 
+#include <algorithm>
 #include <cfloat>
 #include <cmath>
 #include <cstdio>
@@ -59,15 +60,21 @@ __host__ __device__ __forceinline__ float o2f(uint32_t o) {
 #endif
 }
 
-// ---- 1. primitive boxes (triangles then spheres) + centroid bounds ----
+// ---- 1. primitive boxes (triangles then spheres) + centroid bounds + scene box ----
+// Grid-stride: every thread keeps running bounds in registers; one warp shuffle reduction, one shared-memory
+// reduction per block and 12 atomics per block at the end (one atomic set per warp of 32 primitives, all on the same
+// cache line, cost more than the rest of the kernel on 20 M triangles).
 __global__ void __launch_bounds__(256) k_prim_boxes(const float *__restrict__ pos9, uint32_t nt,
                                                     const float4 *__restrict__ spheres, uint32_t ns,
                                                     float4 *__restrict__ blo, float4 *__restrict__ bhi,
-                                                    uint32_t *__restrict__ cbounds /* 6 ordered uints */) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x, n = nt + ns;
-  float c[3] = {0, 0, 0}, b[6] = {0, 0, 0, 0, 0, 0};
-  const bool live = i < n;
-  if (live) {
+                                                    uint32_t *__restrict__ cbounds /* [0..5] centroid, [8..13] box */) {
+  const uint32_t n = nt + ns;
+  float acc[12];  // centroid min xyz, centroid max xyz, box min xyz, box max xyz
+  for (int k = 0; k < 3; ++k) {
+    acc[k] = acc[6 + k] = FLT_MAX;
+    acc[3 + k] = acc[9 + k] = -FLT_MAX;
+  }
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     float lo[3], hi[3];
     if (i < nt) {
       const float *p = pos9 + (size_t)i * 9;
@@ -84,27 +91,34 @@ __global__ void __launch_bounds__(256) k_prim_boxes(const float *__restrict__ po
     blo[i] = make_float4(lo[0], lo[1], lo[2], 0.f);
     bhi[i] = make_float4(hi[0], hi[1], hi[2], 0.f);
     for (int k = 0; k < 3; ++k) {
-      c[k] = 0.5f * (lo[k] + hi[k]);
-      b[k] = lo[k];
-      b[3 + k] = hi[k];
+      const float c = 0.5f * (lo[k] + hi[k]);
+      acc[k] = fminf(acc[k], c);
+      acc[3 + k] = fmaxf(acc[3 + k], c);
+      acc[6 + k] = fminf(acc[6 + k], lo[k]);
+      acc[9 + k] = fmaxf(acc[9 + k], hi[k]);
     }
   }
-  // warp-reduce the centroid bounds (Morton normalisation) and the scene box (margins), then one atomic pair per
-  // warp and axis for each
-  for (int k = 0; k < 3; ++k) {
-    float mn = live ? c[k] : FLT_MAX, mx = live ? c[k] : -FLT_MAX;
-    float bn = live ? b[k] : FLT_MAX, bx = live ? b[3 + k] : -FLT_MAX;
+  __shared__ float red[8][12];
+  for (int k = 0; k < 12; ++k) {
+    const bool is_min = k < 3 || (k >= 6 && k < 9);
+    float v = acc[k];
     for (int o = 16; o; o >>= 1) {
-      mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
-      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-      bn = fminf(bn, __shfl_xor_sync(0xffffffffu, bn, o));
-      bx = fmaxf(bx, __shfl_xor_sync(0xffffffffu, bx, o));
+      const float w = __shfl_xor_sync(0xffffffffu, v, o);
+      v = is_min ? fminf(v, w) : fmaxf(v, w);
     }
-    if ((threadIdx.x & 31) == 0 && mn <= mx) {
-      atomicMin(&cbounds[k], f2o(mn));
-      atomicMax(&cbounds[3 + k], f2o(mx));
-      atomicMin(&cbounds[8 + k], f2o(bn));
-      atomicMax(&cbounds[11 + k], f2o(bx));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5][k] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 12) {
+    const int k = threadIdx.x;
+    const bool is_min = k < 3 || (k >= 6 && k < 9);
+    float v = red[0][k];
+    for (int w = 1; w < 8; ++w) v = is_min ? fminf(v, red[w][k]) : fmaxf(v, red[w][k]);
+    uint32_t *dst = &cbounds[k < 6 ? k : k + 2];
+    if (is_min) {
+      if (v < FLT_MAX) atomicMin(dst, f2o(v));
+    } else if (v > -FLT_MAX) {
+      atomicMax(dst, f2o(v));
     }
   }
 }
@@ -580,7 +594,7 @@ int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_dee
   const float4 cam = make_float4(s.camera[12], s.camera[13], s.camera[14], bvh_margin_scale());
   LB_TRY(cudaMemcpyAsync(cb, init_cb, sizeof init_cb, cudaMemcpyHostToDevice, st));
   const uint32_t g256 = (n + 255) / 256;
-  k_prim_boxes<<<g256, 256, 0, st>>>(d_pos, nt, d_sph, ns, blo, bhi, cb);
+  k_prim_boxes<<<std::min(g256, 148u * 16u), 256, 0, st>>>(d_pos, nt, d_sph, ns, blo, bhi, cb);
   k_morton<<<g256, 256, 0, st>>>(blo, bhi, n, cb, keys, vals);
   k_pad_boxes<<<g256, 256, 0, st>>>(d_pos, nt, d_sph, ns, blo, bhi, cb, cam);  // symmetric: centroids unchanged
   int rc = radix_sort_pairs(keys, vals, keys2, vals2, n, 32, counts, scan_tmp, st);
