@@ -100,17 +100,21 @@ struct ClosestTrav {
     if (t0 < CUDART_INF_F) cur = r0;
     else pop(stk);
   }
-  // Precondition: at_leaf().  Tests ONE primitive of the leaf (uniform cost per step); a triangle leaf with more
-  // primitives left stays current (first+1, count-1 == ref + 7).
-  __device__ __forceinline__ void leaf_step(const DevScene &S, const ClosestStack &stk) {
-    if (cur & 0x40000000u) {
-      leaf_closest(S, cur, r, t_lo, id_lo, st, t_prune, pre);
-      pop(stk);
-      return;
+  // Tests ONE primitive of leaf `ref` (uniform cost per step).  Returns true when the leaf has more primitives, with
+  // `ref` advanced to the rest (first+1, count-1 == ref + 7).
+  __device__ __forceinline__ bool leaf_step_ref(const DevScene &S, uint32_t &ref) {
+    if (ref & 0x40000000u) {
+      leaf_closest(S, ref, r, t_lo, id_lo, st, t_prune, pre);
+      return false;
     }
-    leaf_closest(S, cur & ~7u, r, t_lo, id_lo, st, t_prune, pre);  // count-1 = 0: the first primitive only
-    if (cur & 7u) cur += 7u;
-    else pop(stk);
+    leaf_closest(S, ref & ~7u, r, t_lo, id_lo, st, t_prune, pre);  // count-1 = 0: the first primitive only
+    if (!(ref & 7u)) return false;
+    ref += 7u;
+    return true;
+  }
+  // Precondition: at_leaf().  A triangle leaf with more primitives left stays current.
+  __device__ __forceinline__ void leaf_step(const DevScene &S, const ClosestStack &stk) {
+    if (!leaf_step_ref(S, cur)) pop(stk);
   }
 };
 
