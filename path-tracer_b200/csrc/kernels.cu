@@ -129,9 +129,6 @@ __global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene
 #ifndef PTB_PF_L1
 #define PTB_PF_L1 0
 #endif
-#ifndef PTB_SPEC_LEAF
-#define PTB_SPEC_LEAF 0
-#endif
 __device__ __forceinline__ void prefetch_l2(const void *p) {
 #if PTB_PF_L1
   asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
@@ -256,9 +253,6 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
   NodeOrder no{};
   ClosestStack stk;
   uint32_t q = NONE, slot = 0, alpha_j = 0;
-#if PTB_SPEC_LEAF
-  uint32_t pend = NONE;  // NONE == ClosestTrav::DONE: never a leaf reference
-#endif
   bool recorded = false;
   tv.cur = ClosestTrav::DONE;
 #if PTB_FETCH_AHEAD_EXTEND
@@ -294,35 +288,12 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
     for (;;) {
       const bool has = q != NONE;
       if (has && tv.at_inner()) tv.node_step(S, no, stk);
-#if PTB_SPEC_LEAF
-      // Speculative traversal (Aila & Laine 2009): a lane that reaches a leaf while the warp is not in its primitive
-      // phase parks the leaf in `pend` and goes on with the next stack entry instead of idling; the parked leaf is
-      // tested first when the phase comes.  Nodes visited meanwhile are tested against a bound the parked leaf might
-      // have tightened, so some of those visits are wasted.
-      if (has && pend == NONE && tv.at_leaf()) {
-        pend = tv.cur;
-        tv.pop(stk);
-      }
-      const bool leaf = has && (pend != NONE || tv.at_leaf());
-      const uint32_t m_leaf = __ballot_sync(0xffffffffu, leaf);
-      const uint32_t m_inner = __ballot_sync(0xffffffffu, has && tv.at_inner());
-      if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) {
-        if (pend != NONE) {
-          if (!tv.leaf_step_ref(S, pend)) pend = NONE;
-        } else {
-          tv.leaf_step(S, stk);
-        }
-      }
-      if (has && tv.cur == ClosestTrav::DONE && pend == NONE) {
-        bool done = true;
-#else
       const bool leaf = has && tv.at_leaf();
       const uint32_t m_leaf = __ballot_sync(0xffffffffu, leaf);
       const uint32_t m_inner = __ballot_sync(0xffffffffu, has && tv.at_inner());
       if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) tv.leaf_step(S, stk);
       if (has && tv.cur == ClosestTrav::DONE) {
         bool done = true;
-#endif
         if (tv.st.idx >= 0) {
           // record the examined hit: it is shaded unless a later hit of the alpha walk replaces it (mod.rs:188-205)
           st_wave(&W.hit[q], make_float4(tv.st.best_t, tv.st.u, tv.st.v, __int_as_float(tv.st.idx)));
