@@ -33,10 +33,6 @@ struct ClosestStack {
 #endif
 };
 
-#ifndef PTB_PF_NODE
-#define PTB_PF_NODE 0
-#endif
-
 struct ClosestTrav {
   Ray r;
   RayPre pre;
@@ -100,16 +96,7 @@ struct ClosestTrav {
     PTB_CSWAP(t1, r1, t2, r2)
     if (t3 < CUDART_INF_F) stk.put(sp++, t3, r3);
     if (t2 < CUDART_INF_F) stk.put(sp++, t2, r2);
-    if (t1 < CUDART_INF_F) {
-      stk.put(sp++, t1, r1);
-#if PTB_PF_NODE
-      // the second-nearest child is what this lane visits next unless the nearest subtree yields a closer hit
-      if (!(r1 & 0x80000000u)) asm volatile("prefetch.global.L1 [%0];" ::"l"(S.nodes + r1));
-#if PTB_PF_NODE > 1
-      else if (!(r1 & 0x40000000u)) asm volatile("prefetch.global.L1 [%0];" ::"l"(S.tris + ((r1 & 0x3FFFFFFFu) >> 3)));
-#endif
-#endif
-    }
+    if (t1 < CUDART_INF_F) stk.put(sp++, t1, r1);
     if (t0 < CUDART_INF_F) cur = r0;
     else pop(stk);
   }
