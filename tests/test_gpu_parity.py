@@ -596,6 +596,52 @@ def test_full_size_foliage_properties():
     assert st["alpha_recasts"] > 0 and st["shadow_rays"] > 0 and st["extend_rays"] >= 480 * 270 * 4
 
 
+def test_full_size_console_properties():
+    """BASELINE.json configs[2] geometry (the headline workload, 1 M triangles) at full size."""
+    sc = pt.Scene.synthetic("console", 1000000, seed=3)
+    sa = sc.arrays()
+    assert all(m["type"] == 0 for m in sa.models)  # meshes only: global prim id == triangle index
+    rr = R.random_rays(sa, 1 << 18, seed=22)
+    hits = sc.trace_closest(rr)
+    hit = hits["prim_id"] >= 0
+    assert 0.05 < hit.mean() < 1.0
+    # (a) a reported hit is a real one, bit for bit
+    single = pt.triangle_intersect(rr[hit], sa.tri_pos[hits["prim_id"][hit]])
+    for f in ("t", "u", "v"):
+        assert np.array_equal(single[f], hits[f][hit]), f
+    # (b) the tree is only a filter: the GPU-built LBVH returns the same records
+    pt.set_accel_builder("lbvh")
+    try:
+        sc2 = pt.Scene.synthetic("console", 1000000, seed=3)
+    finally:
+        pt.set_accel_builder("sah")
+    assert sc2.accel_info()["accel"] == "lbvh"
+    assert hits.tobytes() == sc2.trace_closest(rr).tobytes()
+    # (c) nothing closer: brute force of a few rays against every triangle of the scene through pt_triangle_intersect
+    n_tri = len(sa.tri_pos)
+    pick = np.concatenate([np.nonzero(hit)[0][:12], np.nonzero(~hit)[0][:4]])
+    for k in pick:
+        every = pt.triangle_intersect(np.broadcast_to(rr[k], (n_tri, 6)), sa.tri_pos)
+        ok = every["prim_id"] >= 0
+        if hits["prim_id"][k] < 0:
+            assert not ok.any()
+            continue
+        t = np.where(ok, every["t"], np.inf)
+        best = np.lexsort((np.arange(n_tri), t))[0]  # smallest (t, id), the order of utils.rs:13-19
+        assert best == hits["prim_id"][k] and t[best] == hits["t"][k]
+    # (d) disjoint sample subsets sum to the full render
+    import torch
+    prof = pt.Profile(width=480, height=270, samples=4, bounces=5)
+    full = torch.zeros(270, 480, 3, device="cuda")
+    st = pt.render_accum_device(sc, prof, full.data_ptr())
+    parts = torch.zeros_like(full)
+    for g in range(2):
+        pt.render_accum_device(sc, prof, parts.data_ptr(), sample_begin=g, sample_stride=2, n_samples=2)
+    torch.cuda.synchronize()
+    assert torch.isfinite(full).all() and torch.allclose(full, parts, rtol=1e-4, atol=1e-5)
+    assert st["shadow_rays"] > 0 and st["extend_rays"] >= 480 * 270 * 4
+
+
 # ---------------------------------------------------------------- box margins: rays that graze triangle edges
 @pytest.mark.parametrize("accel", ["sah", "lbvh"])
 def test_edge_grazing_rays_match_brute_force(accel):
