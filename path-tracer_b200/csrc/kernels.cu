@@ -292,6 +292,9 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
       const uint32_t m_leaf = __ballot_sync(0xffffffffu, leaf);
       const uint32_t m_inner = __ballot_sync(0xffffffffu, has && tv.at_inner());
       if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) tv.leaf_step(S, stk);
+#if PTB_MERGED_POP
+      if (has && tv.cur == ClosestTrav::NEED_POP) tv.pop(stk);
+#endif
       if (has && tv.cur == ClosestTrav::DONE) {
         bool done = true;
         if (tv.st.idx >= 0) {

@@ -33,6 +33,10 @@ struct ClosestStack {
 #endif
 };
 
+#ifndef PTB_MERGED_POP
+#define PTB_MERGED_POP 0
+#endif
+
 struct ClosestTrav {
   Ray r;
   RayPre pre;
@@ -70,8 +74,20 @@ struct ClosestTrav {
     sp = 0;
   }
   static constexpr uint32_t DONE = 0xFFFFFFFFu;
+  // PTB_MERGED_POP: node_step / leaf_step leave NEED_POP instead of popping, and the kernel pops once per iteration
+  // for every lane that needs it: the pop loop (entries behind the current best hit are skipped lazily) then runs with
+  // the lanes of both paths together instead of once per call site with 2-5 lanes each.
+  static constexpr uint32_t NEED_POP = 0xFFFFFFFEu;
   __device__ __forceinline__ bool at_inner() const { return !(cur & 0x80000000u); }
-  __device__ __forceinline__ bool at_leaf() const { return (cur & 0x80000000u) && cur != DONE; }
+  __device__ __forceinline__ bool at_leaf() const { return (cur & 0x80000000u) && cur < NEED_POP; }
+  __device__ __forceinline__ void after(const ClosestStack &stk) {
+#if PTB_MERGED_POP
+    (void)stk;
+    cur = NEED_POP;
+#else
+    pop(stk);
+#endif
+  }
 
   __device__ __forceinline__ void pop(const ClosestStack &stk) {
     while (sp > 0) {
@@ -98,7 +114,7 @@ struct ClosestTrav {
     if (t2 < CUDART_INF_F) stk.put(sp++, t2, r2);
     if (t1 < CUDART_INF_F) stk.put(sp++, t1, r1);
     if (t0 < CUDART_INF_F) cur = r0;
-    else pop(stk);
+    else after(stk);
   }
   // Tests ONE primitive of leaf `ref` (uniform cost per step).  Returns true when the leaf has more primitives, with
   // `ref` advanced to the rest (first+1, count-1 == ref + 7).
@@ -114,7 +130,7 @@ struct ClosestTrav {
   }
   // Precondition: at_leaf().  A triangle leaf with more primitives left stays current.
   __device__ __forceinline__ void leaf_step(const DevScene &S, const ClosestStack &stk) {
-    if (!leaf_step_ref(S, cur)) pop(stk);
+    if (!leaf_step_ref(S, cur)) after(stk);
   }
 };
 
