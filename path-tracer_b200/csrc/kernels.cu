@@ -226,7 +226,7 @@ __device__ __forceinline__ void st_wave(float4 *p, float4 v) {
 }
 
 #ifndef PTB_REFILL_T
-#define PTB_REFILL_T 24
+#define PTB_REFILL_T 18
 #endif
 #ifndef PTB_LEAF_T
 #define PTB_LEAF_T 12

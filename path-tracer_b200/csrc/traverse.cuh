@@ -152,9 +152,19 @@ struct ShadowTrav {
     pv = v;
     t_max = CUDART_INF_F;
     if (lim >= 0.0f) {
+#if PTB_FAST_INV
+      // a culling bound with a 2e-4 allowance: approximate square roots and division are enough (the exact
+      // `distance > limit` test of mod.rs:319-330 is applied per hit in leaf_step)
+      const V3 b = ray.o - p;
+      const float l2 = dot3(ray.d, ray.d);
+      float bias;
+      asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(bias) : "f"(dot3(b, b)));
+      t_max = l2 > 0.f ? (lim + bias * 1.000001f) * rsqrtf(l2) * 1.0002f + 1e-6f : CUDART_INF_F;
+#else
       float len = length3(ray.d);
       float bias = length3(ray.o - p);
       t_max = len > 0.f ? (lim + bias) / len * 1.0002f + 1e-6f : CUDART_INF_F;
+#endif
     }
     tr = 1.0f;
     cur = 0;
