@@ -619,10 +619,12 @@ int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t
   std::lock_guard<std::mutex> lock(sc->mu);
   cudaStream_t st = (cudaStream_t)stream;
   const uint64_t npix = (uint64_t)prof->width * prof->height;
-  // wave size: as many samples per pixel as fit ~64 Mi paths.  Large waves keep the late-bounce queues (a few % of the
-  // paths) big enough to fill 148 SMs and amortise every launch's tail: 8 Mi -> 64 Mi paths is +21 % throughput on the
-  // console workload.  State is ~292 B per path (19.6 GB at 64 Mi), capped to half of the free device memory.
-  uint64_t target_paths = 64ull << 20;
+  // wave size: as many samples per pixel as fit ~256 Mi paths.  Large waves keep the late-bounce queues (a few % of the
+  // paths) big enough to fill 148 SMs and amortise every launch's tail: on the console workload 8 Mi -> 64 Mi paths is
+  // +21 % throughput, 64 Mi -> 128 Mi -> 256 Mi another +2.2 % / +3.5 % (kernel time 93.9 / 91.9 / 90.6 ms per frame).
+  // State is ~292 B per path (78 GB at 256 Mi: this is what 180 GB of HBM are for), capped to half of the free device
+  // memory and to the paths the call actually renders.
+  uint64_t target_paths = 256ull << 20;
   if (const char *e = std::getenv("PT_B200_WAVE_PATHS")) target_paths = std::max<uint64_t>(1, std::strtoull(e, nullptr, 0));
   {
     size_t free_b = 0, total_b = 0;
@@ -632,6 +634,8 @@ int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t
       target_paths = std::min<uint64_t>(target_paths, std::max<uint64_t>(npix, (free_b + have) / 2 / per_path));
     }
   }
+  // queue positions are 32-bit: the shadow queue holds up to n_lights entries per path
+  target_paths = std::min<uint64_t>(target_paths, 0xFFFFFF00ull / std::max(1u, sc->dev.n_lights));
   uint32_t spw = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(n_samples ? n_samples : 1, target_paths / npix));
   if (n_samples == 0) {
     if (stats_out) std::memset(stats_out, 0, sizeof *stats_out);
