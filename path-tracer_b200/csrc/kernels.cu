@@ -231,7 +231,11 @@ __device__ __forceinline__ void st_wave(float4 *p, float4 v) {
 #ifndef PTB_LEAF_T
 #define PTB_LEAF_T 12
 #endif
+#ifndef PTB_REFILL_T_SHADOW
+#define PTB_REFILL_T_SHADOW PTB_REFILL_T
+#endif
 constexpr int REFILL_THRESHOLD = PTB_REFILL_T;  // refill when fewer lanes than this still own a ray
+constexpr int REFILL_THRESHOLD_SHADOW = PTB_REFILL_T_SHADOW;
 constexpr int LEAF_THRESHOLD = PTB_LEAF_T;      // run the (divergent) primitive test once this many lanes wait at a leaf
 
 // extend: closest accepted hit (alpha walk included) of every queued ray.  Persistent warps with lane-level ray
@@ -594,7 +598,7 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
         q = NONE;
       }
       const uint32_t busy = __ballot_sync(0xffffffffu, q != NONE);
-      if (busy == 0 || (!drained && __popc(busy) < REFILL_THRESHOLD)) break;
+      if (busy == 0 || (!drained && __popc(busy) < REFILL_THRESHOLD_SHADOW)) break;
     }
   }
 }
