@@ -16,7 +16,9 @@
 #define PTB_EXTEND_MINB 7
 #endif
 #ifndef PTB_SHADE_MINB
-#define PTB_SHADE_MINB 6
+// 64 registers, 8 CTAs per SM (164 B spilled): k_shade is latency-bound on the chain hit -> shading record -> material
+// -> texel, so resident warps beat registers: 5 / 6 / 7 / 8 / 9 CTAs = +9 % / ref / -8 % / -11 % / -8 % (console)
+#define PTB_SHADE_MINB 8
 #endif
 #ifndef PTB_SHADOW_MINB
 #define PTB_SHADOW_MINB 6  // 72 registers, 6 CTAs per SM: k_shadow -2 % (console) ... -18 % (foliage) against 90 registers
