@@ -21,7 +21,9 @@
 #define PTB_SHADE_MINB 8
 #endif
 #ifndef PTB_SHADOW_MINB
-#define PTB_SHADOW_MINB 6  // 72 registers, 6 CTAs per SM: k_shadow -2 % (console) ... -18 % (foliage) against 90 registers
+// 90 -> 72 registers: k_shadow -2 % (console) ... -18 % (foliage); 72 -> 64 registers / 8 CTAs per SM (40 B spilled):
+// another -1 % (console) ... -4.5 % (foliage)
+#define PTB_SHADOW_MINB 8
 #endif
 // 1: wave-state loads/stores use the streaming (evict-first) cache policy so that they do not displace BVH nodes
 // (measured: k_shade -10 %, k_extend -2 % on the console workload).

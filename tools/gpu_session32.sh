@@ -1,4 +1,4 @@
-R=gpurun_out/r04c
+R=gpurun_out/r04d
 mkdir -p $R
 timeout 1500 python -m pytest tests -m gpu -x -q > $R/pytest.log 2>&1; echo "pytest rc=$?" >> $R/pytest.log
 timeout 900 python bench.py > $R/bench_console_1080p_128spp.json 2> $R/bench_console.err
