@@ -221,6 +221,21 @@ int pt_tonemap_device(const float *accum_dev, uint32_t width, uint32_t height, u
 int pt_render(const pt_scene *scene, const pt_profile *profile, uint64_t seed, uint8_t *rgb8_out,
               float *accum_out, pt_stats *stats_out);
 
+/* ---- Renderer::render over several GPUs of one box, in one process ---- */
+/* A copy of `scene` resident on `device` (-1: host-only copy).  Nothing is parsed again and the acceleration
+ * structure of the source (built or loaded with it) is reused, so a replica costs one upload.  The reference shares
+ * one `&Scene` between its rayon workers (renderer/mod.rs:76,106); a GPU needs the scene in its own HBM. */
+int pt_scene_replicate(const pt_scene *scene, int device, pt_scene **out);
+/* pt_render split by sample index: replica g of n_replicas renders the samples {s : s mod n_replicas == g} of the
+ * full frame on its own device from its own host thread (what rayon's pool is to mod.rs:105-106); the partial sums
+ * are copied device-to-device onto replica 0's device (NVLink when the devices are peers) and added there in replica
+ * order, then post-processed once.  The set of samples, hence the image up to f32 summation order, is the same for
+ * every n_replicas.  replicas: distinct scene objects (two may share a device); rgb8_out / accum_out as pt_render;
+ * stats_out: optional array of n_replicas entries (per-replica counts and device time).  The one-process-per-GPU
+ * form of the same split (torchrun + one NCCL reduce) is built from pt_render_accum_device. */
+int pt_render_multi(const pt_scene *const *replicas, uint32_t n_replicas, const pt_profile *profile, uint64_t seed,
+                    uint8_t *rgb8_out, float *accum_out, pt_stats *stats_out);
+
 /* ---- debug_render (renderer/debug_renderer.rs:11-105): `render --debug-textures` ---- */
 /* One pixel-centre ray per pixel, first element of ray_cast, material sampled at the hit.  planes_out holds
  * PT_AOV_COUNT consecutive row-major RGB8 images of width*height pixels (host memory), each channel

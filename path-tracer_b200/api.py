@@ -22,7 +22,7 @@ EXPORTS = ["pt_last_error", "pt_device_count", "pt_profile_default", "pt_profile
            "pt_scene_create", "pt_scene_synthetic", "pt_scene_destroy", "pt_set_accel_builder", "pt_scene_accel_info", "pt_scene_upload", "pt_set_kernel_timing", "pt_scene_get_desc", "pt_scene_info",
            "pt_trace_closest", "pt_trace_closest_device", "pt_trace_transmittance", "pt_triangle_intersect",
            "pt_trace_paths", "pt_render_accum_device", "pt_aov_name", "pt_debug_textures", "pt_render_progressive", "pt_convert_gltf", "pt_scene_save_binary",
-           "pt_tonemap_device", "pt_render", "pt_write_png", "pt_read_png", "pt_free"]
+           "pt_tonemap_device", "pt_render", "pt_scene_replicate", "pt_render_multi", "pt_write_png", "pt_read_png", "pt_free"]
 
 
 SNAPSHOT_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_uint8), C.c_uint32, C.c_uint32, C.c_uint32)
@@ -67,6 +67,8 @@ def lib():
         L.pt_render_accum_device.argtypes = [vp, C.POINTER(pt_profile), u32, u32, u32, u64, vp, vp, C.POINTER(pt_stats)]
         L.pt_tonemap_device.argtypes = [vp, u32, u32, u32, C.c_int32, vp, C.c_int, vp]
         L.pt_render.argtypes = [vp, C.POINTER(pt_profile), u64, vp, vp, C.POINTER(pt_stats)]
+        L.pt_scene_replicate.argtypes = [vp, C.c_int, C.POINTER(vp)]
+        L.pt_render_multi.argtypes = [C.POINTER(vp), u32, C.POINTER(pt_profile), u64, vp, vp, C.POINTER(pt_stats)]
         L.pt_write_png.argtypes = [C.c_char_p, vp, u32, u32]
         L.pt_read_png.argtypes = [C.c_char_p, u32, C.POINTER(u32), C.POINTER(u32), C.POINTER(C.POINTER(C.c_uint8))]
         L.pt_set_accel_builder.argtypes = [C.c_int]
@@ -169,6 +171,12 @@ class Scene:
             self.close()
         except Exception:
             pass
+
+    def replicate(self, device):
+        """A copy of this scene on another device (-1: host-only); reuses the parsed arrays and the built tree."""
+        h = C.c_void_p()
+        _check(lib().pt_scene_replicate(self.h, device, C.byref(h)))
+        return Scene(h)
 
     def upload(self, stream=None):
         """Re-send the scene's device arrays from pinned host memory (async on `stream`); returns bytes copied."""
@@ -300,6 +308,20 @@ class Renderer:
         self.last_stats = st.as_dict()
         self.last_accum = accum
         return rgb
+
+
+def render_multi(replicas, profile, seed=0, keep_accum=False):
+    """pt_render_multi: one frame split by sample index over `replicas` (Scene objects, one per device) in this
+    process; returns (rgb8[h, w, 3], accum or None, [per-replica stats])."""
+    p = profile.c
+    n = len(replicas)
+    handles = (C.c_void_p * n)(*[r.h for r in replicas])
+    rgb = np.zeros((p.height, p.width, 3), np.uint8)
+    accum = np.zeros((p.height, p.width, 3), np.float32) if keep_accum else None
+    st = (pt_stats * n)()
+    _check(lib().pt_render_multi(handles, n, C.byref(p), seed, rgb.ctypes.data,
+                                 accum.ctypes.data if keep_accum else None, st))
+    return rgb, accum, [s.as_dict() for s in st]
 
 
 def debug_render(scene, width, height):

@@ -1,7 +1,8 @@
 // cli.cpp — `path-tracer` command line.  Mirrors the reference's clap surface (src/config/mod.rs:14-52) and
 // run_render (src/main.rs:32-52): `path-tracer render <input> [-o FILE|$OUTPUT] [-q] [-v] [--debug-textures]
 // [-p FILE|$PROFILE]`, errors printed to stderr with exit code 2 (main.rs:14-21).  Additive flags: --seed,
-// --stats, --snapshot-every.  The SFML viewer (renderer/viewer.rs) needs a window + GL: unavailable on this box; -v
+// --stats, --snapshot-every, --gpus N|all (one frame split by sample index over N GPUs of the box through
+// pt_render_multi; also $PT_B200_GPUS).  The SFML viewer (renderer/viewer.rs) needs a window + GL: unavailable on this box; -v
 // delivers the same feed headless instead: the running mean image is written over <OUTPUT> after every
 // --snapshot-every samples per pixel (default 16).  --debug-textures writes the seven AOV PNGs of
 // renderer/debug_renderer.rs into the working directory.  `convert <INPUT> <OUTPUT>` (glTF -> isf, scene/gltf.rs) is
@@ -23,6 +24,7 @@ static int usage(const char *msg) {
                "Path-trace awesome things\n\nUsage: path-tracer <COMMAND>\n\nCommands:\n"
                "  render   <INPUT> [-o, --output <OUTPUT>] [-q, --quiet] [-v, --viewer] [--debug-textures]\n"
                "           [-p, --profile <PROFILE>] [--seed <N>] [--stats <FILE>] [--snapshot-every <SPP>]\n"
+               "           [--gpus <N|all>]\n"
                "  convert  <INPUT> <OUTPUT> [--binary]   glTF 2.0 (.gltf / .glb) -> <OUTPUT>/scene.isf + texture PNGs\n"
                "           (--binary: also <OUTPUT>/scene.isfb)\n"
                "  pack     <INPUT> <OUTPUT.isfb> [--no-accel]   isf scene -> binary side-car with its BVH\n");
@@ -77,6 +79,7 @@ int main(int argc, char **argv) {
   bool quiet = false, viewer = false, debug_textures = false;
   unsigned long long seed = 0;
   unsigned snapshot_every = 16;
+  std::string gpus_arg = std::getenv("PT_B200_GPUS") ? std::getenv("PT_B200_GPUS") : "1";
   for (int i = 2; i < argc; ++i) {
     std::string a = argv[i];
     auto need = [&](const char *name) -> const char * {
@@ -95,6 +98,7 @@ int main(int argc, char **argv) {
     else if (a == "--debug-textures") debug_textures = true;
     else if (a == "--seed") seed = std::strtoull(need("--seed"), nullptr, 0);
     else if (a == "--stats") stats_path = need("--stats");
+    else if (a == "--gpus") gpus_arg = need("--gpus");
     else if (a == "--snapshot-every") snapshot_every = (unsigned)std::strtoul(need("--snapshot-every"), nullptr, 0);
     else if (a == "-h" || a == "--help") {
       usage(nullptr);
@@ -155,15 +159,45 @@ int main(int argc, char **argv) {
     if (!s->quiet) std::fprintf(stderr, "  %u spp -> %s\n", done, s->path);
     return 0;
   };
-  int rrc = viewer ? pt_render_progressive(scene, &prof, seed, snapshot_every, on_snapshot, &snap, rgb.data(), nullptr, &st)
-                   : pt_render(scene, &prof, seed, rgb.data(), nullptr, &st);
-  if (rrc != PT_OK) {
-    std::fprintf(stderr, "%s\n", pt_last_error());
+  // --gpus: replicas of the scene on devices 1..N-1, samples split by index (the viewer feed stays on one device)
+  int n_gpus = gpus_arg == "all" ? pt_device_count() : std::atoi(gpus_arg.c_str());
+  if (n_gpus < 1 || n_gpus > pt_device_count()) {
+    std::fprintf(stderr, "--gpus %s: this box has %d CUDA device(s)\n", gpus_arg.c_str(), pt_device_count());
     pt_scene_destroy(scene);
     return 2;
   }
+  std::vector<pt_scene *> replicas{scene};
+  auto destroy_all = [&] {
+    for (pt_scene *r : replicas) pt_scene_destroy(r);
+  };
+  int rrc = PT_OK;
+  if (n_gpus > 1 && !viewer) {
+    for (int d = 1; d < n_gpus && rrc == PT_OK; ++d) {
+      pt_scene *r = nullptr;
+      rrc = pt_scene_replicate(scene, d, &r);
+      if (rrc == PT_OK) replicas.push_back(r);
+    }
+    std::vector<pt_stats> per(replicas.size());
+    if (rrc == PT_OK) rrc = pt_render_multi(replicas.data(), (uint32_t)replicas.size(), &prof, seed, rgb.data(), nullptr, per.data());
+    for (const pt_stats &p : per) {  // whole-frame counts; device time = the slowest replica
+      st.samples += p.samples;
+      st.extend_rays += p.extend_rays;
+      st.shadow_rays += p.shadow_rays;
+      st.alpha_recasts += p.alpha_recasts;
+      st.kernel_launches += p.kernel_launches;
+      if (p.ms_total > st.ms_total) st.ms_total = p.ms_total;
+    }
+  } else {
+    rrc = viewer ? pt_render_progressive(scene, &prof, seed, snapshot_every, on_snapshot, &snap, rgb.data(), nullptr, &st)
+                 : pt_render(scene, &prof, seed, rgb.data(), nullptr, &st);
+  }
+  if (rrc != PT_OK) {
+    std::fprintf(stderr, "%s\n", pt_last_error());
+    destroy_all();
+    return 2;
+  }
   auto t2 = std::chrono::steady_clock::now();
-  pt_scene_destroy(scene);
+  destroy_all();
   if (pt_write_png(output.c_str(), rgb.data(), prof.width, prof.height) != PT_OK) {
     std::fprintf(stderr, "%s\n", pt_last_error());
     return 2;

@@ -635,6 +635,12 @@ __global__ void __launch_bounds__(256) k_tonemap(const float *__restrict__ accum
   rgb8[i] = to_u8(powf(t, 1.0f / 2.2f) * 255.0f);
 }
 
+// Sum of two accumulation buffers (pt_render_multi: the per-device partial sums are added on the root device in
+// replica order, so the result does not depend on which device finished first).
+__global__ void __launch_bounds__(256) k_accum_add(float *__restrict__ dst, const float *__restrict__ src, uint32_t n) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) dst[i] += src[i];
+}
+
 // sRGB -> linear table: the albedo texel conversion of material.rs:132-146, evaluated once per texel value.
 __global__ void k_init_srgb_lut(float *lut) { lut[threadIdx.x] = powf((float)threadIdx.x / 255.0f, 2.2f); }
 
@@ -696,6 +702,9 @@ void launch_shadow(const DevScene &S, const WaveState &W, uint32_t bounce, cudaS
 void launch_resolve(const WaveParams &P, const WaveState &W, float *accum, cudaStream_t st) {
   uint32_t npix = P.width * P.height;
   k_resolve<<<(npix + 255) / 256, 256, 0, st>>>(P, W, accum);
+}
+void launch_accum_add(float *dst, const float *src, uint32_t n, cudaStream_t st) {
+  k_accum_add<<<sm_count() * 8, 256, 0, st>>>(dst, src, n);
 }
 void launch_tonemap(const float *accum, uint32_t npix, uint32_t total_samples, int tonemap, uint8_t *rgb8, cudaStream_t st) {
   k_tonemap<<<(npix * 3 + 255) / 256, 256, 0, st>>>(accum, npix, (float)total_samples, tonemap, rgb8);

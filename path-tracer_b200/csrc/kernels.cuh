@@ -16,5 +16,6 @@ void launch_extend(const DevScene &S, const WaveParams &P, const WaveState &W, u
 void launch_shade(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st);
 void launch_shadow(const DevScene &S, const WaveState &W, uint32_t bounce, cudaStream_t st);
 void launch_resolve(const WaveParams &P, const WaveState &W, float *accum, cudaStream_t st);
+void launch_accum_add(float *dst, const float *src, uint32_t n, cudaStream_t st);
 void launch_tonemap(const float *accum, uint32_t npix, uint32_t total_samples, int tonemap, uint8_t *rgb8, cudaStream_t st);
 }  // namespace ptb

@@ -780,6 +780,152 @@ int pt_render(const pt_scene *sc, const pt_profile *prof, uint64_t seed, uint8_t
   return PT_OK;
 }
 
+int pt_scene_replicate(const pt_scene *src, int device, pt_scene **out) {
+  if (!src || !out) {
+    set_error("null argument");
+    return PT_ERR_INVALID;
+  }
+  *out = nullptr;
+  int ndev = 0;
+  if (device != -1) {
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+      cudaGetLastError();
+      set_error("no CUDA device available (this library has no CPU fallback)");
+      return PT_ERR_CUDA;
+    }
+    if (device < 0 || device >= ndev) {
+      set_error("device %d out of range (%d devices)", device, ndev);
+      return PT_ERR_INVALID;
+    }
+  }
+  pt_scene *sc = new pt_scene();
+  sc->host = src->host;
+  std::string err = sc->host.finalize();  // re-points the texture descriptors at the copy's own texel vectors
+  if (!err.empty()) {
+    delete sc;
+    set_error("%s", err.c_str());
+    return PT_ERR_INVALID;
+  }
+  sc->device = device;
+  if (src->device >= 0 || src->accel_preloaded) {  // the source holds a tree (built or validated at load): reuse it
+    sc->bvh = src->bvh;
+    sc->accel = src->accel;
+    sc->accel_preloaded = true;
+  }
+  if (device == -1) {
+    *out = sc;
+    return PT_OK;
+  }
+  DeviceGuard g(device);
+  int rc = build_device_scene(sc);
+  if (rc != PT_OK) {
+    pt_scene_destroy(sc);
+    return rc;
+  }
+  *out = sc;
+  return PT_OK;
+}
+
+int pt_render_multi(const pt_scene *const *replicas, uint32_t n_replicas, const pt_profile *prof, uint64_t seed,
+                    uint8_t *rgb8_out, float *accum_out, pt_stats *stats_out) {
+  if (!replicas || n_replicas == 0 || !rgb8_out) {
+    set_error("null argument");
+    return PT_ERR_INVALID;
+  }
+  int rc = check_profile(prof);
+  if (rc) return rc;
+  for (uint32_t g = 0; g < n_replicas; ++g) {
+    if (!replicas[g]) {
+      set_error("replica %u is null", g);
+      return PT_ERR_INVALID;
+    }
+    if (replicas[g]->device < 0) return no_device();
+    for (uint32_t k = 0; k < g; ++k)
+      if (replicas[k] == replicas[g]) {
+        set_error("replica %u is the same scene object as replica %u (each needs its own wave buffers)", g, k);
+        return PT_ERR_INVALID;
+      }
+  }
+  const uint32_t G = n_replicas;
+  const size_t npix = (size_t)prof->width * prof->height, nf = npix * 3;
+  std::vector<float *> accum(G, nullptr);
+  std::vector<int> rcs(G, PT_OK);
+  std::vector<std::string> errs(G);
+  std::vector<pt_stats> stats(G);
+  // one host thread per replica (the rayon pool of mod.rs:106 becomes one wave scheduler per device); replica g
+  // renders the samples s = g (mod G) of the full frame, so the union of samples is the same for every G
+  auto work = [&](uint32_t g) {
+    const pt_scene *sc = replicas[g];
+    DeviceGuard dg(sc->device);
+    const uint32_t mine = prof->samples > g ? (prof->samples - g + G - 1) / G : 0;
+    if (cudaMalloc(&accum[g], nf * sizeof(float)) != cudaSuccess || cudaMemset(accum[g], 0, nf * sizeof(float)) != cudaSuccess) {
+      cudaGetLastError();
+      rcs[g] = PT_ERR_NOMEM;
+      errs[g] = "out of device memory";
+      return;
+    }
+    rcs[g] = pt_render_accum_device(sc, prof, g, G, mine, seed, accum[g], nullptr, &stats[g]);
+    if (rcs[g] != PT_OK) errs[g] = g_last_error;  // thread-local: hand it to the calling thread
+    else if (cudaDeviceSynchronize() != cudaSuccess) {
+      rcs[g] = PT_ERR_CUDA;
+      errs[g] = "device synchronisation failed after rendering";
+    }
+  };
+  {
+    std::vector<std::thread> threads;
+    for (uint32_t g = 1; g < G; ++g) threads.emplace_back(work, g);
+    work(0);
+    for (auto &t : threads) t.join();
+  }
+  auto release = [&] {
+    for (uint32_t g = 0; g < G; ++g)
+      if (accum[g]) {
+        DeviceGuard dg(replicas[g]->device);
+        cudaFree(accum[g]);
+      }
+  };
+  for (uint32_t g = 0; g < G; ++g)
+    if (rcs[g] != PT_OK) {
+      set_error("replica %u (device %d): %s", g, replicas[g]->device, errs[g].c_str());
+      release();
+      return rcs[g];
+    }
+  // reduce on replica 0's device in replica order: peer copies (NVLink when the devices are peers) + one add each
+  const int root = replicas[0]->device;
+  DeviceGuard dg(root);
+  float *tmp = nullptr;
+  uint8_t *d_rgb = nullptr;
+  cudaError_t e = cudaSuccess;
+  if (G > 1) e = cudaMalloc(&tmp, nf * sizeof(float));
+  if (e == cudaSuccess) e = cudaMalloc(&d_rgb, nf);
+  for (uint32_t g = 1; g < G && e == cudaSuccess; ++g) {
+    const int dev = replicas[g]->device;
+    if (dev != root) {
+      int can = 0;
+      if (cudaDeviceCanAccessPeer(&can, root, dev) == cudaSuccess && can)
+        if (cudaDeviceEnablePeerAccess(dev, 0) != cudaSuccess) cudaGetLastError();  // already enabled is fine
+      e = cudaMemcpyPeer(tmp, root, accum[g], dev, nf * sizeof(float));
+    } else {
+      e = cudaMemcpy(tmp, accum[g], nf * sizeof(float), cudaMemcpyDeviceToDevice);
+    }
+    if (e != cudaSuccess) break;
+    launch_accum_add(accum[0], tmp, (uint32_t)nf, nullptr);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) {
+    launch_tonemap(accum[0], (uint32_t)npix, prof->samples, prof->tonemap, d_rgb, nullptr);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(rgb8_out, d_rgb, nf, cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess && accum_out) e = cudaMemcpy(accum_out, accum[0], nf * sizeof(float), cudaMemcpyDeviceToHost);
+  cudaFree(tmp);
+  cudaFree(d_rgb);
+  release();
+  CUDA_TRY(e);
+  if (stats_out) std::memcpy(stats_out, stats.data(), G * sizeof(pt_stats));
+  return PT_OK;
+}
+
 const char *pt_aov_name(int aov) {
   static const char *names[PT_AOV_COUNT] = {"normal", "albedo", "opacity", "metalness", "roughness", "emissive", "ior"};
   return aov >= 0 && aov < PT_AOV_COUNT ? names[aov] : nullptr;

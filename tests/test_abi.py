@@ -150,6 +150,32 @@ def test_synthetic_scenes_host_only():
         pt.Scene.synthetic("nope", 10, device=-1)
 
 
+def test_scene_replicate_host_only_and_multi_errors():
+    """pt_scene_replicate copies the parsed scene (texture descriptors re-pointed at the copy's own texels);
+    pt_render_multi refuses host-only / duplicate / missing replicas instead of falling back to the CPU."""
+    src = pt.Scene.load(os.path.join(GOLDEN, "scenes", "alpha_transparency", "scene.isf"), device=-1)
+    a = src.arrays()
+    rep = src.replicate(-1)
+    src.close()  # the replica must not point into the source
+    b = rep.arrays()
+    for k in ("tri_pos", "tri_nrm", "tri_uv"):
+        assert np.array_equal(getattr(a, k), getattr(b, k)), k
+    assert len(a.textures) == len(b.textures) > 0
+    for ta, tb in zip(a.textures, b.textures):
+        assert np.array_equal(ta, tb)
+    assert rep.info() == pt.Scene.load(os.path.join(GOLDEN, "scenes", "alpha_transparency", "scene.isf"), device=-1).info()
+    prof = pt.Profile(width=8, height=8, samples=2)
+    with pytest.raises(pt.PtError) as e:
+        pt.render_multi([rep], prof)
+    assert e.value.code == -4  # host-only: no CPU fallback
+    with pytest.raises(pt.PtError):
+        pt.render_multi([], prof)
+    if not HAS_GPU:
+        with pytest.raises(pt.PtError) as e:
+            rep.replicate(0)
+        assert e.value.code == -4
+
+
 def test_cli_errors_exit_code_2(tmp_path):
     exe = os.path.join(os.path.dirname(pt.__file__), "path-tracer")
     for args in ([], ["bogus"], ["render"], ["render", "/nonexistent/scene.isf", "-q"], ["render", "x.isf", "--nope"]):

@@ -281,6 +281,45 @@ def test_sample_partition_sums_to_full_render(loaded):
     assert torch.allclose(full, parts, rtol=1e-5, atol=1e-6)
 
 
+def test_render_multi_in_process(tmp_path, loaded):
+    """pt_render_multi (one process, one host thread per replica, samples split s mod G): three replicas
+    — spread over the box's devices, which on a one-GPU box is the same device three times — reproduce pt_render's
+    accumulation buffer up to f32 summation order; the CLI's --gpus reaches the same image and rejects a count the
+    box does not have."""
+    import subprocess
+    ndev = pt.device_count()
+    _, _, gsc = loaded["alpha_transparency"]
+    prof = pt.Profile(width=128, height=96, samples=10, bounces=4)  # 10 = 4 + 3 + 3 samples
+    rend = pt.Renderer(profile=prof)
+    full = rend.render(gsc, keep_accum=True)
+    replicas = [gsc] + [gsc.replicate(g % ndev) for g in (1, 2)]
+    rgb, accum, stats = pt.render_multi(replicas, prof, keep_accum=True)
+    assert [s["samples"] for s in stats] == [128 * 96 * k for k in (4, 3, 3)]
+    assert sum(s["extend_rays"] for s in stats) == rend.last_stats["extend_rays"]
+    assert sum(s["shadow_rays"] for s in stats) == rend.last_stats["shadow_rays"]
+    assert np.allclose(accum, rend.last_accum, rtol=1e-5, atol=1e-6)
+    assert np.abs(rgb.astype(np.int16) - full.astype(np.int16)).max() <= 1
+    # more replicas than samples: the idle ones contribute nothing
+    one = pt.Profile(width=64, height=48, samples=1, bounces=2)
+    r1 = pt.Renderer(profile=one).render(gsc)
+    rgb1, _, st1 = pt.render_multi(replicas, one)
+    assert np.array_equal(rgb1, r1) and [s["samples"] for s in st1] == [64 * 48, 0, 0]
+    with pytest.raises(pt.PtError):
+        pt.render_multi([gsc, gsc], prof)  # the same object twice
+    for r in replicas[1:]:
+        r.close()
+    exe = os.path.join(os.path.dirname(pt.__file__), "path-tracer")
+    yml = tmp_path / "p.yml"
+    yml.write_text("resolution:\n  width: 96\n  height: 64\nsamples: 6\nbounces: 2\n")
+    r = subprocess.run([exe, "render", scene_path("cube"), "-q", "--gpus", str(ndev + 1)], capture_output=True)
+    assert r.returncode == 2 and b"CUDA device" in r.stderr
+    out = tmp_path / "all.png"
+    r = subprocess.run([exe, "render", scene_path("cube"), "-o", str(out), "-p", str(yml), "-q", "--gpus", "all"], capture_output=True)
+    assert r.returncode == 0, r.stderr
+    ref = pt.Renderer(profile=pt.Profile.load(str(yml))).render(loaded["cube"][2])
+    assert np.abs(pt.read_png(str(out)).astype(np.int16) - ref.astype(np.int16)).max() <= 1
+
+
 def test_zero_samples_and_bad_arguments(loaded):
     import torch
     _, _, gsc = loaded["cube"]
