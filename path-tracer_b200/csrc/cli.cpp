@@ -14,6 +14,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/pt_b200.h"
@@ -172,10 +173,27 @@ int main(int argc, char **argv) {
   };
   int rrc = PT_OK;
   if (n_gpus > 1 && !viewer) {
-    for (int d = 1; d < n_gpus && rrc == PT_OK; ++d) {
-      pt_scene *r = nullptr;
-      rrc = pt_scene_replicate(scene, d, &r);
-      if (rrc == PT_OK) replicas.push_back(r);
+    // one thread per device: a replica is a host-side repack plus one upload, independent of the others
+    std::vector<pt_scene *> made(n_gpus, nullptr);
+    std::vector<int> rcs(n_gpus, PT_OK);
+    std::vector<std::string> errs(n_gpus);
+    std::vector<std::thread> threads;
+    for (int d = 1; d < n_gpus; ++d)
+      threads.emplace_back([&, d] {
+        rcs[d] = pt_scene_replicate(scene, d, &made[d]);
+        if (rcs[d] != PT_OK) errs[d] = pt_last_error();  // thread-local message: keep it for the main thread
+      });
+    for (auto &t : threads) t.join();
+    for (int d = 1; d < n_gpus; ++d) {
+      if (made[d]) replicas.push_back(made[d]);
+      if (rcs[d] != PT_OK && rrc == PT_OK) {
+        rrc = rcs[d];
+        std::fprintf(stderr, "device %d: %s\n", d, errs[d].c_str());
+      }
+    }
+    if (rrc != PT_OK) {
+      destroy_all();
+      return 2;
     }
     std::vector<pt_stats> per(replicas.size());
     if (rrc == PT_OK) rrc = pt_render_multi(replicas.data(), (uint32_t)replicas.size(), &prof, seed, rgb.data(), nullptr, per.data());

@@ -77,6 +77,12 @@ struct pt_scene {
   WaveState wave{};
   std::vector<void *> wave_allocs;
   uint32_t *cursor = nullptr;  // work cursor of the trace entry points
+  // frame buffers of pt_render_multi, kept between frames (cudaFree synchronises the device: not once per frame)
+  struct FrameBuf {
+    void *p = nullptr;
+    size_t bytes = 0;
+  } multi_accum, multi_tmp, multi_rgb;
+  std::mutex multi_mu;  // held by pt_render_multi over every replica of the call (taken in address order)
 };
 
 namespace {
@@ -275,6 +281,16 @@ int ensure_wave(pt_scene *sc, uint32_t n_paths) {
   return PT_OK;
 }
 
+// grows a cached frame buffer of the scene (current device = the scene's)
+cudaError_t frame_buf(pt_scene::FrameBuf &b, size_t bytes) {
+  if (b.bytes >= bytes) return cudaSuccess;
+  cudaFree(b.p);
+  b = pt_scene::FrameBuf{};
+  cudaError_t e = cudaMalloc(&b.p, bytes);
+  if (e == cudaSuccess) b.bytes = bytes;
+  return e;
+}
+
 int no_device() {
   set_error("scene was created host-only (device -1): no CPU fallback exists for tracing or rendering");
   return PT_ERR_CUDA;
@@ -388,6 +404,7 @@ void pt_scene_destroy(pt_scene *sc) {
   }
   DeviceGuard g(sc->device);
   free_wave(sc);
+  for (pt_scene::FrameBuf *b : {&sc->multi_accum, &sc->multi_tmp, &sc->multi_rgb}) cudaFree(b->p);
   for (void *p : sc->allocs) cudaFree(p);
   for (auto &s : sc->staged) cudaFreeHost(s.host);
   for (cudaEvent_t e : sc->events) cudaEventDestroy(e);
@@ -848,6 +865,11 @@ int pt_render_multi(const pt_scene *const *replicas, uint32_t n_replicas, const 
   }
   const uint32_t G = n_replicas;
   const size_t npix = (size_t)prof->width * prof->height, nf = npix * 3;
+  std::vector<pt_scene *> order;
+  for (uint32_t g = 0; g < G; ++g) order.push_back(const_cast<pt_scene *>(replicas[g]));
+  std::sort(order.begin(), order.end());
+  std::vector<std::unique_lock<std::mutex>> held;
+  for (pt_scene *r : order) held.emplace_back(r->multi_mu);
   std::vector<float *> accum(G, nullptr);
   std::vector<int> rcs(G, PT_OK);
   std::vector<std::string> errs(G);
@@ -858,7 +880,9 @@ int pt_render_multi(const pt_scene *const *replicas, uint32_t n_replicas, const 
     const pt_scene *sc = replicas[g];
     DeviceGuard dg(sc->device);
     const uint32_t mine = prof->samples > g ? (prof->samples - g + G - 1) / G : 0;
-    if (cudaMalloc(&accum[g], nf * sizeof(float)) != cudaSuccess || cudaMemset(accum[g], 0, nf * sizeof(float)) != cudaSuccess) {
+    pt_scene *msc = const_cast<pt_scene *>(sc);
+    if (frame_buf(msc->multi_accum, nf * sizeof(float)) == cudaSuccess) accum[g] = static_cast<float *>(msc->multi_accum.p);
+    if (!accum[g] || cudaMemsetAsync(accum[g], 0, nf * sizeof(float), nullptr) != cudaSuccess) {
       cudaGetLastError();
       rcs[g] = PT_ERR_NOMEM;
       errs[g] = "out of device memory";
@@ -877,27 +901,20 @@ int pt_render_multi(const pt_scene *const *replicas, uint32_t n_replicas, const 
     work(0);
     for (auto &t : threads) t.join();
   }
-  auto release = [&] {
-    for (uint32_t g = 0; g < G; ++g)
-      if (accum[g]) {
-        DeviceGuard dg(replicas[g]->device);
-        cudaFree(accum[g]);
-      }
-  };
   for (uint32_t g = 0; g < G; ++g)
     if (rcs[g] != PT_OK) {
       set_error("replica %u (device %d): %s", g, replicas[g]->device, errs[g].c_str());
-      release();
       return rcs[g];
     }
   // reduce on replica 0's device in replica order: peer copies (NVLink when the devices are peers) + one add each
   const int root = replicas[0]->device;
   DeviceGuard dg(root);
-  float *tmp = nullptr;
-  uint8_t *d_rgb = nullptr;
+  pt_scene *rsc = const_cast<pt_scene *>(replicas[0]);
   cudaError_t e = cudaSuccess;
-  if (G > 1) e = cudaMalloc(&tmp, nf * sizeof(float));
-  if (e == cudaSuccess) e = cudaMalloc(&d_rgb, nf);
+  if (G > 1) e = frame_buf(rsc->multi_tmp, nf * sizeof(float));
+  if (e == cudaSuccess) e = frame_buf(rsc->multi_rgb, nf);
+  float *tmp = static_cast<float *>(rsc->multi_tmp.p);
+  uint8_t *d_rgb = static_cast<uint8_t *>(rsc->multi_rgb.p);
   for (uint32_t g = 1; g < G && e == cudaSuccess; ++g) {
     const int dev = replicas[g]->device;
     if (dev != root) {
@@ -918,9 +935,6 @@ int pt_render_multi(const pt_scene *const *replicas, uint32_t n_replicas, const 
   }
   if (e == cudaSuccess) e = cudaMemcpy(rgb8_out, d_rgb, nf, cudaMemcpyDeviceToHost);
   if (e == cudaSuccess && accum_out) e = cudaMemcpy(accum_out, accum[0], nf * sizeof(float), cudaMemcpyDeviceToHost);
-  cudaFree(tmp);
-  cudaFree(d_rgb);
-  release();
   CUDA_TRY(e);
   if (stats_out) std::memcpy(stats_out, stats.data(), G * sizeof(pt_stats));
   return PT_OK;

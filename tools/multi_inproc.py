@@ -26,9 +26,10 @@ out = dict(workload=name, n_gpus=G, spp_per_gpu=spp, scene_s=round(t1 - t0, 3), 
 wall1, wallm, dev = [], [], []
 for it in range(reps + 1):  # first iteration: warm-up (wave buffers are allocated lazily)
     a = time.perf_counter(); rend1.render(sc); b = time.perf_counter()
-    rgb, accum, stats = pkg.render_multi(replicas, allp, keep_accum=True); c = time.perf_counter()
+    rgb, _, stats = pkg.render_multi(replicas, allp); c = time.perf_counter()
     if it:
         wall1.append(b - a); wallm.append(c - b); dev.append([round(s["ms_total"], 2) for s in stats])
+_, accum, _ = pkg.render_multi(replicas, allp, keep_accum=True)
 ref = rendG.render(sc, keep_accum=True)
 n1, nG = w * h * spp, w * h * spp * G
 out.update(one_gpu_wall_ms=round(1e3 * min(wall1), 2), multi_wall_ms=round(1e3 * min(wallm), 2), replica_device_ms=dev[-1],
