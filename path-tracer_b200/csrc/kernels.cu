@@ -7,6 +7,7 @@
 //   k_shade    renderer/mod.rs:184-186,207-225,230-278; brdf/cook_torrance.rs; utils.rs:23-31
 //   k_shadow   renderer/mod.rs:281-333
 //   k_resolve  renderer/mod.rs:130 ; k_tonemap renderer/mod.rs:150-162,335-353
+#include <atomic>
 #include <cstdlib>
 
 #include "kernels.cuh"
@@ -646,15 +647,25 @@ __global__ void k_init_srgb_lut(float *lut) { lut[threadIdx.x] = powf((float)thr
 
 // ------------------------------------------------------------------------------------------------
 // host-side launchers
-static int g_sm_count = 0;
+// Per-device launch geometry, cached on first use.  pt_render_multi launches from one host thread per device, so
+// the cache is indexed by the current device and its entries are atomics (two threads may fill one entry with the
+// same value).
+constexpr int MAX_DEVICES = 64;
+static int current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev >= 0 && dev < MAX_DEVICES ? dev : 0;
+}
 static int sm_count() {
-  if (g_sm_count == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
-    if (g_sm_count <= 0) g_sm_count = 148;
+  static std::atomic<int> cache[MAX_DEVICES];
+  const int dev = current_device();
+  int n = cache[dev].load(std::memory_order_relaxed);
+  if (n == 0) {
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+    cache[dev].store(n, std::memory_order_relaxed);
   }
-  return g_sm_count;
+  return n;
 }
 constexpr int PERSIST_CTAS_PER_SM = 8;
 // Grid of a persistent kernel: exactly the CTAs that are resident at once (occupancy API), so that statically
@@ -692,8 +703,13 @@ void launch_extend(const DevScene &S, const WaveParams &P, const WaveState &W, u
   k_extend<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, P, W, bounce);
 }
 void launch_shade(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st) {
-  static int grid = 0;
-  if (!grid) grid = resident_grid(k_shade, 128);
+  static std::atomic<int> cache[MAX_DEVICES];
+  const int dev = current_device();
+  int grid = cache[dev].load(std::memory_order_relaxed);
+  if (!grid) {
+    grid = resident_grid(k_shade, 128);
+    cache[dev].store(grid, std::memory_order_relaxed);
+  }
   k_shade<<<grid, 128, 0, st>>>(S, P, W, bounce);
 }
 void launch_shadow(const DevScene &S, const WaveState &W, uint32_t bounce, cudaStream_t st) {
