@@ -31,6 +31,10 @@
 #ifndef PTB_STREAM
 #define PTB_STREAM 1
 #endif
+// ordered hit list between k_extend and k_shade (k_hit_list below); read by k_extend, k_shade and the launchers
+#ifndef PTB_HIT_LIST
+#define PTB_HIT_LIST 1
+#endif
 
 namespace ptb {
 
@@ -254,6 +258,9 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
     W.counters[CTR_QUEUE(outb)] = 0;  // the queues k_shade(bounce) appends to
     W.counters[CTR_SHADOW(outb)] = 0;
     W.counters[CTR_WORK_SHADOW] = 0;
+#if PTB_HIT_LIST
+    W.counters[6] = 0;  // CTR_HITS: filled by k_hit_list after this kernel
+#endif
     stat_add(W.counters, CTR_STAT_EXTEND, n);
   }
   constexpr uint32_t NONE = 0xFFFFFFFFu;
@@ -351,6 +358,54 @@ __device__ __forceinline__ void warp_append2(uint32_t *pair, bool want_path, boo
   pos_shadow = (uint32_t)(base >> 32) + (uint32_t)__popc(ms & lanemask_lt());
 }
 
+// PTB_HIT_LIST (on; console -5.9 % frame time, foliage -0.3 ... -1.2 %, profiles/r06/ab_hitlist.jsonl): a scan pass between k_extend and k_shade lists the queue positions that hit something, in
+// queue order up to 256-position chunks, so that every k_shade warp runs with 32 paths to shade instead of hits
+// interleaved with misses (15 / 12 of 32 lanes on bounces 1 / 2 of the console scene).  Misses get their background
+// term in the scan pass.  The list lives in the unused w component of the INPUT queue's origin records (entry i in
+// ray_o[in][i].w), which k_shade only reads; its length is counters[CTR_HITS].
+#if PTB_HIT_LIST
+constexpr uint32_t CTR_HITS = 6;  // a free slot of the counters[] layout (device_scene.cuh)
+__global__ void __launch_bounds__(256) k_hit_list(const __grid_constant__ DevScene S, WaveState W, uint32_t bounce) {
+  const uint32_t in = bounce & 1u;
+  const uint32_t n = W.counters[CTR_QUEUE(in)];
+  const V3 bgc = mk3(S.background[0], S.background[1], S.background[2]);
+  const bool bg = bgc.x != 0.0f || bgc.y != 0.0f || bgc.z != 0.0f;
+  constexpr uint32_t K = 8;  // positions per lane and iteration: one reservation atomic per 256 queue positions
+  const uint32_t warps = gridDim.x * (blockDim.x >> 5), warp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  for (uint32_t base = warp * (32u * K); base < n; base += warps * (32u * K)) {
+    int idx[K];
+#pragma unroll
+    for (uint32_t k = 0; k < K; ++k) {
+      const uint32_t q = base + k * 32u + lane_id();
+      idx[k] = q < n ? __float_as_int(reinterpret_cast<const float *>(&W.hit[q])[3]) : -1;
+    }
+    uint32_t m[K], total = 0;
+#pragma unroll
+    for (uint32_t k = 0; k < K; ++k) {
+      m[k] = __ballot_sync(0xffffffffu, idx[k] >= 0);
+      total += (uint32_t)__popc(m[k]);
+      const uint32_t q = base + k * 32u + lane_id();
+      if (bg && q < n && idx[k] < 0) {  // mod.rs:184-186: color + throughput * background, and the path ends
+        const float4 t4 = ld_wave(&W.thr[in][q]);
+        const uint32_t slot = (uint32_t)__float_as_int(__ldcs(&reinterpret_cast<const float *>(&W.ray_d[in][q])[3]));
+        add_radiance(W.radiance, slot, mul_el(mk3(t4.x, t4.y, t4.z), bgc));
+      }
+    }
+    if (total == 0) continue;
+    uint32_t pos = 0;
+    if (lane_id() == 0) pos = atomicAdd(&W.counters[CTR_HITS], total);
+    pos = __shfl_sync(0xffffffffu, pos, 0);
+#pragma unroll
+    for (uint32_t k = 0; k < K; ++k) {
+      if (idx[k] >= 0)
+        reinterpret_cast<float *>(&W.ray_o[in][pos + (uint32_t)__popc(m[k] & lanemask_lt())])[3] =
+            __int_as_float((int)(base + k * 32u + lane_id()));
+      pos += (uint32_t)__popc(m[k]);
+    }
+  }
+}
+#endif
+
 // shade: miss/background, emissive, next-event setup (shadow queue), GGX sample, throughput, cutoff, RR,
 // and compaction of the surviving paths into the other queue buffer.  Queue positions are assigned statically
 // (warp-strided): no work-fetch atomic; the last light's shadow entry and the next ray share one reservation atomic.
@@ -358,13 +413,23 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
                                                                const __grid_constant__ WaveParams P, WaveState W,
                                                                uint32_t bounce) {
   const uint32_t in = bounce & 1u, outb = in ^ 1u;
+#if PTB_HIT_LIST
+  const uint32_t n = W.counters[CTR_HITS];
+#else
   const uint32_t n = W.counters[CTR_QUEUE(in)];
+#endif
   if (blockIdx.x == 0 && threadIdx.x == 0) W.counters[CTR_WORK_EXTEND] = 0;
   uint32_t *pair = &W.counters[CTR_QUEUE(outb)];
   const uint32_t warps = gridDim.x * (blockDim.x >> 5), warp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   for (uint32_t base = warp * 32u; base < n; base += warps * 32u) {
+#if PTB_HIT_LIST
+    const bool active = base + lane_id() < n;
+    uint32_t q = 0;
+    if (active) q = (uint32_t)__float_as_int(__ldcs(&reinterpret_cast<const float *>(&W.ray_o[in][base + lane_id()])[3]));
+#else
     const uint32_t q = base + lane_id();
     const bool active = q < n;
+#endif
     Ray r{};
     V3 thr{}, rad = mk3(0.f, 0.f, 0.f);
     ShadeCtx ctx{};
@@ -710,8 +775,12 @@ void launch_shade(const DevScene &S, const WaveParams &P, const WaveState &W, ui
     grid = resident_grid(k_shade, 128);
     cache[dev].store(grid, std::memory_order_relaxed);
   }
+#if PTB_HIT_LIST
+  k_hit_list<<<sm_count() * 8, 256, 0, st>>>(S, W, bounce);
+#endif
   k_shade<<<grid, 128, 0, st>>>(S, P, W, bounce);
 }
+int shade_launches() { return 1 + PTB_HIT_LIST; }
 void launch_shadow(const DevScene &S, const WaveState &W, uint32_t bounce, cudaStream_t st) {
   k_shadow<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, W, bounce);
 }

@@ -14,6 +14,7 @@ void launch_init_srgb_lut(float *lut, cudaStream_t st);
 void launch_raygen(const DevScene &S, const WaveParams &P, const WaveState &W, cudaStream_t st);
 void launch_extend(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st);
 void launch_shade(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st);
+int shade_launches();  // kernels launch_shade enqueues (the hit-list scan pass + k_shade)
 void launch_shadow(const DevScene &S, const WaveState &W, uint32_t bounce, cudaStream_t st);
 void launch_resolve(const WaveParams &P, const WaveState &W, float *accum, cudaStream_t st);
 void launch_accum_add(float *dst, const float *src, uint32_t n, cudaStream_t st);

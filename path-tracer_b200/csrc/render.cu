@@ -701,7 +701,7 @@ int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t
       mark(0);
       launch_shade(sc->dev, P, W, b, st);
       mark(1);
-      launches += 2;
+      launches += 1 + shade_launches();
       ++n_ext;
       ++n_shade;
       if (sc->dev.n_lights) {
