@@ -358,11 +358,12 @@ __device__ __forceinline__ void warp_append2(uint32_t *pair, bool want_path, boo
   pos_shadow = (uint32_t)(base >> 32) + (uint32_t)__popc(ms & lanemask_lt());
 }
 
-// PTB_HIT_LIST (on; console -5.9 % frame time, foliage -0.3 ... -1.2 %, profiles/r06/ab_hitlist.jsonl): a scan pass between k_extend and k_shade lists the queue positions that hit something, in
-// queue order up to 256-position chunks, so that every k_shade warp runs with 32 paths to shade instead of hits
-// interleaved with misses (15 / 12 of 32 lanes on bounces 1 / 2 of the console scene).  Misses get their background
-// term in the scan pass.  The list lives in the unused w component of the INPUT queue's origin records (entry i in
-// ray_o[in][i].w), which k_shade only reads; its length is counters[CTR_HITS].
+// PTB_HIT_LIST (on: console frame -5.9 %, foliage -0.3 ... -1.2 %, profiles/r06/ab_hitlist.jsonl): a scan pass between
+// k_extend and k_shade lists the queue positions that hit something, in queue order up to 256-position chunks, so
+// that every k_shade warp runs with 32 paths to shade instead of hits interleaved with misses (15 / 12 of 32 lanes
+// on bounces 1 / 2 of the console scene).  Misses get their background term in the scan pass.  The list lives in the
+// unused w component of the INPUT queue's origin records (entry i in ray_o[in][i].w), which k_shade only reads; its
+// length is counters[CTR_HITS], reset by k_extend.
 #if PTB_HIT_LIST
 constexpr uint32_t CTR_HITS = 6;  // a free slot of the counters[] layout (device_scene.cuh)
 __global__ void __launch_bounds__(256) k_hit_list(const __grid_constant__ DevScene S, WaveState W, uint32_t bounce) {
