@@ -178,7 +178,8 @@ def test_scene_replicate_host_only_and_multi_errors():
 
 def test_cli_errors_exit_code_2(tmp_path):
     exe = os.path.join(os.path.dirname(pt.__file__), "path-tracer")
-    for args in ([], ["bogus"], ["render"], ["render", "/nonexistent/scene.isf", "-q"], ["render", "x.isf", "--nope"]):
+    for args in ([], ["bogus"], ["render"], ["render", "/nonexistent/scene.isf", "-q"], ["render", "x.isf", "--nope"],
+                 ["render", "x.isf", "--gpus"], ["render", "/nonexistent/scene.isf", "-q", "--gpus", "all"]):
         r = subprocess.run([exe] + args, capture_output=True)
         assert r.returncode == 2, (args, r.returncode)  # main.rs:14-21
         assert r.stderr
