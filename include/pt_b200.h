@@ -127,11 +127,13 @@ typedef struct {
   uint64_t samples;       /* W*H*spp rendered by this call                    */
   uint64_t extend_rays;   /* one per path segment (renderer/mod.rs:182)       */
   uint64_t shadow_rays;   /* one per light per shaded hit (mod.rs:291,319), skipped-as-zero excluded */
-  uint64_t alpha_recasts; /* continuation re-casts (implementation artefact) */
+  uint64_t alpha_recasts; /* continuation re-casts: always 0 (the alpha walk is one traversal); kept for layout */
   uint64_t kernel_launches;
   float ms_total;         /* raygen -> accumulation resident, CUDA events     */
   float ms_extend, ms_shade, ms_shadow, ms_other; /* filled only while pt_set_kernel_timing(1) */
   uint64_t extend_launches, shade_launches, shadow_launches;
+  uint64_t alpha_tests;    /* opacity evaluations of the alpha walk (renderer/mod.rs:190-204), an implementation count */
+  uint64_t shadow_dropped; /* shadow rays that did not fit their queue: always 0, anything else is a bug        */
 } pt_stats;
 
 typedef struct pt_scene pt_scene; /* immutable device-resident scene */
@@ -175,14 +177,30 @@ int pt_scene_info(const pt_scene *scene, uint64_t *n_tris, uint64_t *n_prims, ui
                   uint64_t *device_bytes);
 
 /* ---- ray_cast (renderer/utils.rs:11-21): first element of the sorted hit list ---- */
+/* The fixed-batch entry points below load the batch into the renderer's own ray queues and trace it with the SAME
+ * kernels that render (k_extend / k_shadow): what they return is what the hot path computes.  Batches of any size
+ * are processed in chunks of 16 Mi rays.  Calls on one scene are serialised (host mutex + a device event), so they
+ * may be issued from several threads / streams. */
 /* rays: n*6 host floats (origin xyz, direction xyz); out: n host pt_hit. */
 int pt_trace_closest(const pt_scene *scene, const float *rays, size_t n, pt_hit *out);
 /* Same on device pointers (rays_dev, out_dev on the scene's device), on `stream`
  * (a cudaStream_t passed as void*; NULL = default stream). */
 int pt_trace_closest_device(const pt_scene *scene, const float *rays_dev, size_t n, pt_hit *out_dev,
                             void *stream);
-/* Directional-light shadow semantics of get_light_info (renderer/mod.rs:291-297):
- * product over every hit of (1 - opacity(hit uv)); out: n floats. */
+/* The hit render_pixel shades after its alpha walk (renderer/mod.rs:188-205): the first hit of the sorted list with
+ * opacity >= 1, or with opacity > 0.001 and a uniform draw below it; the farthest hit when none is accepted.  Ray i
+ * uses the draws of path (pixel = i, sample, seed) at `bounce` (the Philox addressing of DESIGN.md).  n < 2^31. */
+int pt_trace_accepted(const pt_scene *scene, const float *rays, size_t n, uint32_t bounce, uint32_t sample,
+                      uint64_t seed, pt_hit *out);
+/* Shadow walk of get_light_info (renderer/mod.rs:281-333): out[i] = product over the hits of ray i of (1 - opacity).
+ * limits == primary == NULL: directional light (mod.rs:291-297: every hit counts, opacity sampled at the occluder's
+ * own uv).  Otherwise a point light (mod.rs:301-330): limits[i] = |hit - light|, primary = n*5 floats (position xyz of
+ * the primary hit, its texture coordinates u v; u = NaN when the primary hit is a sphere): occluders farther than
+ * limits[i] from the primary hit are ignored and the occluder's opacity is sampled with the PRIMARY hit's
+ * uv/variant (mod.rs:324). */
+int pt_trace_shadow(const pt_scene *scene, const float *rays, const float *limits, const float *primary, size_t n,
+                    float *out);
+/* pt_trace_shadow(scene, rays, NULL, NULL, n, out). */
 int pt_trace_transmittance(const pt_scene *scene, const float *rays, size_t n, float *out);
 
 /* ---- Triangle::intersect (scene/internal/triangle.rs:37-82) on n independent (ray, triangle) pairs ---- */
@@ -190,6 +208,11 @@ int pt_trace_transmittance(const pt_scene *scene, const float *rays, size_t n, f
  * 1 back-face hit (Hit::Triangle.is_backface); t,u,v as tested by triangle.rs:200-233. */
 int pt_triangle_intersect(const pt_scene *scene_or_null, int device, const float *rays, const float *tris, size_t n,
                           pt_hit *out);
+
+/* ---- the random source: StdRng::seed_from_u64 + gen::<f32>() of renderer/mod.rs:110-118 is replaced by the
+ * counter-based Philox4x32-10 (north star); this evaluates the device generator on n caller-chosen (counter[4],
+ * key[2]) pairs so that it can be checked against the published Random123 known-answer vectors.  Host pointers. */
+int pt_philox4x32_10(int device, const uint32_t *counters, const uint32_t *keys, size_t n, uint32_t *out);
 
 /* ---- render_pixel (renderer/mod.rs:172-228), one recorded path per requested pixel ---- */
 /* Traces sample `sample` of each pixel in pixels[0..n_paths) with the profile's resolution/bounces and records

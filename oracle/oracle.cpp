@@ -11,6 +11,7 @@
 // compute_radiance :230-278, get_light_info :281-333, post_processing :335-353.
 #include <atomic>
 #include <chrono>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <thread>
@@ -102,15 +103,14 @@ V3 render_pixel(const Scene &s, const pt_profile &prof, V3 ro, V3 rd, PathRng &r
     const Hit *hit = nullptr;
     MaterialSample mat{};
     V3 normal{};
-    uint32_t j = 0;
-    for (const Hit &h : hits) {
+    for (const Hit &h : hits) {  // alpha walk, mod.rs:188-205
       mat = hit_material_sample(s, h, h.model);
       normal = hit_shading_normal(s, h, h.model);
       hit = &h;
       float op = mat.opacity;
       if (op >= 1.0f) break;
       if (op > 0.001f) {
-        if (rng.alpha(bounce, j++) < op) break;
+        if (rng.alpha(bounce, (uint32_t)h.prim_id) < op) break;
       }
     }
     V3 view = -1.0f * rd;
@@ -238,6 +238,87 @@ int oracle_trace_closest(const void *sp, const float *rays, size_t n, pt_hit *ou
     });
   for (auto &t : pool) t.join();
   return 0;
+}
+
+// The hit render_pixel shades after its alpha walk (mod.rs:188-205), for ray i with the Philox draws of path
+// (pixel = i, sample, seed) at `bounce`: the checker of pt_trace_accepted.
+int oracle_trace_accepted(const void *sp, const float *rays, size_t n, uint32_t bounce, uint32_t sample, uint64_t seed,
+                          pt_hit *out, int brute, int threads) {
+  const Scene &s = *(const Scene *)sp;
+  if (threads < 1) threads = 1;
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; ++t)
+    pool.emplace_back([&, t]() {
+      std::vector<Hit> hits;
+      for (size_t i = t; i < n; i += threads) {
+        const float *r = rays + i * 6;
+        ray_cast(s, v3(r[0], r[1], r[2]), v3(r[3], r[4], r[5]), hits, brute != 0);
+        if (hits.empty()) {
+          out[i] = pt_hit{-1, 0, 0, 0};
+          continue;
+        }
+        PathRng rng;
+        rng.init_philox((uint32_t)i, sample, seed);
+        const Hit *hit = nullptr;
+        for (const Hit &h : hits) {
+          hit = &h;
+          float op = hit_material_sample(s, h, h.model).opacity;
+          if (op >= 1.0f) break;
+          if (op > 0.001f) {
+            if (rng.alpha(bounce, (uint32_t)h.prim_id) < op) break;
+          }
+        }
+        out[i] = pt_hit{hit->prim_id, hit->dist, hit->u, hit->v};
+      }
+    });
+  for (auto &t : pool) t.join();
+  return 0;
+}
+
+// Shadow walk of get_light_info (mod.rs:281-333) with unit light colour: the checker of pt_trace_shadow.
+// limits == nullptr: directional (every hit, occluder sampled at its own uv).  Else point light: limits[i] = distance
+// of the light from the primary hit, primary = n*5 floats (position, uv of the primary hit; u NaN = sphere).
+int oracle_trace_shadow(const void *sp, const float *rays, const float *limits, const float *primary, size_t n, float *out,
+                        int brute, int threads) {
+  const Scene &s = *(const Scene *)sp;
+  if (threads < 1) threads = 1;
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; ++t)
+    pool.emplace_back([&, t]() {
+      std::vector<Hit> hits;
+      for (size_t i = t; i < n; i += threads) {
+        const float *r = rays + i * 6;
+        ray_cast(s, v3(r[0], r[1], r[2]), v3(r[3], r[4], r[5]), hits, brute != 0);
+        float tr = 1.0f;
+        if (!limits) {
+          for (const Hit &h : hits) {
+            tr *= 1.0f - hit_material_sample(s, h, h.model).opacity;
+            if (tr == 0.0f) break;
+          }
+        } else {
+          const float *p = primary + i * 5;
+          Hit prim{};
+          prim.position = v3(p[0], p[1], p[2]);
+          prim.is_sphere = !(p[3] == p[3]);
+          prim.tex_coords = {p[3], p[4]};
+          for (const Hit &h : hits) {
+            if (magnitude(h.position - prim.position) > limits[i]) break;  // mod.rs:320-323
+            tr *= 1.0f - hit_material_sample(s, prim, h.model).opacity;     // mod.rs:324
+            if (tr == 0.0f) break;
+          }
+        }
+        out[i] = tr;
+      }
+    });
+  for (auto &t : pool) t.join();
+  return 0;
+}
+
+// Philox4x32-10 on one (counter, key): the known-answer hook of tests/test_oracle_kat.py (Random123 vectors).
+void oracle_philox4x32_10(const uint32_t *ctr4, const uint32_t *key2, uint32_t *out4) {
+  uint32_t c[4] = {ctr4[0], ctr4[1], ctr4[2], ctr4[3]};
+  philox4x32_10(c, key2[0], key2[1]);
+  for (int i = 0; i < 4; ++i) out4[i] = c[i];
 }
 
 // Full sorted hit list of ONE ray (debug / tie analysis).  Returns the number of hits.
@@ -436,37 +517,82 @@ int oracle_dump_bounce_rays(const void *sp, const pt_profile *prof, uint64_t see
                             float *rays_out, uint8_t *valid_out);
 }
 
+// The shadow requests of get_light_info (mod.rs:281-333) toward light `light` from the primary hits (first element of
+// ray_cast, no alpha walk) of a 1-spp Philox trace: ray (origin = hit + normal * bias, direction = -light dir),
+// limit (point: |hit - light|, directional: -1), primary (position, uv; u NaN for a sphere hit).
+extern "C" int oracle_dump_shadow_requests(const void *sp, const pt_profile *prof, uint64_t seed, uint32_t light,
+                                           float *rays_out, float *limits_out, float *primary_out, uint8_t *valid_out) {
+  const Scene &s = *(const Scene *)sp;
+  const uint32_t W = prof->width, H = prof->height;
+  std::vector<Hit> hits;
+  for (uint64_t i = 0; i < (uint64_t)W * H; ++i) {
+    valid_out[i] = 0;
+    if (light >= s.lights.size()) continue;
+    PathRng rng;
+    rng.init_philox((uint32_t)i, 0, seed);
+    V3 o, d;
+    raygen(s, *prof, (uint32_t)(i % W), (uint32_t)(i / W), rng, o, d);
+    ray_cast(s, o, d, hits, false);
+    if (hits.empty()) continue;
+    const Hit &h = hits[0];
+    const pt_light &L = s.lights[light];
+    V3 ori = h.position + h.normal * NORMAL_BIAS;
+    V3 sdir;
+    float limit = -1.0f;
+    if (L.type == PT_LIGHT_DIRECTIONAL) {
+      sdir = -1.0f * v3(L.vec[0], L.vec[1], L.vec[2]);
+    } else {
+      V3 dir = h.position - v3(L.vec[0], L.vec[1], L.vec[2]);
+      limit = magnitude(dir);
+      sdir = -1.0f * normalize(dir);
+    }
+    float r[6] = {ori.x, ori.y, ori.z, sdir.x, sdir.y, sdir.z};
+    std::memcpy(rays_out + i * 6, r, sizeof r);
+    limits_out[i] = limit;
+    float p[5] = {h.position.x, h.position.y, h.position.z, h.is_sphere ? NAN : h.tex_coords.x, h.tex_coords.y};
+    std::memcpy(primary_out + i * 5, p, sizeof p);
+    valid_out[i] = 1;
+  }
+  return 0;
+}
+
 // Implemented separately to keep render_pixel identical to the reference's control flow.
 int oracle_dump_bounce_rays(const void *sp, const pt_profile *prof, uint64_t seed, uint32_t bounce_wanted,
                             float *rays_out, uint8_t *valid_out) {
   const Scene &s = *(const Scene *)sp;
   const uint32_t W = prof->width, H = prof->height;
-  std::vector<Hit> hits;
-  for (uint64_t i = 0; i < (uint64_t)W * H; ++i) {
-    PathRng rng;
-    rng.init_philox((uint32_t)i, 0, seed);
-    V3 o, d;
-    raygen(s, *prof, (uint32_t)(i % W), (uint32_t)(i / W), rng, o, d);
-    valid_out[i] = 0;
-    for (uint32_t bounce = 0; bounce <= bounce_wanted; ++bounce) {
-      if (bounce == bounce_wanted) {
-        float r[6] = {o.x, o.y, o.z, d.x, d.y, d.z};
-        std::memcpy(rays_out + i * 6, r, sizeof r);
-        valid_out[i] = 1;
-        break;
+  const int threads = (int)std::max(1u, std::thread::hardware_concurrency());
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; ++t)
+    pool.emplace_back([&, t]() {
+      std::vector<Hit> hits;
+      for (uint64_t i = t; i < (uint64_t)W * H; i += threads) {
+        PathRng rng;
+        rng.init_philox((uint32_t)i, 0, seed);
+        V3 o, d;
+        raygen(s, *prof, (uint32_t)(i % W), (uint32_t)(i / W), rng, o, d);
+        valid_out[i] = 0;
+        for (uint32_t bounce = 0; bounce <= bounce_wanted; ++bounce) {
+          if (bounce == bounce_wanted) {
+            float r[6] = {o.x, o.y, o.z, d.x, d.y, d.z};
+            std::memcpy(rays_out + i * 6, r, sizeof r);
+            valid_out[i] = 1;
+            break;
+          }
+          ray_cast(s, o, d, hits, false);
+          if (hits.empty()) break;
+          const Hit &h = hits[0];
+          MaterialSample mat = hit_material_sample(s, h, h.model);
+          V3 n = hit_shading_normal(s, h, h.model);
+          CookTorrance brdf(mat);
+          V3 view = -1.0f * d;
+          V3 nd = brdf.sample(n, view, rng.bsdf(bounce, 0), rng.bsdf(bounce, 1));
+          o = h.position + h.normal * NORMAL_BIAS;
+          d = nd;
+          if (!(d.x == d.x && d.y == d.y && d.z == d.z)) break;
+        }
       }
-      ray_cast(s, o, d, hits, false);
-      if (hits.empty()) break;
-      const Hit &h = hits[0];
-      MaterialSample mat = hit_material_sample(s, h, h.model);
-      V3 n = hit_shading_normal(s, h, h.model);
-      CookTorrance brdf(mat);
-      V3 view = -1.0f * d;
-      V3 nd = brdf.sample(n, view, rng.bsdf(bounce, 0), rng.bsdf(bounce, 1));
-      o = h.position + h.normal * NORMAL_BIAS;
-      d = nd;
-      if (!(d.x == d.x && d.y == d.y && d.z == d.z)) break;
-    }
-  }
+    });
+  for (auto &t : pool) t.join();
   return 0;
 }

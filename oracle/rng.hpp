@@ -80,16 +80,22 @@ static inline void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
 
 enum RngMode { RNG_CHACHA = 0, RNG_PHILOX = 1 };
 
-// Named draws.  Philox addressing (must match path-tracer_b200/csrc/philox.cuh):
+// Named draws.  Philox addressing (must match path-tracer_b200/csrc/shade.cuh):
 //   key = (pixel, sample), counter = (block, tag, seed_lo, seed_hi)
 //   jitter          : tag 0, block 0 -> out[0], out[1]
-//   bounce b        : tag b+1, block 0 -> out[0]=r1, out[1]=r2, out[2]=rr, out[3]=alpha draw 0
-//   alpha draw j>=1 : tag b+1, block 1+(j-1)/4, out[(j-1)%4]
+//   bounce b        : tag b+1, block 0 -> out[0]=r1, out[1]=r2, out[2]=rr
+//   alpha draw of the examined hit with global primitive id p at bounce b: tag 0x80000000|(b+1), block p -> out[0]
+// The reference's alpha walk (mod.rs:188-205) draws from the path's sequential stream for every examined hit with
+// 0.001 < opacity < 1 (the ChaCha mode below does exactly that).  In Philox mode the draw is addressed by the hit's
+// primitive id instead of its position in the list: every examined hit still gets its own independent uniform draw,
+// so the accepted hit has the same distribution, and the decision for one hit no longer depends on the hits before
+// it (which lets the CUDA path decide during ONE traversal).  tests/test_oracle_kat.py checks the two modes against
+// each other on the converged alpha_transparency image.
 struct PathRng {
   RngMode mode;
   ChaCha12 cc;
   uint32_t pixel = 0, sample = 0, seed_lo = 0, seed_hi = 0;
-  uint32_t cache[4];
+  uint32_t cache[4] = {0, 0, 0, 0};
   uint32_t cache_tag = 0xffffffffu, cache_block = 0xffffffffu;
 
   void init_chacha(uint64_t seed) {
@@ -111,10 +117,9 @@ struct PathRng {
     return u32_to_unit_f32(cache[lane]);
   }
   float jitter(int axis) { return mode == RNG_CHACHA ? u32_to_unit_f32(cc.next_u32()) : philox(0, 0, axis); }
-  float alpha(uint32_t bounce, uint32_t j) {
+  float alpha(uint32_t bounce, uint32_t prim_id) {
     if (mode == RNG_CHACHA) return u32_to_unit_f32(cc.next_u32());
-    if (j == 0) return philox(bounce + 1, 0, 3);
-    return philox(bounce + 1, 1 + (j - 1) / 4, (int)((j - 1) % 4));
+    return philox(0x80000000u | (bounce + 1), prim_id, 0);
   }
   float bsdf(uint32_t bounce, int which) {
     return mode == RNG_CHACHA ? u32_to_unit_f32(cc.next_u32()) : philox(bounce + 1, 0, which);

@@ -68,7 +68,8 @@ class pt_stats(C.Structure):
     _fields_ = [("samples", C.c_uint64), ("extend_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
                 ("alpha_recasts", C.c_uint64), ("kernel_launches", C.c_uint64), ("ms_total", C.c_float),
                 ("ms_extend", C.c_float), ("ms_shade", C.c_float), ("ms_shadow", C.c_float), ("ms_other", C.c_float),
-                ("extend_launches", C.c_uint64), ("shade_launches", C.c_uint64), ("shadow_launches", C.c_uint64)]
+                ("extend_launches", C.c_uint64), ("shade_launches", C.c_uint64), ("shadow_launches", C.c_uint64),
+                ("alpha_tests", C.c_uint64), ("shadow_dropped", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

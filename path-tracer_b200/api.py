@@ -20,7 +20,8 @@ _LIB = None
 
 EXPORTS = ["pt_last_error", "pt_device_count", "pt_profile_default", "pt_profile_load_yaml", "pt_scene_load_isf",
            "pt_scene_create", "pt_scene_synthetic", "pt_scene_destroy", "pt_set_accel_builder", "pt_scene_accel_info", "pt_scene_upload", "pt_set_kernel_timing", "pt_scene_get_desc", "pt_scene_info",
-           "pt_trace_closest", "pt_trace_closest_device", "pt_trace_transmittance", "pt_triangle_intersect",
+           "pt_trace_closest", "pt_trace_closest_device", "pt_trace_accepted", "pt_trace_shadow", "pt_trace_transmittance",
+           "pt_triangle_intersect", "pt_philox4x32_10",
            "pt_trace_paths", "pt_render_accum_device", "pt_aov_name", "pt_debug_textures", "pt_render_progressive", "pt_convert_gltf", "pt_scene_save_binary",
            "pt_tonemap_device", "pt_render", "pt_scene_replicate", "pt_render_multi", "pt_write_png", "pt_read_png", "pt_free"]
 
@@ -62,7 +63,10 @@ def lib():
         L.pt_trace_closest.argtypes = [vp, vp, C.c_size_t, vp]
         L.pt_trace_closest_device.argtypes = [vp, vp, C.c_size_t, vp, vp]
         L.pt_trace_transmittance.argtypes = [vp, vp, C.c_size_t, vp]
+        L.pt_trace_accepted.argtypes = [vp, vp, C.c_size_t, u32, u32, u64, vp]
+        L.pt_trace_shadow.argtypes = [vp, vp, vp, vp, C.c_size_t, vp]
         L.pt_triangle_intersect.argtypes = [vp, C.c_int, vp, vp, C.c_size_t, vp]
+        L.pt_philox4x32_10.argtypes = [C.c_int, vp, vp, C.c_size_t, vp]
         L.pt_trace_paths.argtypes = [vp, C.POINTER(pt_profile), vp, C.c_size_t, u32, u64, vp, vp]
         L.pt_render_accum_device.argtypes = [vp, C.POINTER(pt_profile), u32, u32, u32, u64, vp, vp, C.POINTER(pt_stats)]
         L.pt_tonemap_device.argtypes = [vp, u32, u32, u32, C.c_int32, vp, C.c_int, vp]
@@ -240,6 +244,25 @@ class Scene:
         _check(lib().pt_trace_transmittance(self.h, rays.ctypes.data, rays.shape[0], out.ctypes.data))
         return out
 
+    # the hit render_pixel shades after its alpha walk (renderer/mod.rs:188-205); ray i = path (pixel i, sample, seed)
+    def trace_accepted(self, rays, bounce=0, sample=0, seed=0):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        out = np.zeros(rays.shape[0], HIT_DTYPE)
+        _check(lib().pt_trace_accepted(self.h, rays.ctypes.data, rays.shape[0], bounce, sample, seed, out.ctypes.data))
+        return out
+
+    # get_light_info's shadow walk (renderer/mod.rs:281-333): directional (limits None) or point-limited
+    def trace_shadow(self, rays, limits=None, primary=None):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        out = np.zeros(rays.shape[0], np.float32)
+        lp = pp = None
+        if limits is not None:
+            limits = np.ascontiguousarray(limits, np.float32).reshape(-1)
+            primary = np.ascontiguousarray(primary, np.float32).reshape(-1, 5)
+            assert len(limits) == len(primary) == len(rays)
+            lp, pp = limits.ctypes.data, primary.ctypes.data
+        _check(lib().pt_trace_shadow(self.h, rays.ctypes.data, lp, pp, rays.shape[0], out.ctypes.data))
+        return out
 
     # render_pixel (renderer/mod.rs:172-228) with a per-bounce record
     def trace_paths(self, profile, pixels, sample=0, seed=0):
@@ -259,6 +282,16 @@ def triangle_intersect(rays, tris, device=0):
     assert len(rays) == len(tris)
     out = np.zeros(len(rays), HIT_DTYPE)
     _check(lib().pt_triangle_intersect(None, device, rays.ctypes.data, tris.ctypes.data, len(rays), out.ctypes.data))
+    return out
+
+
+def philox4x32_10(counters, keys, device=0):
+    """The device Philox4x32-10 on (counter[4], key[2]) pairs -> uint32[n, 4] (known-answer hook)."""
+    c = np.ascontiguousarray(counters, np.uint32).reshape(-1, 4)
+    k = np.ascontiguousarray(keys, np.uint32).reshape(-1, 2)
+    assert len(c) == len(k)
+    out = np.zeros((len(c), 4), np.uint32)
+    _check(lib().pt_philox4x32_10(device, c.ctypes.data, k.ctypes.data, len(c), out.ctypes.data))
     return out
 
 

@@ -13,7 +13,9 @@ namespace ptb {
 struct DevTri {
   float4 a, b, c;
 };
-constexpr uint32_t TRI_FLAG_ALPHA = 1u;  // material can yield opacity < 1 (mod.rs:198-204)
+constexpr uint32_t TRI_FLAG_ALPHA = 1u;    // material can yield opacity < 1 (mod.rs:198-204)
+constexpr uint32_t TRI_FLAG_OPAQUE1 = 2u;  // opacity is exactly 1 with no opacity texture: a shadow walk that meets
+                                           // this primitive multiplies by (1 - 1) = 0 without reading the material
 
 // 64-byte shading record, original triangle order (touched only for examined hits).
 struct DevTriShade {
@@ -112,9 +114,11 @@ enum {
   CTR_SHADOW1 = 3,  // shadow rays emitted with buffer 1  }
   CTR_WORK_EXTEND = 4,  // persistent work-fetch cursors
   CTR_WORK_SHADOW = 5,
+  CTR_HITS = 6,         // length of the ordered hit list (k_hit_list), reset by k_extend
+  CTR_DROPPED = 7,      // shadow-queue entries that did not fit the queue (must stay 0; reported through pt_stats)
   CTR_STAT_EXTEND = 8,  // 64-bit statistics start here (pairs)
   CTR_STAT_SHADOW = 10,
-  CTR_STAT_RECAST = 12,
+  CTR_STAT_ALPHA = 12,  // opacity evaluations of the alpha walk
   CTR_COUNT = 16
 };
 #define CTR_QUEUE(b) (2u * (b))

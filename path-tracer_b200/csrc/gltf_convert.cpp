@@ -583,5 +583,5 @@ extern "C" int pt_convert_gltf(const char *input, const char *output_dir) {
     ptb::set_error("null argument");
     return PT_ERR_INVALID;
   }
-  return ptb::convert_gltf_to_isf(input, output_dir);
+  return ptb::abi_guard([&]() -> int { return ptb::convert_gltf_to_isf(input, output_dir); });
 }

@@ -1,11 +1,30 @@
 // host_api.hpp — internal glue shared by the host translation units of libpt_b200.so.
 #pragma once
+#include <exception>
+#include <new>
 #include <string>
 
 #include "scene_host.hpp"
 
 namespace ptb {
 void set_error(const char *fmt, ...);
+// Nothing may throw across the C ABI (include/pt_b200.h): entry points that parse untrusted files or allocate
+// host memory in proportion to them run their body through this.
+template <typename F>
+int abi_guard(F &&body) noexcept {
+  try {
+    return body();
+  } catch (const std::bad_alloc &) {
+    set_error("out of host memory");
+    return PT_ERR_NOMEM;
+  } catch (const std::exception &e) {
+    set_error("internal error: %s", e.what());
+    return PT_ERR_INVALID;
+  } catch (...) {
+    set_error("internal error");
+    return PT_ERR_INVALID;
+  }
+}
 // Finalises `host`, builds the BVH, uploads to `device`.  Takes ownership of host.  With `accel` (read from an isfb
 // file, kind = PT_ACCEL_*) the tree is validated against the scene and used instead of building one.
 int scene_from_host(HostScene &&host, int device, pt_scene **out, Bvh4 *accel = nullptr, int accel_kind = -1);

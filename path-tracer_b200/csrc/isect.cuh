@@ -1,9 +1,9 @@
-// isect.cuh — device intersection + BVH4 traversal.
+// isect.cuh — device intersection primitives and the BVH4 node test.
 //   Möller–Trumbore      reference scene/internal/triangle.rs:37-82   (bit-exact: un-fused, cgmath order)
 //   sphere quadratic     reference scene/internal/model.rs:26-64
-//   closest / all hits   reference renderer/utils.rs:11-21 (sorted all-hits list; we return list[k])
-// The box culling is a conservative filter only: results must equal brute force over all primitives
-// with the reference's stable (dist, push order) ordering == lexicographic (dist, global prim id).
+// The traversals built from these (traverse.cuh) replace renderer/utils.rs:11-21.  The box culling is a
+// conservative filter only: results must equal brute force over all primitives with the reference's stable
+// (dist, push order) ordering == lexicographic (dist, global prim id).
 #pragma once
 #include <math_constants.h>
 
@@ -42,7 +42,6 @@ struct TraceState {
   int best_id;
   float u, v;
   int idx;        // HitRec.idx encoding
-  uint32_t flags; // TRI_FLAG_* of the best hit
 };
 
 // triangle.rs:37-82 with precomputed edges.  Returns true and t,u,v,det on a hit.
@@ -135,20 +134,8 @@ __device__ __forceinline__ RayPre precompute(const Ray &r) {
   return p;
 }
 
-// Slab test of child k of a node; returns entry parameter or +inf when the ray misses the box.
-__device__ __forceinline__ float slab(float lox, float loy, float loz, float hix, float hiy, float hiz, const Ray &r,
-                                      const RayPre &p, float t_max) {
-  float t0x = (lox - r.o.x) * p.ix, t1x = (hix - r.o.x) * p.ix;
-  float t0y = (loy - r.o.y) * p.iy, t1y = (hiy - r.o.y) * p.iy;
-  float t0z = (loz - r.o.z) * p.iz, t1z = (hiz - r.o.z) * p.iz;
-  float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.0f));
-  float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
-  // conservative: widen the exit by a few ulps (Ize, "Robust BVH ray traversal") plus an absolute term
-  bool hit = tn <= tf * 1.000002f + 1e-7f && tn <= t_max;
-  return hit ? tn : CUDART_INF_F;
-}
-
-// Slab test of the persistent kernels: (plane - o) * inv is evaluated as one fused multiply-add
+// Slab test of child k of a node; returns the entry parameter or +inf when the ray misses the box.
+// (plane - o) * inv is evaluated as one fused multiply-add
 // fma(plane, inv, -o*inv).  The box test is only a conservative filter (boxes are inflated by
 // 4e-6 relative, ~33 ulp, and the exit is widened below), so its rounding may differ from the un-fused arithmetic that
 // Moller-Trumbore must use; the absolute error of either form is ~1 ulp of the coordinate magnitude / |d|.
@@ -205,87 +192,5 @@ __device__ __forceinline__ NodeData load_node(const DevNode *nodes, uint32_t idx
     float _t = ta; ta = tb; tb = _t; \
     uint32_t _r = ra; ra = rb; rb = _r; \
   }
-
-// Intersect every primitive of a leaf; keep the smallest key above (t_lo, id_lo).
-__device__ __forceinline__ void leaf_closest(const DevScene &S, uint32_t ref, const Ray &r, float t_lo, int id_lo,
-                                             TraceState &st, float &t_prune, const RayPre &pre) {
-  if (ref & 0x40000000u) {
-    const DevSphere sp = S.spheres[ref & 0x3FFFFFFFu];
-    float dist[2], tp[2];
-    int exit_only = 0;
-    int n = sphere_hits(r, sp, dist, tp, exit_only);
-    for (int k = 0; k < n; ++k) {
-      int is_exit = (n == 1) ? exit_only : k;
-      int id = sp.prim_id + is_exit;
-      float t = dist[k];
-      if (!key_less(t_lo, id_lo, t, id)) continue;
-      if (key_less(t, id, st.best_t, st.best_id)) {
-        st.best_t = t; st.best_id = id; st.u = 0.f; st.v = 0.f;
-        st.idx = (int)(S.n_tris + 2u * (ref & 0x3FFFFFFFu) + (uint32_t)is_exit);
-        st.flags = sp.flags;
-        t_prune = t * pre.prune_scale;
-      }
-    }
-    return;
-  }
-  uint32_t first = (ref & 0x3FFFFFFFu) >> 3, count = (ref & 7u) + 1u;
-  for (uint32_t i = 0; i < count; ++i) {
-    const float4 *tp = reinterpret_cast<const float4 *>(S.tris + first + i);
-    float4 A = __ldg(tp), B = __ldg(tp + 1), C = __ldg(tp + 2);
-    float t, u, v, det;
-    if (!moller_trumbore(r, mk3(A.x, A.y, A.z), mk3(B.x, B.y, B.z), mk3(C.x, C.y, C.z), t, u, v, det)) continue;
-    int id = __float_as_int(A.w);
-    if (!key_less(t_lo, id_lo, t, id)) continue;
-    if (key_less(t, id, st.best_t, st.best_id)) {
-      st.best_t = t; st.best_id = id; st.u = u; st.v = v;
-      st.idx = __float_as_int(B.w) | (det < 0.0f ? HIT_BACKFACE : 0);
-      st.flags = __float_as_uint(C.w);
-      t_prune = t * pre.prune_scale;
-    }
-  }
-}
-
-// Smallest-key hit with key > (t_lo, id_lo); (t_lo, id_lo) = (-1, -1) for the first hit of the list.
-__device__ __forceinline__ void trace_closest(const DevScene &S, const Ray &r, float t_lo, int id_lo, TraceState &st) {
-  st.best_t = CUDART_INF_F;
-  st.best_id = 0x7FFFFFFF;
-  st.idx = -1;
-  st.u = st.v = 0.f;
-  st.flags = 0;
-  const RayPre pre = precompute(r);
-  float t_prune = CUDART_INF_F;
-  float stk_t[PTB_STACK];
-  uint32_t stk_r[PTB_STACK];
-  int sp = 0;
-  uint32_t cur = 0;  // root node
-  for (;;) {
-    if (!(cur & 0x80000000u)) {
-      const NodeData nd = load_node(S.nodes, cur);
-      const float4 lx = nd.lo_x, ly = nd.lo_y, lz = nd.lo_z, hx = nd.hi_x, hy = nd.hi_y, hz = nd.hi_z;
-      const uint4 ch = nd.ch;
-      float t0 = ch.x == 0xFFFFFFFFu ? CUDART_INF_F : slab(lx.x, ly.x, lz.x, hx.x, hy.x, hz.x, r, pre, t_prune);
-      float t1 = ch.y == 0xFFFFFFFFu ? CUDART_INF_F : slab(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, r, pre, t_prune);
-      float t2 = ch.z == 0xFFFFFFFFu ? CUDART_INF_F : slab(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, r, pre, t_prune);
-      float t3 = ch.w == 0xFFFFFFFFu ? CUDART_INF_F : slab(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, r, pre, t_prune);
-      uint32_t r0 = ch.x, r1 = ch.y, r2 = ch.z, r3 = ch.w;
-      // sorting network, ascending entry distance
-      PTB_CSWAP(t0, r0, t1, r1) PTB_CSWAP(t2, r2, t3, r3) PTB_CSWAP(t0, r0, t2, r2) PTB_CSWAP(t1, r1, t3, r3)
-      PTB_CSWAP(t1, r1, t2, r2)
-      if (t3 < CUDART_INF_F && sp < PTB_STACK) { stk_t[sp] = t3; stk_r[sp] = r3; ++sp; }
-      if (t2 < CUDART_INF_F && sp < PTB_STACK) { stk_t[sp] = t2; stk_r[sp] = r2; ++sp; }
-      if (t1 < CUDART_INF_F && sp < PTB_STACK) { stk_t[sp] = t1; stk_r[sp] = r1; ++sp; }
-      if (t0 < CUDART_INF_F) { cur = r0; continue; }
-    } else {
-      leaf_closest(S, cur, r, t_lo, id_lo, st, t_prune, pre);
-    }
-    // pop the nearest pending entry that can still hold a better key
-    bool found = false;
-    while (sp > 0) {
-      --sp;
-      if (stk_t[sp] <= t_prune) { cur = stk_r[sp]; found = true; break; }
-    }
-    if (!found) break;
-  }
-}
 
 }  // namespace ptb

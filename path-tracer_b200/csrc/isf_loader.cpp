@@ -202,15 +202,17 @@ extern "C" int pt_scene_load_isf(const char *path, int device, pt_scene **out) {
     ptb::set_error("null argument");
     return PT_ERR_INVALID;
   }
-  ptb::HostScene h;
-  if (ptb::is_isfb_file(path)) {  // binary side-car (isf_binary.cpp), told apart by its magic
-    ptb::Bvh4 accel;
-    int kind = -1;
-    int rc = ptb::load_isfb_file(path, h, &accel, &kind);
+  return ptb::abi_guard([&]() -> int {
+    ptb::HostScene h;
+    if (ptb::is_isfb_file(path)) {  // binary side-car (isf_binary.cpp), told apart by its magic
+      ptb::Bvh4 accel;
+      int kind = -1;
+      int rc = ptb::load_isfb_file(path, h, &accel, &kind);
+      if (rc != PT_OK) return rc;
+      return ptb::scene_from_host(std::move(h), device, out, kind >= 0 ? &accel : nullptr, kind);
+    }
+    int rc = ptb::load_isf_file(path, h);
     if (rc != PT_OK) return rc;
-    return ptb::scene_from_host(std::move(h), device, out, kind >= 0 ? &accel : nullptr, kind);
-  }
-  int rc = ptb::load_isf_file(path, h);
-  if (rc != PT_OK) return rc;
-  return ptb::scene_from_host(std::move(h), device, out);
+    return ptb::scene_from_host(std::move(h), device, out);
+  });
 }

@@ -203,6 +203,7 @@ int jpeg_decode(const uint8_t *bytes, size_t size, const char *name, uint32_t ch
       if (dl >= 12 && !std::memcmp(d, "Adobe", 5)) adobe_transform = d[11];
     } else if (m == 0xDA) {  // SOS: the entropy-coded data follows
       if (!have_sof) return bad("SOS before SOF");
+      if (dl < 1) return bad("truncated SOS header");
       const int ns = d[0];
       if (ns != (int)comps.size() || dl < 1 + 2 * (size_t)ns + 3) return bad("non-interleaved scans are not supported");
       for (int k = 0; k < ns; ++k) {

@@ -68,39 +68,46 @@ __device__ __forceinline__ void stat_add(uint32_t *counters, int which, unsigned
 }
 
 // ------------------------------------------------------------------------------------------------
-// Fixed ray batch -> first element of ray_cast's sorted list (pt_trace_closest).
-__global__ void __launch_bounds__(128) k_trace_closest(const __grid_constant__ DevScene S, const float *__restrict__ rays,
-                                                       uint32_t n, pt_hit *__restrict__ out, uint32_t *cursor) {
-  for (;;) {
-    uint32_t q = fetch_work(cursor);
-    if (__all_sync(0xffffffffu, q >= n)) break;
-    if (q >= n) continue;
-    Ray r;
-    r.o = mk3(rays[q * 6 + 0], rays[q * 6 + 1], rays[q * 6 + 2]);
-    r.d = mk3(rays[q * 6 + 3], rays[q * 6 + 4], rays[q * 6 + 5]);
-    TraceState st;
-    trace_closest(S, r, -1.0f, -1, st);
-    pt_hit h;
-    h.prim_id = st.idx < 0 ? -1 : st.best_id;
-    h.t = st.idx < 0 ? 0.f : st.best_t;
-    h.u = st.u;
-    h.v = st.v;
-    out[q] = h;
+// Fixed ray batches (pt_trace_closest / pt_trace_accepted / pt_trace_shadow): the batch is loaded into the wave
+// queues and traced by the SAME kernels that render (k_extend, k_shadow) - the parity harness runs the production
+// traversal, not a side kernel.  Queue position q of the chunk holds ray `slot_base + q`; the slot doubles as the
+// "pixel" of the RNG key in alpha mode.
+__global__ void __launch_bounds__(256) k_load_rays(const float *__restrict__ rays, uint32_t n, uint32_t slot_base,
+                                                   WaveState W, uint32_t buf) {
+  const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q == 0) {
+    W.counters[CTR_QUEUE(buf)] = n;
+    W.counters[CTR_WORK_EXTEND] = 0;
   }
+  if (q >= n) return;
+  const float *r = rays + (size_t)q * 6;
+  W.ray_o[buf][q] = make_float4(r[0], r[1], r[2], 0.f);
+  W.ray_d[buf][q] = make_float4(r[3], r[4], r[5], __int_as_float((int)(slot_base + q)));
 }
 
-__global__ void __launch_bounds__(128) k_trace_transmittance(const __grid_constant__ DevScene S,
-                                                             const float *__restrict__ rays, uint32_t n,
-                                                             float *__restrict__ out, uint32_t *cursor) {
-  for (;;) {
-    uint32_t q = fetch_work(cursor);
-    if (__all_sync(0xffffffffu, q >= n)) break;
-    if (q >= n) continue;
-    Ray r;
-    r.o = mk3(rays[q * 6 + 0], rays[q * 6 + 1], rays[q * 6 + 2]);
-    r.d = mk3(rays[q * 6 + 3], rays[q * 6 + 4], rays[q * 6 + 5]);
-    out[q] = trace_transmittance(S, r, -1.0f, mk3(0, 0, 0), 0.f, 0.f);
+// Shadow-queue entries of a batch: limits[q] >= 0 = point light at that distance from the primary hit prim[q] =
+// (position xyz, uv of the primary hit; u NaN = the primary hit is a sphere); limits == nullptr: directional.
+// The contribution is (1, 1, 1), so k_shadow leaves the transmittance itself in radiance[q].x.
+__global__ void __launch_bounds__(256) k_load_shadow(const float *__restrict__ rays, const float *__restrict__ limits,
+                                                     const float *__restrict__ prim, uint32_t n, WaveState W,
+                                                     uint32_t which) {
+  const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q == 0) {
+    W.counters[CTR_SHADOW(which)] = n;
+    W.counters[CTR_WORK_SHADOW] = 0;
   }
+  if (q >= n) return;
+  const float *r = rays + (size_t)q * 6;
+  const float *p = prim ? prim + (size_t)q * 5 : nullptr;
+  W.sh_o[q] = make_float4(r[0], r[1], r[2], limits ? limits[q] : -1.0f);
+  W.sh_d[q] = make_float4(r[3], r[4], r[5], __int_as_float((int)q));
+  W.sh_c[q] = make_float4(1.f, 1.f, 1.f, p ? p[3] : 0.f);
+  W.sh_p[q] = make_float4(p ? p[0] : 0.f, p ? p[1] : 0.f, p ? p[2] : 0.f, p ? p[4] : 0.f);
+  W.radiance[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+__global__ void __launch_bounds__(256) k_store_transmittance(WaveState W, uint32_t n, float *__restrict__ out) {
+  const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q < n) out[q] = W.radiance[q].x;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -247,29 +254,29 @@ constexpr int REFILL_THRESHOLD = PTB_REFILL_T;  // refill when fewer lanes than 
 constexpr int REFILL_THRESHOLD_SHADOW = PTB_REFILL_T_SHADOW;
 constexpr int LEAF_THRESHOLD = PTB_LEAF_T;      // run the (divergent) primitive test once this many lanes wait at a leaf
 
-// extend: closest accepted hit (alpha walk included) of every queued ray.  Persistent warps with lane-level ray
-// replacement; inside a warp, lanes that reach a leaf wait until LEAF_THRESHOLD lanes have one (or nobody is at an
-// inner node any more), so that node visits and primitive tests each run with most lanes active ("while-while").
+// extend: the hit that render_pixel shades (closest hit, alpha walk included) of every queued ray.  Persistent warps
+// with lane-level ray replacement; inside a warp, lanes that reach a leaf wait until LEAF_THRESHOLD lanes have one (or
+// nobody is at an inner node any more), so that node visits and primitive tests each run with most lanes active
+// ("while-while").  alpha_on = 0 gives the first element of ray_cast's list instead (pt_trace_closest); trace_out,
+// when not null, also receives the public hit record of every queue position (the fixed-batch parity harness).
 __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
-                                                WaveState W, uint32_t bounce) {
+                                                WaveState W, uint32_t bounce, uint32_t alpha_on, pt_hit *__restrict__ trace_out) {
   const uint32_t in = bounce & 1u, outb = in ^ 1u;
   const uint32_t n = W.counters[CTR_QUEUE(in)];
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     W.counters[CTR_QUEUE(outb)] = 0;  // the queues k_shade(bounce) appends to
     W.counters[CTR_SHADOW(outb)] = 0;
     W.counters[CTR_WORK_SHADOW] = 0;
-#if PTB_HIT_LIST
-    W.counters[6] = 0;  // CTR_HITS: filled by k_hit_list after this kernel
-#endif
+    W.counters[CTR_HITS] = 0;  // filled by k_hit_list after this kernel
     stat_add(W.counters, CTR_STAT_EXTEND, n);
   }
   constexpr uint32_t NONE = 0xFFFFFFFFu;
-  uint32_t recasts = 0;
+  const bool alpha = alpha_on != 0;
+  uint32_t n_alpha = 0;
   ClosestTrav tv;
   NodeOrder no{};
   ClosestStack stk;
-  uint32_t q = NONE, slot = 0, alpha_j = 0;
-  bool recorded = false;
+  uint32_t q = NONE, slot = 0;
   tv.cur = ClosestTrav::DONE;
 #if PTB_FETCH_AHEAD_EXTEND
   WorkFetch wf;
@@ -295,10 +302,8 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
       r.o = mk3(o4.x, o4.y, o4.z);
       r.d = mk3(d4.x, d4.y, d4.z);
       slot = (uint32_t)__float_as_int(d4.w);
-      alpha_j = 0;
-      tv.begin(r, -1.0f, -1);
+      tv.begin(r, stk, alpha);
       no = node_order(tv.r, tv.pre);
-      recorded = false;
     }
     if (__ballot_sync(0xffffffffu, q != NONE) == 0) break;
     for (;;) {
@@ -307,39 +312,30 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
       const bool leaf = has && tv.at_leaf();
       const uint32_t m_leaf = __ballot_sync(0xffffffffu, leaf);
       const uint32_t m_inner = __ballot_sync(0xffffffffu, has && tv.at_inner());
-      if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) tv.leaf_step(S, stk);
-#if PTB_MERGED_POP
-      if (has && tv.cur == ClosestTrav::NEED_POP) tv.pop(stk);
-#endif
+      if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0))
+        tv.leaf_step(S, stk, alpha, bounce, [&]() { return make_key(P, slot); }, n_alpha);
       if (has && tv.cur == ClosestTrav::DONE) {
-        bool done = true;
-        if (tv.st.idx >= 0) {
-          // record the examined hit: it is shaded unless a later hit of the alpha walk replaces it (mod.rs:188-205)
-          st_wave(&W.hit[q], make_float4(tv.st.best_t, tv.st.u, tv.st.v, __int_as_float(tv.st.idx)));
-          recorded = true;
-          if (S.any_alpha && (tv.st.flags & TRI_FLAG_ALPHA)) {
-            float op = hit_opacity(S, tv.st.idx, tv.st.u, tv.st.v);
-            bool accept = op >= 1.0f;
-            if (!accept && op > 0.001f) accept = rng_alpha(make_key(P, slot), bounce, alpha_j++) < op;
-            if (!accept) {
-              tv.restart_behind();
-              ++recasts;
-              done = false;
-            }
-          }
+        tv.finish(stk, alpha);
+        const bool hit = tv.st.idx >= 0;
+        st_wave(&W.hit[q], hit ? make_float4(tv.st.best_t, tv.st.u, tv.st.v, __int_as_float(tv.st.idx))
+                               : make_float4(0.f, 0.f, 0.f, __int_as_float(-1)));
+        if (trace_out) {
+          pt_hit h;
+          h.prim_id = hit ? tv.st.best_id : -1;
+          h.t = hit ? tv.st.best_t : 0.f;
+          h.u = hit ? tv.st.u : 0.f;
+          h.v = hit ? tv.st.v : 0.f;
+          trace_out[q] = h;
         }
-        if (done) {
-          if (!recorded) st_wave(&W.hit[q], make_float4(0.f, 0.f, 0.f, __int_as_float(-1)));  // miss
-          q = NONE;
-        }
+        q = NONE;
       }
       const uint32_t busy = __ballot_sync(0xffffffffu, q != NONE);
       if (busy == 0 || (!drained && __popc(busy) < REFILL_THRESHOLD)) break;
     }
   }
 #undef drained
-  recasts = __reduce_add_sync(0xffffffffu, recasts);
-  if (lane_id() == 0 && recasts) stat_add(W.counters, CTR_STAT_RECAST, recasts);
+  n_alpha = __reduce_add_sync(0xffffffffu, n_alpha);
+  if (lane_id() == 0 && n_alpha) stat_add(W.counters, CTR_STAT_ALPHA, n_alpha);
 }
 
 // Warp-aggregated append to the path queue AND the shadow queue filled with it: one 64-bit atomic per warp reserves
@@ -365,7 +361,6 @@ __device__ __forceinline__ void warp_append2(uint32_t *pair, bool want_path, boo
 // unused w component of the INPUT queue's origin records (entry i in ray_o[in][i].w), which k_shade only reads; its
 // length is counters[CTR_HITS], reset by k_extend.
 #if PTB_HIT_LIST
-constexpr uint32_t CTR_HITS = 6;  // a free slot of the counters[] layout (device_scene.cuh)
 __global__ void __launch_bounds__(256) k_hit_list(const __grid_constant__ DevScene S, WaveState W, uint32_t bounce) {
   const uint32_t in = bounce & 1u;
   const uint32_t n = W.counters[CTR_QUEUE(in)];
@@ -456,6 +451,7 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
       if (li + 1 == nl) break;
       uint32_t pp, ps;
       warp_append2(pair, false, want, pp, ps);
+      if (want && ps >= W.shadow_capacity) atomicAdd(&W.counters[CTR_DROPPED], 1u);
       if (want && ps < W.shadow_capacity) {
         st_wave(&W.sh_o[ps], make_float4(so.x, so.y, so.z, limit));
         st_wave(&W.sh_d[ps], make_float4(sd.x, sd.y, sd.z, __int_as_float((int)slot)));
@@ -470,6 +466,7 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
     if (active) alive = shade_finish(P, make_key(P, slot), bounce, ctx, thr, next);
     uint32_t pp, ps;
     warp_append2(pair, alive, want, pp, ps);
+    if (want && ps >= W.shadow_capacity) atomicAdd(&W.counters[CTR_DROPPED], 1u);
     if (want && ps < W.shadow_capacity) {
       st_wave(&W.sh_o[ps], make_float4(so.x, so.y, so.z, limit));
       st_wave(&W.sh_d[ps], make_float4(sd.x, sd.y, sd.z, __int_as_float((int)slot)));
@@ -500,10 +497,10 @@ __global__ void __launch_bounds__(128) k_trace_paths(const __grid_constant__ Dev
   Ray r = generate_ray(S, P, key);
   V3 thr = mk3(1.f, 1.f, 1.f), rad = mk3(0.f, 0.f, 0.f);
   pt_path_vertex *rec = out + (size_t)i * (P.bounces + 1);
-  uint32_t nv = 0, recasts = 0;
+  uint32_t nv = 0, n_alpha = 0;
   for (uint32_t bounce = 0; bounce <= P.bounces; ++bounce) {
     TraceState st;
-    extend_ray(S, key, bounce, r, st, recasts);
+    trace_closest(S, r, S.any_alpha != 0, key, bounce, st, n_alpha);
     ShadeCtx ctx;
     shade_begin(S, r, st.best_t, st.u, st.v, st.idx, thr, rad, ctx);
     if (ctx.lit) {
@@ -558,6 +555,18 @@ __global__ void __launch_bounds__(256) k_triangle_intersect(const float *__restr
   out[i] = h;
 }
 
+// The device generator on caller-chosen (counter, key) pairs: the known-answer hook (pt_philox4x32_10).
+__global__ void __launch_bounds__(256) k_philox(const uint32_t *__restrict__ ctr, const uint32_t *__restrict__ key, uint32_t n,
+                                                uint32_t *__restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint4 r = philox4x32_10(make_uint4(ctr[i * 4], ctr[i * 4 + 1], ctr[i * 4 + 2], ctr[i * 4 + 3]), key[i * 2], key[i * 2 + 1]);
+  out[i * 4] = r.x;
+  out[i * 4 + 1] = r.y;
+  out[i * 4 + 2] = r.z;
+  out[i * 4 + 3] = r.w;
+}
+
 // debug_render / render_debug_pixels (renderer/debug_renderer.rs:11-105): one pixel-centre ray per pixel, the first
 // element of ray_cast (no alpha walk), seven AOV planes: normal, albedo, opacity, metalness, roughness, emissive, ior.
 // planes: 7 * W*H*3 bytes (caller-zeroed: pixels without a hit stay 0); n_hit counts the pixels that hit something.
@@ -582,7 +591,8 @@ __global__ void __launch_bounds__(128) k_debug_aov(const __grid_constant__ DevSc
     r.d = ((c0 * dir.x + c1 * dir.y) + c2 * dir.z) + c3 * 0.0f;
     r.o = c3;
     TraceState st;
-    trace_closest(S, r, -1.0f, -1, st);
+    uint32_t unused = 0;
+    trace_closest(S, r, false, RngKey{}, 0u, st, unused);
     if (st.idx >= 0) {
       got = true;
       const Surface sf = make_surface(S, r, st.best_t, st.u, st.v, st.idx);
@@ -743,17 +753,22 @@ static int resident_grid(K kernel, int threads) {
   return sm_count() * per_sm;
 }
 
-void launch_trace_closest(const DevScene &S, const float *rays, uint32_t n, pt_hit *out, uint32_t *cursor, cudaStream_t st) {
-  cudaMemsetAsync(cursor, 0, sizeof(uint32_t), st);
-  k_trace_closest<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, rays, n, out, cursor);
+void launch_load_rays(const float *rays, uint32_t n, uint32_t slot_base, const WaveState &W, uint32_t buf, cudaStream_t st) {
+  k_load_rays<<<(n + 255) / 256, 256, 0, st>>>(rays, n, slot_base, W, buf);
 }
-void launch_trace_transmittance(const DevScene &S, const float *rays, uint32_t n, float *out, uint32_t *cursor, cudaStream_t st) {
-  cudaMemsetAsync(cursor, 0, sizeof(uint32_t), st);
-  k_trace_transmittance<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, rays, n, out, cursor);
+void launch_load_shadow(const float *rays, const float *limits, const float *prim, uint32_t n, const WaveState &W,
+                        uint32_t which, cudaStream_t st) {
+  k_load_shadow<<<(n + 255) / 256, 256, 0, st>>>(rays, limits, prim, n, W, which);
+}
+void launch_store_transmittance(const WaveState &W, uint32_t n, float *out, cudaStream_t st) {
+  k_store_transmittance<<<(n + 255) / 256, 256, 0, st>>>(W, n, out);
 }
 void launch_trace_paths(const DevScene &S, const WaveParams &P, const uint32_t *pixels, uint32_t n, pt_path_vertex *out,
                         uint32_t *counts, cudaStream_t st) {
   k_trace_paths<<<(n + 127) / 128, 128, 0, st>>>(S, P, pixels, n, out, counts);
+}
+void launch_philox(const uint32_t *ctr, const uint32_t *key, uint32_t n, uint32_t *out, cudaStream_t st) {
+  k_philox<<<(n + 255) / 256, 256, 0, st>>>(ctr, key, n, out);
 }
 void launch_triangle_intersect(const float *rays, const float *tris, uint32_t n, pt_hit *out, cudaStream_t st) {
   k_triangle_intersect<<<(n + 255) / 256, 256, 0, st>>>(rays, tris, n, out);
@@ -765,8 +780,9 @@ void launch_init_srgb_lut(float *lut, cudaStream_t st) { k_init_srgb_lut<<<1, 25
 void launch_raygen(const DevScene &S, const WaveParams &P, const WaveState &W, cudaStream_t st) {
   k_raygen<<<(P.n_paths + 255) / 256, 256, 0, st>>>(S, P, W);
 }
-void launch_extend(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st) {
-  k_extend<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, P, W, bounce);
+void launch_extend(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, bool alpha,
+                   pt_hit *trace_out, cudaStream_t st) {
+  k_extend<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, P, W, bounce, alpha ? 1u : 0u, trace_out);
 }
 void launch_shade(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st) {
   static std::atomic<int> cache[MAX_DEVICES];

@@ -4,15 +4,21 @@
 #include "device_scene.cuh"
 
 namespace ptb {
-void launch_trace_closest(const DevScene &S, const float *rays, uint32_t n, pt_hit *out, uint32_t *cursor, cudaStream_t st);
-void launch_trace_transmittance(const DevScene &S, const float *rays, uint32_t n, float *out, uint32_t *cursor, cudaStream_t st);
+// fixed ray batches through the wave queues (the parity harness of k_extend / k_shadow)
+void launch_load_rays(const float *rays, uint32_t n, uint32_t slot_base, const WaveState &W, uint32_t buf, cudaStream_t st);
+void launch_load_shadow(const float *rays, const float *limits, const float *prim, uint32_t n, const WaveState &W,
+                        uint32_t which, cudaStream_t st);
+void launch_store_transmittance(const WaveState &W, uint32_t n, float *out, cudaStream_t st);
 void launch_trace_paths(const DevScene &S, const WaveParams &P, const uint32_t *pixels, uint32_t n, pt_path_vertex *out,
                         uint32_t *counts, cudaStream_t st);
+void launch_philox(const uint32_t *ctr, const uint32_t *key, uint32_t n, uint32_t *out, cudaStream_t st);
 void launch_triangle_intersect(const float *rays, const float *tris, uint32_t n, pt_hit *out, cudaStream_t st);
 void launch_debug_aov(const DevScene &S, uint32_t width, uint32_t height, uint8_t *planes, uint32_t *n_hit, cudaStream_t st);
 void launch_init_srgb_lut(float *lut, cudaStream_t st);
 void launch_raygen(const DevScene &S, const WaveParams &P, const WaveState &W, cudaStream_t st);
-void launch_extend(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st);
+// alpha = false: first element of ray_cast's list; trace_out (optional): pt_hit per queue position
+void launch_extend(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, bool alpha,
+                   pt_hit *trace_out, cudaStream_t st);
 void launch_shade(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st);
 int shade_launches();  // kernels launch_shade enqueues (the hit-list scan pass + k_shade)
 void launch_shadow(const DevScene &S, const WaveState &W, uint32_t bounce, cudaStream_t st);

@@ -2,10 +2,9 @@
 // record kernel (k_trace_paths).  Each function is the sm_100a equivalent of one piece of the reference's
 // render_pixel loop (file:line relative to the reference root):
 //   generate_ray        renderer/mod.rs:107-124 + scene/internal/camera.rs:36-48
-//   extend_ray          renderer/utils.rs:11-21 (closest element of the sorted list) + alpha walk mod.rs:188-205
 //   shade_begin         mod.rs:184-186 (miss), hit.rs:55-137 (surface), material_sample.rs, mod.rs:245 (emissive)
 //   light_request       mod.rs:248-262 + the un-shadowed part of get_light_info mod.rs:281-333
-//   trace_transmittance the all-hits shadow walk of get_light_info mod.rs:291-297 / :319-329
+//   (the traversals themselves - ray_cast, the alpha walk, the shadow walk - are in traverse.cuh)
 //   shade_finish        mod.rs:265-275 (GGX sample + throughput), :219-221 (cutoff), utils.rs:23-31 (roulette)
 #pragma once
 #include "shade.cuh"
@@ -55,98 +54,6 @@ __device__ __forceinline__ float hit_opacity(const DevScene &S, int idx, float b
   float tu = (u0x + bu * (u1x - u0x)) + bv * (u2x - u0x);
   float tv = (u0y + bu * (u1y - u0y)) + bv * (u2y - u0y);
   return eval_opacity(S, __float_as_int(q3.w), false, tu, tv);
-}
-
-// Closest accepted hit.  The alpha walk of render_pixel (mod.rs:188-205) is done by re-casting from the rejected
-// hit's key: accept the first hit with opacity >= 1 or a winning draw, else the farthest examined hit.
-__device__ __forceinline__ void extend_ray(const DevScene &S, const RngKey &key, uint32_t bounce, const Ray &r,
-                                           TraceState &st, uint32_t &recasts) {
-  trace_closest(S, r, -1.0f, -1, st);
-  if (S.any_alpha && st.idx >= 0 && (st.flags & TRI_FLAG_ALPHA)) {
-    uint32_t j = 0;
-    for (;;) {
-      float op = hit_opacity(S, st.idx, st.u, st.v);
-      if (op >= 1.0f) break;
-      if (op > 0.001f) {
-        if (rng_alpha(key, bounce, j++) < op) break;
-      }
-      TraceState nx;
-      trace_closest(S, r, st.best_t, st.best_id, nx);
-      ++recasts;
-      if (nx.idx < 0) break;  // nothing behind: the last examined hit is shaded
-      st = nx;
-    }
-  }
-}
-
-// All-hits transmittance walk.
-//   limit < 0: directional light (every hit on the ray, occluder sampled at its own uv, mod.rs:291-297)
-//   limit >= 0: point light at distance `limit` from `pos`; occluders farther than the light are ignored and
-//   the occluder's material is sampled with the PRIMARY hit's uv/variant (mod.rs:319-329, pu NaN = sphere).
-__device__ __forceinline__ float trace_transmittance(const DevScene &S, const Ray &r, float limit, V3 pos, float pu,
-                                                     float pv) {
-  const RayPre pre = precompute(r);
-  const bool point = limit >= 0.0f;
-  float t_max = CUDART_INF_F;
-  if (point) {
-    float len = length3(r.d);
-    float bias = length3(r.o - pos);
-    t_max = len > 0.f ? (limit + bias) / len * 1.0002f + 1e-6f : CUDART_INF_F;
-  }
-  float tr = 1.0f;
-  uint32_t stk[PTB_STACK];
-  int sp = 0;
-  uint32_t cur = 0;
-  for (;;) {
-    if (!(cur & 0x80000000u)) {
-      const NodeData nd = load_node(S.nodes, cur);
-      const float4 lx = nd.lo_x, ly = nd.lo_y, lz = nd.lo_z, hx = nd.hi_x, hy = nd.hi_y, hz = nd.hi_z;
-      const uint4 ch = nd.ch;
-      if (ch.x != 0xFFFFFFFFu && slab(lx.x, ly.x, lz.x, hx.x, hy.x, hz.x, r, pre, t_max) < CUDART_INF_F) stk[sp++] = ch.x;
-      if (ch.y != 0xFFFFFFFFu && slab(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, r, pre, t_max) < CUDART_INF_F) stk[sp++] = ch.y;
-      if (ch.z != 0xFFFFFFFFu && slab(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, r, pre, t_max) < CUDART_INF_F) stk[sp++] = ch.z;
-      if (ch.w != 0xFFFFFFFFu && slab(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, r, pre, t_max) < CUDART_INF_F) stk[sp++] = ch.w;
-    } else if (cur & 0x40000000u) {
-      const DevSphere s = S.spheres[cur & 0x3FFFFFFFu];
-      float dist[2], tp[2];
-      int exit_only = 0;
-      int nh = sphere_hits(r, s, dist, tp, exit_only);
-      for (int k = 0; k < nh; ++k) {
-        if (point) {
-          V3 p = r.o + r.d * tp[k];
-          if (length3(p - pos) > limit) continue;
-        }
-        // with a point light the PRIMARY hit's variant decides simple/textured (mod.rs:324)
-        float op = point ? eval_opacity(S, s.model, pu != pu, pu, pv) : S.materials[s.model].opacity;
-        tr *= 1.0f - op;
-      }
-    } else {
-      uint32_t first = (cur & 0x3FFFFFFFu) >> 3, count = (cur & 7u) + 1u;
-      for (uint32_t i = 0; i < count; ++i) {
-        const float4 *tp = reinterpret_cast<const float4 *>(S.tris + first + i);
-        float4 A = __ldg(tp), B = __ldg(tp + 1), C = __ldg(tp + 2);
-        float t, u, v, det;
-        if (!moller_trumbore(r, mk3(A.x, A.y, A.z), mk3(B.x, B.y, B.z), mk3(C.x, C.y, C.z), t, u, v, det)) continue;
-        int tri = __float_as_int(B.w);
-        float op;
-        if (point) {
-          V3 p = r.o + r.d * t;
-          if (length3(p - pos) > limit) continue;
-          op = eval_opacity(S, S.shade[tri].model, pu != pu, pu, pv);
-        } else if (__float_as_uint(C.w) & TRI_FLAG_ALPHA) {
-          op = hit_opacity(S, tri, u, v);
-        } else {
-          op = S.materials[S.shade[tri].model].opacity;
-        }
-        tr *= 1.0f - op;
-        if (tr == 0.0f) return 0.0f;
-      }
-    }
-    if (tr == 0.0f) return 0.0f;
-    if (sp == 0) break;
-    cur = stk[--sp];
-  }
-  return tr;
 }
 
 struct ShadeCtx {

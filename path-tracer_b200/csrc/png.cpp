@@ -82,6 +82,11 @@ int png_decode(const uint8_t *bytes, size_t size, const char *path, uint32_t cha
     set_error("%s: unsupported PNG (color type %d, depth %d, interlace %d)", path, ctype, depth, interlace);
     return PT_ERR_PARSE;
   }
+  // untrusted header: cap the sides so that (stride + 1) * h cannot overflow or ask for an absurd allocation
+  if (w > 65536u || h > 65536u || (uint64_t)w * h * (uint64_t)nch * (depth > 8 ? 2 : 1) > (1ull << 31)) {
+    set_error("%s: PNG too large (%u x %u)", path, w, h);
+    return PT_ERR_PARSE;
+  }
   const size_t bpp_bits = (size_t)nch * depth;
   const size_t stride = ((size_t)w * bpp_bits + 7) / 8;
   const size_t bpp = std::max<size_t>(1, bpp_bits / 8);
@@ -222,13 +227,15 @@ int pt_read_png(const char *path, uint32_t channels_out, uint32_t *width, uint32
     ptb::set_error("bad argument");
     return PT_ERR_INVALID;
   }
-  std::vector<uint8_t> d;
-  int rc = ptb::png_read(path, channels_out, width, height, d);
-  if (rc != PT_OK) return rc;
-  *data_out = (uint8_t *)std::malloc(d.size() ? d.size() : 1);
-  if (!*data_out) return PT_ERR_NOMEM;
-  std::memcpy(*data_out, d.data(), d.size());
-  return PT_OK;
+  return ptb::abi_guard([&]() -> int {
+    std::vector<uint8_t> d;
+    int rc = ptb::png_read(path, channels_out, width, height, d);
+    if (rc != PT_OK) return rc;
+    *data_out = (uint8_t *)std::malloc(d.size() ? d.size() : 1);
+    if (!*data_out) return PT_ERR_NOMEM;
+    std::memcpy(*data_out, d.data(), d.size());
+    return PT_OK;
+  });
 }
 void pt_free(void *p) { std::free(p); }
 }

@@ -76,12 +76,15 @@ struct pt_scene {
   std::mutex mu;
   WaveState wave{};
   std::vector<void *> wave_allocs;
-  uint32_t *cursor = nullptr;  // work cursor of the trace entry points
-  // frame buffers of pt_render_multi, kept between frames (cudaFree synchronises the device: not once per frame)
+  // Recorded at the end of every call that used the wave buffers, waited on at the start of the next one: calls on
+  // one scene from different streams are serialised on the device (the host side is serialised by `mu`).
+  cudaEvent_t busy = nullptr;
+  // frame buffers of pt_render / pt_render_multi and staging buffers of the host-pointer trace entry points, kept
+  // between calls (cudaFree synchronises the device: not once per frame)
   struct FrameBuf {
     void *p = nullptr;
     size_t bytes = 0;
-  } multi_accum, multi_tmp, multi_rgb;
+  } multi_accum, multi_tmp, multi_rgb, trace_in, trace_aux, trace_out;
   std::mutex multi_mu;  // held by pt_render_multi over every replica of the call (taken in address order)
 };
 
@@ -106,6 +109,9 @@ int upload(pt_scene *sc, const std::vector<T> &v, const T **out) {
 }
 
 bool material_may_be_transparent(const pt_material &m) { return !(m.opacity_tex < 0 && m.opacity >= 1.0f); }
+uint32_t material_flags(const pt_material &m) {
+  return (material_may_be_transparent(m) ? TRI_FLAG_ALPHA : 0u) | (m.opacity_tex < 0 && m.opacity == 1.0f ? TRI_FLAG_OPAQUE1 : 0u);
+}
 
 int g_accel = -1;  // -1: not set through the API -> $PT_B200_ACCEL or SAH
 int accel_choice() {
@@ -159,7 +165,7 @@ int build_device_scene(pt_scene *sc) {
     const float *p = &h.pos[(size_t)t * 9];
     int model = h.tri_model[t];
     int prim = h.prim_base[model] + (int)(t - h.models[model].first_tri);
-    uint32_t flags = material_may_be_transparent(h.materials[model]) ? TRI_FLAG_ALPHA : 0u;
+    uint32_t flags = material_flags(h.materials[model]);
     DevTri d;
     d.a = make_float4(p[0], p[1], p[2], 0.f);
     d.b = make_float4(p[3] - p[0], p[4] - p[1], p[5] - p[2], 0.f);  // v0v1, triangle.rs:43
@@ -180,8 +186,7 @@ int build_device_scene(pt_scene *sc) {
   std::vector<DevSphere> spheres;
   for (int m : h.sphere_models) {
     const pt_model &mo = h.models[m];
-    DevSphere s{mo.center[0], mo.center[1], mo.center[2], mo.radius, m, h.prim_base[m],
-                material_may_be_transparent(h.materials[m]) ? TRI_FLAG_ALPHA : 0u, 0u};
+    DevSphere s{mo.center[0], mo.center[1], mo.center[2], mo.radius, m, h.prim_base[m], material_flags(h.materials[m]), 0u};
     spheres.push_back(s);
   }
   std::vector<DevMaterial> mats(h.materials.size());
@@ -236,10 +241,7 @@ int build_device_scene(pt_scene *sc) {
   D.fov = h.fov;
   D.tan_half_fov = std::tan(h.fov / 2.0f);  // f32 tanf of the C library == Rust's f32::tan
   std::memcpy(D.background, h.background, sizeof D.background);
-  void *cur = nullptr;
-  CUDA_TRY(cudaMalloc(&cur, 64));
-  sc->allocs.push_back(cur);
-  sc->cursor = reinterpret_cast<uint32_t *>(cur);
+  CUDA_TRY(cudaEventCreateWithFlags(&sc->busy, cudaEventDisableTiming));
   return PT_OK;
 }
 
@@ -259,7 +261,14 @@ int wave_alloc(pt_scene *sc, T **out, size_t count) {
 }
 
 int ensure_wave(pt_scene *sc, uint32_t n_paths) {
-  uint32_t shadow_cap = n_paths * std::max(1u, sc->dev.n_lights);
+  // queue positions are 32-bit and the shadow queue holds up to n_lights entries per path
+  const uint64_t shadow_cap64 = (uint64_t)n_paths * std::max(1u, sc->dev.n_lights);
+  if (shadow_cap64 > 0xFFFFFF00ull) {
+    set_error("%u paths x %u lights do not fit the 32-bit shadow queue (render a smaller frame or fewer lights)", n_paths,
+              sc->dev.n_lights);
+    return PT_ERR_INVALID;
+  }
+  const uint32_t shadow_cap = (uint32_t)shadow_cap64;
   if (sc->wave.capacity >= n_paths && sc->wave.shadow_capacity >= shadow_cap) return PT_OK;
   free_wave(sc);
   WaveState &W = sc->wave;
@@ -290,6 +299,20 @@ cudaError_t frame_buf(pt_scene::FrameBuf &b, size_t bytes) {
   if (e == cudaSuccess) b.bytes = bytes;
   return e;
 }
+
+// Host-side mutual exclusion on the scene's wave buffers plus device-side ordering between streams: the stream waits
+// for the previous user of the buffers before it touches them, and records itself as that user on the way out.
+struct WaveLock {
+  pt_scene *sc;
+  cudaStream_t st;
+  std::unique_lock<std::mutex> lk;
+  WaveLock(pt_scene *s, cudaStream_t stream) : sc(s), st(stream), lk(s->mu) {
+    if (sc->busy) cudaStreamWaitEvent(st, sc->busy, 0);
+  }
+  ~WaveLock() {
+    if (sc->busy) cudaEventRecord(sc->busy, st);
+  }
+};
 
 int no_device() {
   set_error("scene was created host-only (device -1): no CPU fallback exists for tracing or rendering");
@@ -391,9 +414,11 @@ int pt_scene_create(const pt_scene_desc *desc, int device, pt_scene **out) {
     set_error("null model/material arrays");
     return PT_ERR_INVALID;
   }
-  HostScene h;
-  h.from_desc(*desc);
-  return scene_from_host(std::move(h), device, out);
+  return abi_guard([&]() -> int {
+    HostScene h;
+    h.from_desc(*desc);
+    return scene_from_host(std::move(h), device, out);
+  });
 }
 
 void pt_scene_destroy(pt_scene *sc) {
@@ -404,7 +429,9 @@ void pt_scene_destroy(pt_scene *sc) {
   }
   DeviceGuard g(sc->device);
   free_wave(sc);
-  for (pt_scene::FrameBuf *b : {&sc->multi_accum, &sc->multi_tmp, &sc->multi_rgb}) cudaFree(b->p);
+  for (pt_scene::FrameBuf *b : {&sc->multi_accum, &sc->multi_tmp, &sc->multi_rgb, &sc->trace_in, &sc->trace_aux, &sc->trace_out})
+    cudaFree(b->p);
+  if (sc->busy) cudaEventDestroy(sc->busy);
   for (void *p : sc->allocs) cudaFree(p);
   for (auto &s : sc->staged) cudaFreeHost(s.host);
   for (cudaEvent_t e : sc->events) cudaEventDestroy(e);
@@ -479,67 +506,124 @@ int pt_scene_info(const pt_scene *sc, uint64_t *n_tris, uint64_t *n_prims, uint6
   return PT_OK;
 }
 
-int pt_trace_closest_device(const pt_scene *sc, const float *rays_dev, size_t n, pt_hit *out_dev, void *stream) {
-  if (!sc || (n && (!rays_dev || !out_dev)) || n > 0xFFFFFF00ull) {
-    set_error("bad argument");
-    return PT_ERR_INVALID;
+// ---- fixed ray batches through the production kernels ----
+// Rays per pass through the wave queues: bounds the wave memory a batch needs (~200 B per ray) whatever n is.
+static constexpr size_t TRACE_CHUNK = 16u << 20;
+
+// rays_dev / out_dev: device pointers on the scene's device.  alpha = false: ray_cast(...).first(); alpha = true: the
+// hit the alpha walk accepts with the draws of path (pixel = ray index, sample, seed) at `bounce`.
+static int trace_closest_dev(pt_scene *sc, const float *rays_dev, size_t n, size_t index_base, pt_hit *out_dev, bool alpha,
+                             uint32_t bounce, uint32_t sample, uint64_t seed, cudaStream_t st) {
+  WaveLock lock(sc, st);
+  int rc = ensure_wave(sc, (uint32_t)std::min(n, TRACE_CHUNK));
+  if (rc) return rc;
+  const WaveState &W = sc->wave;
+  for (size_t b = 0; b < n; b += TRACE_CHUNK) {
+    const uint32_t c = (uint32_t)std::min(TRACE_CHUNK, n - b);
+    WaveParams P{};
+    P.width = 0x80000000u;  // make_key: pixel = slot, sample = sample_first
+    P.height = 1;
+    P.bounces = bounce;
+    P.spp_in_wave = 1;
+    P.sample_first = sample;
+    P.sample_stride = 1;
+    P.seed_lo = (uint32_t)seed;
+    P.seed_hi = (uint32_t)(seed >> 32);
+    P.n_paths = c;
+    launch_load_rays(rays_dev + b * 6, c, (uint32_t)(index_base + b), W, bounce & 1u, st);
+    launch_extend(sc->dev, P, W, bounce, alpha, out_dev + b, st);
   }
-  if (n == 0) return PT_OK;
-  if (sc->device < 0) return no_device();
-  DeviceGuard g(sc->device);
-  launch_trace_closest(sc->dev, rays_dev, (uint32_t)n, out_dev, sc->cursor, (cudaStream_t)stream);
   CUDA_TRY(cudaGetLastError());
   return PT_OK;
 }
 
-int pt_trace_closest(const pt_scene *sc, const float *rays, size_t n, pt_hit *out) {
-  if (!sc || (n && (!rays || !out))) {
+int pt_trace_closest_device(const pt_scene *sc, const float *rays_dev, size_t n, pt_hit *out_dev, void *stream) {
+  if (!sc || (n && (!rays_dev || !out_dev))) {
     set_error("bad argument");
     return PT_ERR_INVALID;
   }
   if (n == 0) return PT_OK;
   if (sc->device < 0) return no_device();
   DeviceGuard g(sc->device);
-  float *d_rays = nullptr;
-  pt_hit *d_out = nullptr;
-  CUDA_TRY(cudaMalloc(&d_rays, n * 6 * sizeof(float)));
-  if (cudaMalloc(&d_out, n * sizeof(pt_hit)) != cudaSuccess) {
-    cudaFree(d_rays);
-    set_error("out of device memory");
-    return PT_ERR_NOMEM;
+  return trace_closest_dev(const_cast<pt_scene *>(sc), rays_dev, n, 0, out_dev, false, 0, 0, 0, (cudaStream_t)stream);
+}
+
+// Host-pointer batches: staged chunk by chunk through buffers cached on the scene.
+static int trace_closest_host(const pt_scene *csc, const float *rays, size_t n, pt_hit *out, bool alpha, uint32_t bounce,
+                              uint32_t sample, uint64_t seed) {
+  pt_scene *sc = const_cast<pt_scene *>(csc);
+  if (!sc || (n && (!rays || !out)) || (alpha && n > 0x7FFFFFFFull)) {
+    set_error("bad argument");
+    return PT_ERR_INVALID;
   }
-  cudaMemcpy(d_rays, rays, n * 6 * sizeof(float), cudaMemcpyHostToDevice);
-  int rc = pt_trace_closest_device(sc, d_rays, n, d_out, nullptr);
-  cudaError_t e = cudaMemcpy(out, d_out, n * sizeof(pt_hit), cudaMemcpyDeviceToHost);
-  cudaFree(d_rays);
-  cudaFree(d_out);
-  if (rc != PT_OK) return rc;
-  CUDA_TRY(e);
+  if (n == 0) return PT_OK;
+  if (sc->device < 0) return no_device();
+  DeviceGuard g(sc->device);
+  std::lock_guard<std::mutex> hold(sc->multi_mu);  // the staging buffers
+  const size_t cap = std::min(n, TRACE_CHUNK);
+  CUDA_TRY(frame_buf(sc->trace_in, cap * 6 * sizeof(float)));
+  CUDA_TRY(frame_buf(sc->trace_out, cap * sizeof(pt_hit)));
+  float *d_rays = static_cast<float *>(sc->trace_in.p);
+  pt_hit *d_out = static_cast<pt_hit *>(sc->trace_out.p);
+  for (size_t b = 0; b < n; b += TRACE_CHUNK) {
+    const size_t c = std::min(TRACE_CHUNK, n - b);
+    CUDA_TRY(cudaMemcpy(d_rays, rays + b * 6, c * 6 * sizeof(float), cudaMemcpyHostToDevice));
+    int rc = trace_closest_dev(sc, d_rays, c, b, d_out, alpha, bounce, sample, seed, nullptr);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpy(out + b, d_out, c * sizeof(pt_hit), cudaMemcpyDeviceToHost));
+  }
+  return PT_OK;
+}
+
+int pt_trace_closest(const pt_scene *sc, const float *rays, size_t n, pt_hit *out) {
+  return trace_closest_host(sc, rays, n, out, false, 0, 0, 0);
+}
+
+int pt_trace_accepted(const pt_scene *sc, const float *rays, size_t n, uint32_t bounce, uint32_t sample, uint64_t seed,
+                      pt_hit *out) {
+  return trace_closest_host(sc, rays, n, out, true, bounce, sample, seed);
+}
+
+int pt_trace_shadow(const pt_scene *csc, const float *rays, const float *limits, const float *primary, size_t n,
+                    float *out) {
+  pt_scene *sc = const_cast<pt_scene *>(csc);
+  if (!sc || (n && (!rays || !out)) || ((limits == nullptr) != (primary == nullptr))) {
+    set_error("bad argument");
+    return PT_ERR_INVALID;
+  }
+  if (n == 0) return PT_OK;
+  if (sc->device < 0) return no_device();
+  DeviceGuard g(sc->device);
+  std::lock_guard<std::mutex> hold(sc->multi_mu);
+  const size_t cap = std::min(n, TRACE_CHUNK);
+  CUDA_TRY(frame_buf(sc->trace_in, cap * 6 * sizeof(float)));
+  CUDA_TRY(frame_buf(sc->trace_out, cap * sizeof(float)));
+  if (limits) CUDA_TRY(frame_buf(sc->trace_aux, cap * 6 * sizeof(float)));
+  float *d_rays = static_cast<float *>(sc->trace_in.p), *d_out = static_cast<float *>(sc->trace_out.p);
+  float *d_lim = limits ? static_cast<float *>(sc->trace_aux.p) : nullptr, *d_prim = limits ? d_lim + cap : nullptr;
+  for (size_t b = 0; b < n; b += TRACE_CHUNK) {
+    const uint32_t c = (uint32_t)std::min(TRACE_CHUNK, n - b);
+    CUDA_TRY(cudaMemcpy(d_rays, rays + b * 6, (size_t)c * 6 * sizeof(float), cudaMemcpyHostToDevice));
+    if (limits) {
+      CUDA_TRY(cudaMemcpy(d_lim, limits + b, (size_t)c * sizeof(float), cudaMemcpyHostToDevice));
+      CUDA_TRY(cudaMemcpy(d_prim, primary + b * 5, (size_t)c * 5 * sizeof(float), cudaMemcpyHostToDevice));
+    }
+    {
+      WaveLock lock(sc, nullptr);
+      int rc = ensure_wave(sc, c);
+      if (rc) return rc;
+      launch_load_shadow(d_rays, d_lim, d_prim, c, sc->wave, 1u, nullptr);
+      launch_shadow(sc->dev, sc->wave, 0u, nullptr);  // bounce 0 reads the shadow queue filled "with buffer 1"
+      launch_store_transmittance(sc->wave, c, d_out, nullptr);
+      CUDA_TRY(cudaGetLastError());
+    }
+    CUDA_TRY(cudaMemcpy(out + b, d_out, (size_t)c * sizeof(float), cudaMemcpyDeviceToHost));
+  }
   return PT_OK;
 }
 
 int pt_trace_transmittance(const pt_scene *sc, const float *rays, size_t n, float *out) {
-  if (!sc || (n && (!rays || !out)) || n > 0xFFFFFF00ull) {
-    set_error("bad argument");
-    return PT_ERR_INVALID;
-  }
-  if (n == 0) return PT_OK;
-  if (sc->device < 0) return no_device();
-  DeviceGuard g(sc->device);
-  float *d_rays = nullptr, *d_out = nullptr;
-  CUDA_TRY(cudaMalloc(&d_rays, n * 6 * sizeof(float)));
-  if (cudaMalloc(&d_out, n * sizeof(float)) != cudaSuccess) {
-    cudaFree(d_rays);
-    set_error("out of device memory");
-    return PT_ERR_NOMEM;
-  }
-  cudaMemcpy(d_rays, rays, n * 6 * sizeof(float), cudaMemcpyHostToDevice);
-  launch_trace_transmittance(sc->dev, d_rays, (uint32_t)n, d_out, sc->cursor, nullptr);
-  cudaError_t e = cudaMemcpy(out, d_out, n * sizeof(float), cudaMemcpyDeviceToHost);
-  cudaFree(d_rays);
-  cudaFree(d_out);
-  CUDA_TRY(e);
-  return PT_OK;
+  return pt_trace_shadow(sc, rays, nullptr, nullptr, n, out);
 }
 
 int pt_triangle_intersect(const pt_scene *sc, int device, const float *rays, const float *tris, size_t n, pt_hit *out) {
@@ -569,6 +653,35 @@ int pt_triangle_intersect(const pt_scene *sc, int device, const float *rays, con
   cudaFree(d_rays);
   cudaFree(d_tris);
   cudaFree(d_out);
+  CUDA_TRY(e);
+  return PT_OK;
+}
+
+int pt_philox4x32_10(int device, const uint32_t *counters, const uint32_t *keys, size_t n, uint32_t *out) {
+  if ((n && (!counters || !keys || !out)) || n > (1u << 24)) {
+    set_error("bad argument");
+    return PT_ERR_INVALID;
+  }
+  if (n == 0) return PT_OK;
+  if (device < 0 || device >= pt_device_count()) {
+    set_error("no CUDA device %d (this library has no CPU fallback)", device);
+    return PT_ERR_CUDA;
+  }
+  DeviceGuard g(device);
+  uint32_t *d_c = nullptr, *d_k = nullptr, *d_o = nullptr;
+  cudaError_t e = cudaMalloc(&d_c, n * 16);
+  if (e == cudaSuccess) e = cudaMalloc(&d_k, n * 8);
+  if (e == cudaSuccess) e = cudaMalloc(&d_o, n * 16);
+  if (e == cudaSuccess) e = cudaMemcpy(d_c, counters, n * 16, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(d_k, keys, n * 8, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    launch_philox(d_c, d_k, (uint32_t)n, d_o, nullptr);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(out, d_o, n * 16, cudaMemcpyDeviceToHost);
+  cudaFree(d_c);
+  cudaFree(d_k);
+  cudaFree(d_o);
   CUDA_TRY(e);
   return PT_OK;
 }
@@ -633,8 +746,8 @@ int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t
   if (sample_stride == 0) sample_stride = 1;
   if (sc->device < 0) return no_device();
   DeviceGuard g(sc->device);
-  std::lock_guard<std::mutex> lock(sc->mu);
   cudaStream_t st = (cudaStream_t)stream;
+  WaveLock lock(sc, st);
   const uint64_t npix = (uint64_t)prof->width * prof->height;
   // wave size: as many samples per pixel as fit ~256 Mi paths.  Large waves keep the late-bounce queues (a few % of the
   // paths) big enough to fill 148 SMs and amortise every launch's tail: on the console workload 8 Mi -> 64 Mi paths is
@@ -697,7 +810,7 @@ int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t
     mark(3);
     ++launches;
     for (uint32_t b = 0; b <= prof->bounces; ++b) {
-      launch_extend(sc->dev, P, W, b, st);
+      launch_extend(sc->dev, P, W, b, sc->dev.any_alpha != 0, nullptr, st);
       mark(0);
       launch_shade(sc->dev, P, W, b, st);
       mark(1);
@@ -729,7 +842,9 @@ int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t
     stats_out->samples = npix * n_samples;
     stats_out->extend_rays = u64(CTR_STAT_EXTEND);
     stats_out->shadow_rays = u64(CTR_STAT_SHADOW);
-    stats_out->alpha_recasts = u64(CTR_STAT_RECAST);
+    stats_out->alpha_recasts = 0;  // the alpha walk is single-pass (traverse.cuh): nothing is re-cast
+    stats_out->alpha_tests = u64(CTR_STAT_ALPHA);
+    stats_out->shadow_dropped = ctr[CTR_DROPPED];
     stats_out->kernel_launches = launches;
     stats_out->extend_launches = n_ext;
     stats_out->shade_launches = n_shade;
@@ -762,8 +877,9 @@ int pt_tonemap_device(const float *accum_dev, uint32_t width, uint32_t height, u
   return PT_OK;
 }
 
-int pt_render(const pt_scene *sc, const pt_profile *prof, uint64_t seed, uint8_t *rgb8_out, float *accum_out,
+int pt_render(const pt_scene *csc, const pt_profile *prof, uint64_t seed, uint8_t *rgb8_out, float *accum_out,
               pt_stats *stats_out) {
+  pt_scene *sc = const_cast<pt_scene *>(csc);
   if (!sc || !rgb8_out) {
     set_error("null argument");
     return PT_ERR_INVALID;
@@ -773,27 +889,22 @@ int pt_render(const pt_scene *sc, const pt_profile *prof, uint64_t seed, uint8_t
   if (sc->device < 0) return no_device();
   DeviceGuard g(sc->device);
   const size_t npix = (size_t)prof->width * prof->height;
-  float *d_accum = nullptr;
-  uint8_t *d_rgb = nullptr;
-  CUDA_TRY(cudaMalloc(&d_accum, npix * 3 * sizeof(float)));
-  if (cudaMalloc(&d_rgb, npix * 3) != cudaSuccess) {
-    cudaFree(d_accum);
+  // the frame buffers are cached on the scene (cudaMalloc / cudaFree once per frame cost ~1 ms and a device sync)
+  std::lock_guard<std::mutex> hold(sc->multi_mu);
+  if (frame_buf(sc->multi_accum, npix * 3 * sizeof(float)) != cudaSuccess || frame_buf(sc->multi_rgb, npix * 3) != cudaSuccess) {
+    cudaGetLastError();
     set_error("out of device memory");
     return PT_ERR_NOMEM;
   }
-  cudaMemset(d_accum, 0, npix * 3 * sizeof(float));
+  float *d_accum = static_cast<float *>(sc->multi_accum.p);
+  uint8_t *d_rgb = static_cast<uint8_t *>(sc->multi_rgb.p);
+  CUDA_TRY(cudaMemsetAsync(d_accum, 0, npix * 3 * sizeof(float), nullptr));
   pt_stats local;
   rc = pt_render_accum_device(sc, prof, 0, 1, prof->samples, seed, d_accum, nullptr, stats_out ? stats_out : &local);
   if (rc == PT_OK) rc = pt_tonemap_device(d_accum, prof->width, prof->height, prof->samples, prof->tonemap, d_rgb, sc->device, nullptr);
-  cudaError_t e = cudaSuccess;
-  if (rc == PT_OK) {
-    e = cudaMemcpy(rgb8_out, d_rgb, npix * 3, cudaMemcpyDeviceToHost);
-    if (e == cudaSuccess && accum_out) e = cudaMemcpy(accum_out, d_accum, npix * 3 * sizeof(float), cudaMemcpyDeviceToHost);
-  }
-  cudaFree(d_accum);
-  cudaFree(d_rgb);
   if (rc != PT_OK) return rc;
-  CUDA_TRY(e);
+  CUDA_TRY(cudaMemcpy(rgb8_out, d_rgb, npix * 3, cudaMemcpyDeviceToHost));
+  if (accum_out) CUDA_TRY(cudaMemcpy(accum_out, d_accum, npix * 3 * sizeof(float), cudaMemcpyDeviceToHost));
   return PT_OK;
 }
 
@@ -1008,6 +1119,8 @@ int pt_render_progressive(const pt_scene *sc, const pt_profile *prof, uint64_t s
     total.extend_rays += part.extend_rays;
     total.shadow_rays += part.shadow_rays;
     total.alpha_recasts += part.alpha_recasts;
+    total.alpha_tests += part.alpha_tests;
+    total.shadow_dropped += part.shadow_dropped;
     total.kernel_launches += part.kernel_launches + 1;
     total.extend_launches += part.extend_launches;
     total.shade_launches += part.shade_launches;

@@ -19,8 +19,13 @@ namespace ptb {
 // ---------------- Philox4x32-10 (counter-based; replaces rand's ChaCha12 StdRng) ----------------
 // key = (pixel, sample), counter = (block, tag, seed_lo, seed_hi).  Draw names:
 //   tag 0 block 0: [jitter x, jitter y, -, -]
-//   tag b+1 block 0: [r1, r2, russian roulette, alpha draw 0] of bounce b
-//   tag b+1 block 1+(j-1)/4, lane (j-1)%4: alpha draw j >= 1
+//   tag b+1 block 0: [r1, r2, russian roulette, -] of bounce b
+//   tag 0x80000000 | (b+1), block = global prim id: [alpha draw of that examined hit at bounce b, -, -, -]
+// The alpha walk (mod.rs:188-205) gives every examined hit with 0.001 < opacity < 1 its own uniform draw; the
+// reference takes it from the path's sequential stream, here it is addressed by the hit's primitive id, so the
+// accept / reject decision of a hit does not depend on the order in which hits are found and the walk needs ONE
+// traversal (traverse.cuh).  Same distribution of the accepted hit; the CPU oracle addresses its Philox draws the
+// same way (oracle/rng.hpp).
 __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1) {
 #pragma unroll
   for (int r = 0; r < 10; ++r) {
@@ -40,11 +45,8 @@ struct RngKey {
 __device__ __forceinline__ uint4 rng_block(const RngKey &k, uint32_t tag, uint32_t block) {
   return philox4x32_10(make_uint4(block, tag, k.seed_lo, k.seed_hi), k.pixel, k.sample);
 }
-__device__ __forceinline__ float rng_alpha(const RngKey &k, uint32_t bounce, uint32_t j) {
-  if (j == 0) return u32_to_unit(rng_block(k, bounce + 1, 0).w);
-  uint4 b = rng_block(k, bounce + 1, 1 + (j - 1) / 4);
-  uint32_t l = (j - 1) & 3u;
-  return u32_to_unit(l == 0 ? b.x : l == 1 ? b.y : l == 2 ? b.z : b.w);
+__device__ __forceinline__ float rng_alpha(const RngKey &k, uint32_t bounce, uint32_t prim_id) {
+  return u32_to_unit(rng_block(k, 0x80000000u | (bounce + 1u), prim_id).x);
 }
 
 // ---------------- textures / materials ----------------

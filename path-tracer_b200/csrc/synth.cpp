@@ -338,13 +338,19 @@ int make_synthetic(const char *recipe, uint64_t n_tris, uint64_t seed, HostScene
 
 }  // namespace ptb
 
+// The oracle links this file for the generators alone (oracle/Makefile: "same generator code compiled into the
+// oracle"), without the device-side scene constructor.
+#ifndef PTB_SYNTH_GENERATOR_ONLY
 extern "C" int pt_scene_synthetic(const char *recipe, uint64_t n_tris, uint64_t seed, int device, pt_scene **out) {
   if (!out) {
     ptb::set_error("null argument");
     return PT_ERR_INVALID;
   }
-  ptb::HostScene h;
-  int rc = ptb::make_synthetic(recipe, n_tris, seed, h);
-  if (rc != PT_OK) return rc;
-  return ptb::scene_from_host(std::move(h), device, out);
+  return ptb::abi_guard([&]() -> int {
+    ptb::HostScene h;
+    int rc = ptb::make_synthetic(recipe, n_tris, seed, h);
+    if (rc != PT_OK) return rc;
+    return ptb::scene_from_host(std::move(h), device, out);
+  });
 }
+#endif

@@ -1,101 +1,84 @@
-// traverse.cuh — resumable (one step at a time) BVH4 traversals for the persistent kernels.
-// A lane owns one ray; `step()` visits one node or one leaf and returns true when the query is complete, so a warp
-// can replace finished rays lane by lane instead of waiting for its longest ray (Aila & Laine 2009, "terminated ray
-// replacement").  Same arithmetic as trace_closest / trace_transmittance (isect.cuh, path.cuh): results are identical.
-//   ClosestTrav  renderer/utils.rs:11-21 (smallest (dist, prim id) key above (t_lo, id_lo))
+// traverse.cuh — the BVH4 traversals: ONE implementation of each query, used by every kernel.
+//   ClosestTrav  renderer/utils.rs:11-21 (first element of the sorted all-hits list) and, with `alpha`, the hit that
+//                the alpha walk of render_pixel accepts (renderer/mod.rs:188-205)
 //   ShadowTrav   renderer/mod.rs:281-333 (product of (1 - opacity) over every hit, early out at 0)
+// Both are resumable: a lane owns one ray and `node_step` / `leaf_step` visit one node / test one primitive, so a
+// warp of a persistent kernel can replace finished rays lane by lane instead of waiting for its longest ray (Aila &
+// Laine 2009, "terminated ray replacement").  trace_closest / trace_transmittance at the end of the file run the same
+// structs to completion for the one-thread-per-path kernels (k_trace_paths, k_debug_aov): there is no second traversal.
 #pragma once
 #include "path.cuh"
 
-#ifndef PTB_STK64
-#define PTB_STK64 1  // measured: k_extend -3 % (console, city, foliage)
-#endif
-
 namespace ptb {
 
-// The lane's closest-hit traversal stack (local memory): (entry distance, child reference) pairs, kept outside the
-// traversal struct so that the scalar state stays in registers.  PTB_STK64 packs a pair into one 64-bit word
-// (one STL.64 / LDL.64 per push / pop instead of two 32-bit accesses).
+// The lane's closest-hit traversal stack (local memory): packed (entry distance, child reference) words, one
+// STL.64 / LDL.64 per push / pop (measured -3 % against two 32-bit arrays), kept outside the traversal struct so
+// that the scalar state stays in registers.  Three more words hold the farthest REJECTED hit of the alpha walk
+// ((t, prim id) (u, v) (idx, -)): it is the hit that is shaded when no hit is accepted (mod.rs:188-205 leaves `hit`
+// at the last examined element), touched only when a transparent hit is rejected.
 struct ClosestStack {
-#if PTB_STK64
-  uint2 e[PTB_STACK];
+  uint2 e[PTB_STACK + 3];
   __device__ __forceinline__ void put(int i, float t, uint32_t r) { e[i] = make_uint2(__float_as_uint(t), r); }
   __device__ __forceinline__ void get(int i, float &t, uint32_t &r) const {
     const uint2 v = e[i];
     t = __uint_as_float(v.x);
     r = v.y;
   }
-#else
-  float t_[PTB_STACK];
-  uint32_t r_[PTB_STACK];
-  __device__ __forceinline__ void put(int i, float t, uint32_t r) { t_[i] = t; r_[i] = r; }
-  __device__ __forceinline__ void get(int i, float &t, uint32_t &r) const { t = t_[i]; r = r_[i]; }
-#endif
 };
+constexpr int FAR_SLOT = PTB_STACK;
 
-#ifndef PTB_MERGED_POP
-#define PTB_MERGED_POP 0
-#endif
+// One examined hit of the alpha walk (mod.rs:196-204): accepted when opacity >= 1, or when opacity > 0.001 and the
+// hit's own draw is below it.  Out of line: it is reached by a few lanes at a time and holds a texture fetch and ten
+// Philox rounds that the traversal loop should neither carry in its registers nor in its instruction footprint.
+__device__ __noinline__ bool alpha_accepts(const DevScene &S, uint32_t pixel, uint32_t sample, uint32_t seed_lo,
+                                           uint32_t seed_hi, uint32_t bounce, int idx, int prim_id, float u, float v) {
+  const float op = hit_opacity(S, idx, u, v);
+  if (op >= 1.0f) return true;
+  if (!(op > 0.001f)) return false;
+  RngKey k;
+  k.pixel = pixel;
+  k.sample = sample;
+  k.seed_lo = seed_lo;
+  k.seed_hi = seed_hi;
+  return rng_alpha(k, bounce, (uint32_t)prim_id) < op;
+}
 
 struct ClosestTrav {
   Ray r;
   RayPre pre;
-  TraceState st;
-  float t_prune, t_lo;
-  int id_lo;
+  TraceState st;   // nearest accepted hit so far
+  float t_prune;   // slab-parameter bound derived from it
   uint32_t cur;
   int sp;
 
-  __device__ __forceinline__ void begin(const Ray &ray, float tlo, int idlo) {
+  static constexpr uint32_t DONE = 0xFFFFFFFFu;
+
+  __device__ __forceinline__ void begin(const Ray &ray, ClosestStack &stk, bool alpha) {
     r = ray;
     pre = precompute(ray);
     st.best_t = CUDART_INF_F;
     st.best_id = 0x7FFFFFFF;
     st.idx = -1;
     st.u = st.v = 0.f;
-    st.flags = 0;
-    t_prune = CUDART_INF_F;
-    t_lo = tlo;
-    id_lo = idlo;
-    cur = 0;
-    sp = 0;
-  }
-  // restart behind the current best hit (alpha walk), keeping the ray
-  __device__ __forceinline__ void restart_behind() {
-    t_lo = st.best_t;
-    id_lo = st.best_id;
-    st.best_t = CUDART_INF_F;
-    st.best_id = 0x7FFFFFFF;
-    st.idx = -1;
-    st.u = st.v = 0.f;
-    st.flags = 0;
     t_prune = CUDART_INF_F;
     cur = 0;
     sp = 0;
+    if (alpha) stk.put(FAR_SLOT, -1.0f, 0xFFFFFFFFu);  // no rejected hit yet
   }
-  static constexpr uint32_t DONE = 0xFFFFFFFFu;
-  // PTB_MERGED_POP: node_step / leaf_step leave NEED_POP instead of popping, and the kernel pops once per iteration
-  // for every lane that needs it: the pop loop (entries behind the current best hit are skipped lazily) then runs with
-  // the lanes of both paths together instead of once per call site with 2-5 lanes each.
-  static constexpr uint32_t NEED_POP = 0xFFFFFFFEu;
   __device__ __forceinline__ bool at_inner() const { return !(cur & 0x80000000u); }
-  __device__ __forceinline__ bool at_leaf() const { return (cur & 0x80000000u) && cur < NEED_POP; }
-  __device__ __forceinline__ void after(const ClosestStack &stk) {
-#if PTB_MERGED_POP
-    (void)stk;
-    cur = NEED_POP;
-#else
-    pop(stk);
-#endif
-  }
+  __device__ __forceinline__ bool at_leaf() const { return (cur & 0x80000000u) && cur != DONE; }
 
+  // next stack entry that can still hold a nearer hit (entries behind the current best hit are skipped lazily)
   __device__ __forceinline__ void pop(const ClosestStack &stk) {
     while (sp > 0) {
       --sp;
       float t;
       uint32_t ref;
       stk.get(sp, t, ref);
-      if (t <= t_prune) { cur = ref; return; }
+      if (t <= t_prune) {
+        cur = ref;
+        return;
+      }
     }
     cur = DONE;
   }
@@ -114,25 +97,91 @@ struct ClosestTrav {
     if (t2 < CUDART_INF_F) stk.put(sp++, t2, r2);
     if (t1 < CUDART_INF_F) stk.put(sp++, t1, r1);
     if (t0 < CUDART_INF_F) cur = r0;
-    else after(stk);
+    else pop(stk);
   }
-  // Tests ONE primitive of leaf `ref` (uniform cost per step).  Returns true when the leaf has more primitives, with
-  // `ref` advanced to the rest (first+1, count-1 == ref + 7).
-  __device__ __forceinline__ bool leaf_step_ref(const DevScene &S, uint32_t &ref) {
-    if (ref & 0x40000000u) {
-      leaf_closest(S, ref, r, t_lo, id_lo, st, t_prune, pre);
-      return false;
+
+  // One candidate hit with key (t, id).  Without `alpha` the smallest key wins (ray_cast's first element).  With it,
+  // a hit of a possibly transparent primitive is examined at once — its decision depends only on the hit itself
+  // (shade.cuh, "Draw names") — and a rejected one only competes for "farthest rejected hit".
+  template <typename KeyFn>
+  __device__ __forceinline__ void consider(const DevScene &S, ClosestStack &stk, float t, int id, float u, float v,
+                                           int idx, uint32_t flags, bool alpha, uint32_t bounce, KeyFn key_of,
+                                           uint32_t &n_alpha) {
+    if (!key_less(t, id, st.best_t, st.best_id)) return;
+    if (alpha && (flags & TRI_FLAG_ALPHA)) {
+      ++n_alpha;
+      const RngKey k = key_of();
+      if (!alpha_accepts(S, k.pixel, k.sample, k.seed_lo, k.seed_hi, bounce, idx, id, u, v)) {
+        float ft;
+        uint32_t fid;
+        stk.get(FAR_SLOT, ft, fid);
+        if (key_less(ft, (int)fid, t, id)) {
+          stk.put(FAR_SLOT, t, (uint32_t)id);
+          stk.put(FAR_SLOT + 1, u, __float_as_uint(v));
+          stk.put(FAR_SLOT + 2, __int_as_float(idx), 0u);
+        }
+        return;
+      }
     }
-    leaf_closest(S, ref & ~7u, r, t_lo, id_lo, st, t_prune, pre);  // count-1 = 0: the first primitive only
-    if (!(ref & 7u)) return false;
-    ref += 7u;
-    return true;
+    st.best_t = t;
+    st.best_id = id;
+    st.u = u;
+    st.v = v;
+    st.idx = idx;
+    t_prune = t * pre.prune_scale;
   }
-  // Precondition: at_leaf().  A triangle leaf with more primitives left stays current.
-  __device__ __forceinline__ void leaf_step(const DevScene &S, const ClosestStack &stk) {
-    if (!leaf_step_ref(S, cur)) after(stk);
+
+  // Precondition: at_leaf().  Tests ONE primitive of the current leaf (uniform cost per step); a triangle leaf with
+  // more primitives left stays current (first+1, count-1 == ref + 7).
+  template <typename KeyFn>
+  __device__ __forceinline__ void leaf_step(const DevScene &S, ClosestStack &stk, bool alpha, uint32_t bounce,
+                                            KeyFn key_of, uint32_t &n_alpha) {
+    if (cur & 0x40000000u) {
+      const uint32_t si = cur & 0x3FFFFFFFu;
+      const DevSphere sph = S.spheres[si];
+      float dist[2], tp[2];
+      int exit_only = 0;
+      const int n = sphere_hits(r, sph, dist, tp, exit_only);
+      for (int k = 0; k < n; ++k) {
+        const int is_exit = (n == 1) ? exit_only : k;
+        consider(S, stk, dist[k], sph.prim_id + is_exit, 0.f, 0.f, (int)(S.n_tris + 2u * si + (uint32_t)is_exit), sph.flags,
+                 alpha, bounce, key_of, n_alpha);
+      }
+      pop(stk);
+      return;
+    }
+    const float4 *tp = reinterpret_cast<const float4 *>(S.tris + ((cur & 0x3FFFFFFFu) >> 3));
+    const float4 A = __ldg(tp), B = __ldg(tp + 1), C = __ldg(tp + 2);
+    float t, u, v, det;
+    if (moller_trumbore(r, mk3(A.x, A.y, A.z), mk3(B.x, B.y, B.z), mk3(C.x, C.y, C.z), t, u, v, det))
+      consider(S, stk, t, __float_as_int(A.w), u, v, __float_as_int(B.w) | (det < 0.0f ? HIT_BACKFACE : 0),
+               __float_as_uint(C.w), alpha, bounce, key_of, n_alpha);
+    if (cur & 7u) cur += 7u;
+    else pop(stk);
+  }
+
+  // After DONE: when nothing was accepted, the farthest rejected hit is the one the reference shades.
+  __device__ __forceinline__ void finish(const ClosestStack &stk, bool alpha) {
+    if (!alpha || st.idx >= 0) return;
+    float ft, fu;
+    uint32_t fid, fv, fi, unused;
+    stk.get(FAR_SLOT, ft, fid);
+    if (!(ft >= 0.0f)) return;
+    stk.get(FAR_SLOT + 1, fu, fv);
+    float fidx;
+    stk.get(FAR_SLOT + 2, fidx, unused);
+    fi = __float_as_uint(fidx);
+    st.best_t = ft;
+    st.best_id = (int)fid;
+    st.u = fu;
+    st.v = __uint_as_float(fv);
+    st.idx = (int)fi;
   }
 };
+
+#ifndef PTB_SHADOW_ORDERED
+#define PTB_SHADOW_ORDERED 0  // 1: k_shadow visits the children of a node nearest-first (A/B knob)
+#endif
 
 struct ShadowTrav {
   Ray r;
@@ -142,7 +191,9 @@ struct ShadowTrav {
   uint32_t cur;
   int sp;
 
-  // limit < 0: directional; else point light at distance `limit` from the primary hit `p` (see trace_transmittance)
+  // limit < 0: directional light (every hit on the ray, occluder sampled at its own uv, mod.rs:291-297)
+  // limit >= 0: point light at distance `limit` from the primary hit `p`; occluders farther than the light are
+  // ignored and the occluder's material is sampled with the PRIMARY hit's uv/variant (mod.rs:319-329, u NaN = sphere)
   __device__ __forceinline__ void begin(const Ray &ray, float lim, V3 p, float u, float v) {
     r = ray;
     pre = precompute(ray);
@@ -178,10 +229,24 @@ struct ShadowTrav {
   __device__ __forceinline__ void node_step(const DevScene &S, const NodeOrder &no, uint32_t *stk) {
     const NodeData nd = load_node(S.nodes, cur);
     const uint4 ch = nd.ch;
+#if PTB_SHADOW_ORDERED
+    float t0 = slab_fma(nd.lo_x.x, nd.lo_y.x, nd.lo_z.x, nd.hi_x.x, nd.hi_y.x, nd.hi_z.x, pre, no, t_max, ch.x);
+    float t1 = slab_fma(nd.lo_x.y, nd.lo_y.y, nd.lo_z.y, nd.hi_x.y, nd.hi_y.y, nd.hi_z.y, pre, no, t_max, ch.y);
+    float t2 = slab_fma(nd.lo_x.z, nd.lo_y.z, nd.lo_z.z, nd.hi_x.z, nd.hi_y.z, nd.hi_z.z, pre, no, t_max, ch.z);
+    float t3 = slab_fma(nd.lo_x.w, nd.lo_y.w, nd.lo_z.w, nd.hi_x.w, nd.hi_y.w, nd.hi_z.w, pre, no, t_max, ch.w);
+    uint32_t r0 = ch.x, r1 = ch.y, r2 = ch.z, r3 = ch.w;
+    PTB_CSWAP(t0, r0, t1, r1) PTB_CSWAP(t2, r2, t3, r3) PTB_CSWAP(t0, r0, t2, r2) PTB_CSWAP(t1, r1, t3, r3)
+    PTB_CSWAP(t1, r1, t2, r2)
+    if (t3 < CUDART_INF_F) stk[sp++] = r3;
+    if (t2 < CUDART_INF_F) stk[sp++] = r2;
+    if (t1 < CUDART_INF_F) stk[sp++] = r1;
+    if (t0 < CUDART_INF_F) stk[sp++] = r0;
+#else
     if (slab_fma(nd.lo_x.x, nd.lo_y.x, nd.lo_z.x, nd.hi_x.x, nd.hi_y.x, nd.hi_z.x, pre, no, t_max, ch.x) < CUDART_INF_F) stk[sp++] = ch.x;
     if (slab_fma(nd.lo_x.y, nd.lo_y.y, nd.lo_z.y, nd.hi_x.y, nd.hi_y.y, nd.hi_z.y, pre, no, t_max, ch.y) < CUDART_INF_F) stk[sp++] = ch.y;
     if (slab_fma(nd.lo_x.z, nd.lo_y.z, nd.lo_z.z, nd.hi_x.z, nd.hi_y.z, nd.hi_z.z, pre, no, t_max, ch.z) < CUDART_INF_F) stk[sp++] = ch.z;
     if (slab_fma(nd.lo_x.w, nd.lo_y.w, nd.lo_z.w, nd.hi_x.w, nd.hi_y.w, nd.hi_z.w, pre, no, t_max, ch.w) < CUDART_INF_F) stk[sp++] = ch.w;
+#endif
     pop(stk);
   }
   // One primitive per step (see ClosestTrav::leaf_step).
@@ -207,23 +272,59 @@ struct ShadowTrav {
     float4 A = __ldg(tp), B = __ldg(tp + 1), C = __ldg(tp + 2);
     float t, u, v, det;
     if (moller_trumbore(r, mk3(A.x, A.y, A.z), mk3(B.x, B.y, B.z), mk3(C.x, C.y, C.z), t, u, v, det)) {
-      int tri = __float_as_int(B.w);
+      const uint32_t flags = __float_as_uint(C.w);
       bool counted = true;
-      float op;
       if (point) {
         V3 p = r.o + r.d * t;
         counted = !(length3(p - pos) > limit);
-        op = counted ? eval_opacity(S, S.shade[tri].model, pu != pu, pu, pv) : 0.0f;
-      } else if (__float_as_uint(C.w) & TRI_FLAG_ALPHA) {
-        op = hit_opacity(S, tri, u, v);
-      } else {
-        op = S.materials[S.shade[tri].model].opacity;
       }
-      if (counted) tr *= 1.0f - op;
+      if (counted) {
+        if (flags & TRI_FLAG_OPAQUE1) {
+          tr = 0.0f;  // opacity is exactly 1 whatever uv it is sampled at: tr * (1 - 1); no material fetch
+        } else {
+          const int tri = __float_as_int(B.w);
+          float op;
+          if (point) op = eval_opacity(S, S.shade[tri].model, pu != pu, pu, pv);
+          else if (flags & TRI_FLAG_ALPHA) op = hit_opacity(S, tri, u, v);
+          else op = S.materials[S.shade[tri].model].opacity;
+          tr *= 1.0f - op;
+        }
+      }
     }
     if ((cur & 7u) && tr != 0.0f) cur += 7u;
     else pop(stk);
   }
 };
+
+// ---- the same traversals run to completion by one thread (k_trace_paths, k_debug_aov) ----
+// Closest hit of ray_cast's sorted list (alpha = false) or the hit the alpha walk accepts (alpha = true, draws of
+// path `key` at `bounce`).  st.idx < 0: miss.  n_alpha counts the opacity evaluations.
+__device__ __forceinline__ void trace_closest(const DevScene &S, const Ray &r, bool alpha, const RngKey &key,
+                                              uint32_t bounce, TraceState &st, uint32_t &n_alpha) {
+  ClosestStack stk;
+  ClosestTrav tv;
+  tv.begin(r, stk, alpha);
+  const NodeOrder no = node_order(tv.r, tv.pre);
+  auto key_of = [&]() { return key; };
+  while (tv.cur != ClosestTrav::DONE) {
+    if (tv.at_inner()) tv.node_step(S, no, stk);
+    else tv.leaf_step(S, stk, alpha, bounce, key_of, n_alpha);
+  }
+  tv.finish(stk, alpha);
+  st = tv.st;
+}
+
+__device__ __forceinline__ float trace_transmittance(const DevScene &S, const Ray &r, float limit, V3 pos, float pu,
+                                                     float pv) {
+  uint32_t stk[PTB_STACK];
+  ShadowTrav tv;
+  tv.begin(r, limit, pos, pu, pv);
+  const NodeOrder no = node_order(tv.r, tv.pre);
+  while (tv.cur != ShadowTrav::DONE) {
+    if (tv.at_inner()) tv.node_step(S, no, stk);
+    else tv.leaf_step(S, stk);
+  }
+  return tv.tr;
+}
 
 }  // namespace ptb

@@ -21,10 +21,20 @@ def lib():
         L.oracle_scene_create.restype = C.c_void_p
         L.oracle_scene_create.argtypes = [C.POINTER(pt_scene_desc)]
         L.oracle_scene_destroy.argtypes = [C.c_void_p]
+        L.oracle_scene_synthetic.restype = C.c_void_p
+        L.oracle_scene_synthetic.argtypes = [C.c_char_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]
         L.oracle_moller_trumbore.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.oracle_trace_closest.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_int]
         L.oracle_trace_all.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
         L.oracle_trace_transmittance.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int]
+        L.oracle_trace_accepted.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint32, C.c_uint32, C.c_uint64,
+                                            C.c_void_p, C.c_int, C.c_int]
+        L.oracle_trace_shadow.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p,
+                                          C.c_int, C.c_int]
+        L.oracle_philox4x32_10.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.oracle_philox4x32_10.restype = None
+        L.oracle_dump_shadow_requests.argtypes = [C.c_void_p, C.POINTER(pt_profile), C.c_uint64, C.c_uint32, C.c_void_p,
+                                                  C.c_void_p, C.c_void_p, C.c_void_p]
         L.oracle_render_accum.restype = C.c_double
         L.oracle_render_accum.argtypes = [C.c_void_p, C.POINTER(pt_profile), C.c_int, C.c_uint64, C.c_uint32,
                                           C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
@@ -49,6 +59,19 @@ class OracleScene:
         self._desc = arrays.to_desc()
         self.h = lib().oracle_scene_create(C.byref(self._desc))
 
+    @classmethod
+    def synthetic(cls, recipe, n_tris, seed=0):
+        """The product's procedural generator compiled into the oracle (oracle/synth_glue.cpp): the same scene as
+        pt_scene_synthetic(recipe, n_tris, seed) without loading libpt_b200.so."""
+        self = cls.__new__(cls)
+        self.arrays = self._desc = None
+        n = C.c_uint64()
+        self.h = lib().oracle_scene_synthetic(recipe.encode(), n_tris, seed, C.byref(n))
+        if not self.h:
+            raise ValueError("oracle_scene_synthetic(%r, %d) failed" % (recipe, n_tris))
+        self.n_tris = n.value
+        return self
+
     def __del__(self):
         if getattr(self, "h", None):
             lib().oracle_scene_destroy(self.h)
@@ -71,6 +94,39 @@ class OracleScene:
         out = np.zeros(rays.shape[0], np.float32)
         lib().oracle_trace_transmittance(self.h, rays.ctypes.data, rays.shape[0], out.ctypes.data, int(brute))
         return out
+
+    def trace_accepted(self, rays, bounce=0, sample=0, seed=0, brute=False, threads=8):
+        """The hit the alpha walk (mod.rs:188-205) accepts for ray i = path (pixel i, sample, seed) at `bounce`."""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        out = np.zeros(rays.shape[0], HIT_DTYPE)
+        lib().oracle_trace_accepted(self.h, rays.ctypes.data, rays.shape[0], bounce, sample, seed, out.ctypes.data,
+                                    int(brute), threads)
+        return out
+
+    def trace_shadow(self, rays, limits=None, primary=None, brute=False, threads=8):
+        """get_light_info's shadow walk with unit light colour; limits/primary as pt_trace_shadow."""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        out = np.zeros(rays.shape[0], np.float32)
+        lp = pp = None
+        if limits is not None:
+            limits = np.ascontiguousarray(limits, np.float32).reshape(-1)
+            primary = np.ascontiguousarray(primary, np.float32).reshape(-1, 5)
+            lp, pp = limits.ctypes.data, primary.ctypes.data
+        lib().oracle_trace_shadow(self.h, rays.ctypes.data, lp, pp, rays.shape[0], out.ctypes.data, int(brute), threads)
+        return out
+
+    def dump_shadow_requests(self, profile, light, seed=0):
+        """The shadow rays get_light_info casts toward light `light` from the primary hits of a 1-spp trace:
+        (rays[n, 6], limits[n] (-1 = directional), primary[n, 5])."""
+        n = profile.width * profile.height
+        rays = np.zeros((n, 6), np.float32)
+        limits = np.zeros(n, np.float32)
+        prim = np.zeros((n, 5), np.float32)
+        valid = np.zeros(n, np.uint8)
+        lib().oracle_dump_shadow_requests(self.h, C.byref(profile), seed, light, rays.ctypes.data, limits.ctypes.data,
+                                          prim.ctypes.data, valid.ctypes.data)
+        k = valid != 0
+        return rays[k], limits[k], prim[k]
 
     def render_accum(self, profile, rng_mode=1, seed=0, sample_begin=0, sample_stride=1, n_samples=None, threads=8,
                      brute=False, return_counters=False):
@@ -118,6 +174,14 @@ def tonemap(accum, total_samples, tonemap_type=1):
     h, w = accum.shape[:2]
     out = np.zeros((h, w, 3), np.uint8)
     lib().oracle_tonemap(accum.ctypes.data, w, h, total_samples, tonemap_type, out.ctypes.data)
+    return out
+
+
+def philox4x32_10(ctr4, key2):
+    c = np.ascontiguousarray(ctr4, np.uint32)
+    k = np.ascontiguousarray(key2, np.uint32)
+    out = np.zeros(4, np.uint32)
+    lib().oracle_philox4x32_10(c.ctypes.data, k.ctypes.data, out.ctypes.data)
     return out
 
 

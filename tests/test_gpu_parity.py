@@ -1,5 +1,10 @@
 """GPU parity tests: every call goes through the C ABI (libpt_b200.so) and is checked against the CPU oracle.
 
+The fixed-batch entry points (pt_trace_closest / pt_trace_accepted / pt_trace_shadow) load the batch into the
+renderer's own queues and run the production kernels k_extend / k_shadow (ClosestTrav / ShadowTrav of
+csrc/traverse.cuh: fused slab test, approximate reciprocals, one-primitive leaf steps, lazy pops, lane-level ray
+replacement): every batch below is a check of the traversal that ships pixels.
+
 Bars (BASELINE.json north_star): closest-hit primitive ids bit-exact, t/u/v within 1e-5 relative (they are in fact
 bit-identical: the kernels compute Möller–Trumbore un-fused in the reference's operand order); images within 1 %
 relative RMSE.  Nothing here reads /root/reference: inputs are the committed fixtures under tests/golden/.
@@ -78,7 +83,7 @@ def test_closest_hit_random_rays(loaded, name):
 def test_closest_hit_secondary_rays(loaded, name):
     """Bounce-1 and bounce-2 rays of the oracle's own paths (origins on surfaces, biased by 1e-5)."""
     sa, osc, gsc = loaded[name]
-    prof = oracle_lib.make_profile(512, 512, 1, 4)
+    prof = oracle_lib.make_profile(1024, 1024, 1, 4)  # SURVEY 8(c): the oracle's bounce-1 rays at 1024x1024x1 spp
     for bounce in (1, 2):
         rr = osc.dump_bounce_rays(prof, bounce, seed=0xB2000002)
         if len(rr) == 0:
@@ -177,6 +182,126 @@ def test_directional_transmittance(loaded, name):
         assert ((o > 0) & (o < 1)).sum() > 100  # partial transmittance exercised
 
 
+@pytest.mark.parametrize("name", SCENES)
+def test_shadow_walk_of_real_requests(loaded, name):
+    """k_shadow on the shadow rays get_light_info (mod.rs:281-333) casts from the primary hits of a 512x512 frame,
+    one batch per light: point lights carry the distance limit and the primary hit's uv (the occluder's opacity is
+    sampled there, mod.rs:324), directional lights walk every hit."""
+    sa, osc, gsc = loaded[name]
+    prof = oracle_lib.make_profile(512, 512, 1, 1)
+    total = 0
+    for li, light in enumerate(sa.lights):
+        rays, lim, prim = osc.dump_shadow_requests(prof, li, seed=3)
+        if len(rays) == 0:
+            continue
+        if light["type"] == 0:
+            assert (lim >= 0).all()
+            g, o = gsc.trace_shadow(rays, lim, prim), osc.trace_shadow(rays, lim, prim, threads=THREADS)
+        else:
+            g, o = gsc.trace_shadow(rays), osc.trace_shadow(rays, threads=THREADS)
+        # products of (1 - opacity) in traversal order vs sorted order: equal up to float re-association
+        assert np.allclose(g, o, rtol=2e-6, atol=1e-7), (name, li, np.abs(g - o).max())
+        assert ((o == 0) == (g == 0)).all(), (name, li)
+        total += len(rays)
+    assert total > 1000 or not sa.lights
+
+
+def test_shadow_walk_point_light_synthetic_limits(loaded):
+    """Point-limited walk on random rays: the limit cuts the walk at random places (occluders beyond it are ignored),
+    the primary uv decides the opacity of textured occluders, a NaN u marks a sphere primary (simple material)."""
+    for sa, osc, gsc in (loaded["alpha_transparency"], loaded["spheres"]):
+        rr = R.random_rays(sa, 1 << 16, seed=31)
+        rng = np.random.Generator(np.random.PCG64(7))
+        c, rad = R.scene_bounds(sa)
+        lim = rng.uniform(0.0, 2.5 * rad, len(rr)).astype(np.float32)
+        prim = np.concatenate([rr[:, :3], rng.uniform(-1.5, 2.5, (len(rr), 2))], 1).astype(np.float32)
+        prim[::7, 3] = np.nan
+        g, o = gsc.trace_shadow(rr, lim, prim), osc.trace_shadow(rr, lim, prim, threads=THREADS)
+        assert np.allclose(g, o, rtol=2e-6, atol=1e-7)
+        assert ((o == 0) == (g == 0)).all()
+        assert (o == 1).sum() > 100 and (o < 1).sum() > 100
+
+
+# ---------------------------------------------------------------- alpha walk of render_pixel (mod.rs:188-205)
+@pytest.mark.parametrize("name", ["alpha_transparency", "head", "spheres"])
+def test_accepted_hit_alpha_walk(loaded, name):
+    """k_extend with the alpha walk on: the hit that gets shaded, for primary-like rays and for the oracle's bounce-1
+    rays, with the draws of path (pixel = ray index, sample, seed) — bit-exact ids and t/u/v."""
+    sa, osc, gsc = loaded[name]
+    batches = [(R.random_rays(sa, 1 << 18, seed=41), 0, 5, 77),
+               (osc.dump_bounce_rays(oracle_lib.make_profile(512, 512, 1, 4), 1, seed=0xB2000002), 1, 0, 0)]
+    for rr, bounce, sample, seed in batches:
+        g = gsc.trace_accepted(rr, bounce=bounce, sample=sample, seed=seed)
+        o = osc.trace_accepted(rr, bounce=bounce, sample=sample, seed=seed, threads=THREADS)
+        assert np.array_equal(g["prim_id"], o["prim_id"]), (name, bounce, int((g["prim_id"] != o["prim_id"]).sum()))
+        assert g.tobytes() == o.tobytes(), (name, bounce)
+    if name == "alpha_transparency":
+        first = gsc.trace_closest(batches[0][0])
+        g0 = gsc.trace_accepted(batches[0][0], bounce=0, sample=5, seed=77)
+        assert (first["prim_id"] != g0["prim_id"]).sum() > 1000  # transparent hits really are skipped
+        assert (g0["t"] >= first["t"])[first["prim_id"] >= 0].all()
+
+
+def test_accepted_hit_textured_scene_and_farthest_rule():
+    """Opacity textures (an opaque texel of a transparent-capable material ends the walk), a constant-alpha sphere,
+    and the rule that the farthest examined hit is shaded when every hit is rejected (mod.rs:188-205)."""
+    sa = textured_scene()
+    gsc, osc = pt.Scene.from_arrays(sa), oracle_lib.OracleScene(sa)
+    rr = R.random_rays(sa, 1 << 17, seed=2)
+    for bounce, sample in ((0, 0), (3, 9)):
+        g = gsc.trace_accepted(rr, bounce=bounce, sample=sample, seed=1)
+        o = osc.trace_accepted(rr, bounce=bounce, sample=sample, seed=1, brute=True, threads=THREADS)
+        assert g.tobytes() == o.tobytes()
+    # a scene of transparent cards only (opacity 0.0005 < 0.001: never accepted, no draw): the LAST card is shaded
+    cards = pt.abi.SceneArrays()
+    pos, n = [], 6
+    for k in range(n):
+        z = -float(k)
+        pos += [[-1, -1, z, 1, -1, z, 1, 1, z], [-1, -1, z, 1, 1, z, -1, 1, z]]
+    cards.tri_pos = np.array(pos, np.float32)
+    cards.tri_nrm = np.tile(np.array([0, 0, 1] * 3, np.float32), (2 * n, 1))
+    cards.tri_uv = np.tile(np.array([0, 0, 1, 0, 1, 1], np.float32), (2 * n, 1))
+    for k in range(n):
+        cards.models.append(dict(type=0, first_tri=2 * k, n_tris=2, center=[0, 0, 0], radius=0.0))
+        cards.materials.append(dict(albedo=[1, 1, 1], emissive=[0, 0, 0], opacity=0.5 if k % 2 == 0 else 0.0005,
+                                    metalness=0.0, roughness=1.0, ior=1.0))
+    gc, oc = pt.Scene.from_arrays(cards), oracle_lib.OracleScene(cards)
+    rng = np.random.Generator(np.random.PCG64(3))
+    o3 = np.concatenate([rng.uniform(-0.9, 0.9, (4096, 2)), np.full((4096, 1), 2.0)], 1)
+    rays = np.concatenate([o3, np.tile([0.0, 0.0, -1.0], (4096, 1))], 1).astype(np.float32)
+    g, o = gc.trace_accepted(rays, seed=5), oc.trace_accepted(rays, seed=5, brute=True, threads=THREADS)
+    assert g.tobytes() == o.tobytes()
+    last = g["prim_id"] >= 2 * (n - 1)
+    assert 0.08 < last.mean() < 0.18  # 0.5^3 of the paths reject all three half-transparent cards -> the last card
+
+
+def test_trace_large_batch_is_chunked(loaded):
+    """Batches larger than one pass through the queues (16 Mi rays) are split by the library: same records as the
+    rays traced on their own (32-bit ray indexing)."""
+    sa, osc, gsc = loaded["cube"]
+    base = R.random_rays(sa, 1 << 16, seed=8)
+    reps = (16 << 20) // len(base) + 3  # a little over one chunk
+    big = np.tile(base, (reps, 1))
+    g = gsc.trace_closest(big)
+    ref = gsc.trace_closest(base)
+    assert np.array_equal(g, np.tile(ref, reps))
+    assert np.array_equal(ref, osc.trace_closest(base, threads=THREADS))
+
+
+# ---------------------------------------------------------------- Philox4x32-10 (replaces rand's StdRng, mod.rs:110-118)
+def test_philox_kat():
+    from test_oracle_kat import PHILOX_KAT
+    ctr = np.array([c for c, _, _ in PHILOX_KAT], np.uint32)
+    key = np.array([k for _, k, _ in PHILOX_KAT], np.uint32)
+    want = np.array([w for _, _, w in PHILOX_KAT], np.uint32)
+    assert np.array_equal(pt.philox4x32_10(ctr, key), want)
+    rng = np.random.default_rng(4)
+    c, k = rng.integers(0, 2**32, (4096, 4), dtype=np.uint64), rng.integers(0, 2**32, (4096, 2), dtype=np.uint64)
+    got = pt.philox4x32_10(c, k)
+    for i in range(0, 4096, 97):
+        assert np.array_equal(got[i], oracle_lib.philox4x32_10(c[i], k[i]))
+
+
 # ---------------------------------------------------------------- render_pixel, vertex by vertex (mod.rs:172-228)
 @pytest.mark.parametrize("name", SCENES)
 def test_path_records(loaded, name):
@@ -224,24 +349,33 @@ def test_image_same_streams(loaded, name):
     gacc = rend.last_accum
     # per-pixel agreement almost everywhere; the mean image within the 1 % bar even at 16 spp
     close = np.abs(gacc - oacc) <= 1e-3 * np.maximum(np.abs(oacc), 1.0)
-    assert close.mean() > 0.97, close.mean()
+    # what differs: paths whose direction moved by an ulp of CUDA's vs glibc's sinf/cosf/acosf and flipped a hit at a
+    # silhouette or a roulette decision (a handful per frame); a wrong traversal would move whole regions
+    assert close.mean() >= 0.999, close.mean()
     med_g, med_o = np.median(gacc), np.median(oacc)
     assert abs(med_g - med_o) <= 1e-3 * max(1.0, abs(med_o))
     # 4x4 box-filtered means (fireflies of the pdf()=1 estimator dominate a raw RMSE at 16 spp)
     f = lambda a: a.reshape(64, 4, 64, 4, 3).mean((1, 3))
     assert rel_rmse(np.minimum(f(gacc), 1e3), np.minimum(f(oacc), 1e3)) < 0.01 or close.mean() > 0.995
     oimg = oracle_lib.tonemap(oacc, 16, 1)
-    assert (np.abs(img.astype(int) - oimg.astype(int)) <= 1).mean() > 0.97
+    assert (np.abs(img.astype(int) - oimg.astype(int)) <= 1).mean() >= 0.999
     st = rend.last_stats
     assert st["samples"] == 256 * 256 * 16 and st["extend_rays"] >= st["samples"]
+    assert st["shadow_dropped"] == 0 and st["alpha_recasts"] == 0
 
 
-@pytest.mark.parametrize("name", ["cube", "alpha_transparency", "spheres", "white_furnace_indirect"])
+# oracle-vs-oracle noise floor of the 48x48 / 4096 spp comparison, measured with tools/noise_floor.py:
+# where it is under 0.7 % the plain 1 % bar of the north star applies; above it (fireflies of the reference's pdf()=1
+# estimator) the bar is 1.5x the floor measured in the same test.
+NOISE_FLOOR_UNDER_0_7 = {"cube", "spheres", "white_furnace_direct", "white_furnace_indirect", "alpha_transparency"}
+
+
+@pytest.mark.parametrize("name", SCENES)
 def test_image_converged_4096spp(loaded, name):
     """north_star: rel-RMSE <= 1 % at 4096 spp, GPU vs oracle, with independent sample streams (different seeds),
-    and the oracle-vs-oracle noise floor beside it."""
+    and the oracle-vs-oracle noise floor beside it.  All seven reference scenes (src/main.rs:100-165)."""
     sa, osc, gsc = loaded[name]
-    prof = pt.Profile(width=48, height=48, samples=4096, bounces=4)
+    prof = pt.Profile(width=48, height=48, samples=4096, bounces=0 if name == "white_furnace_direct" else 4)
     rend = pt.Renderer(config=pt.RenderConfig(seed=1), profile=prof)
     rend.render(gsc, keep_accum=True)
     g = rend.last_accum / 4096.0
@@ -249,7 +383,10 @@ def test_image_converged_4096spp(loaded, name):
     o2 = osc.render_accum(prof.c, rng_mode=1, seed=3, threads=THREADS) / 4096.0
     clip = lambda a: np.minimum(a, 50.0)  # the reference's pdf()=1 estimator has unbounded-variance fireflies
     err, floor = rel_rmse(clip(g), clip(o)), rel_rmse(clip(o2), clip(o))
-    assert err < max(0.01, 1.5 * floor), (err, floor)
+    if name in NOISE_FLOOR_UNDER_0_7:
+        assert floor < 0.007 and err < 0.01, (err, floor)
+    else:
+        assert err < max(0.01, 1.5 * floor), (err, floor)
     assert abs(g.mean() - o.mean()) < 0.01 * o.mean() + 3e-3 * abs(o).max()
 
 
@@ -445,7 +582,7 @@ def test_textured_materials_vs_oracle():
     oacc = osc.render_accum(prof.c, rng_mode=1, threads=THREADS)
     close = np.abs(rend.last_accum - oacc) <= 1e-3 * np.maximum(np.abs(oacc), 1.0)
     assert close.mean() > 0.97, close.mean()
-    assert rend.last_stats["alpha_recasts"] > 0
+    assert rend.last_stats["alpha_tests"] > 0 and rend.last_stats["alpha_recasts"] == 0
 
 
 # ---------------------------------------------------------------- debug_render (debug_renderer.rs:11-105)
@@ -632,7 +769,8 @@ def test_full_size_foliage_properties():
     torch.cuda.synchronize()
     assert torch.isfinite(full).all()
     assert torch.allclose(full, parts, rtol=1e-4, atol=1e-5)
-    assert st["alpha_recasts"] > 0 and st["shadow_rays"] > 0 and st["extend_rays"] >= 480 * 270 * 4
+    assert st["alpha_tests"] > 0 and st["alpha_recasts"] == 0 and st["shadow_dropped"] == 0
+    assert st["shadow_rays"] > 0 and st["extend_rays"] >= 480 * 270 * 4
 
 
 def test_full_size_console_properties():
@@ -701,8 +839,7 @@ def test_edge_grazing_rays_match_brute_force(accel):
     bad = np.nonzero((got["prim_id"] != ref["prim_id"]) | (got["t"] != ref["t"]))[0]
     assert len(bad) == 0, (len(bad), rays[bad[:4]], got[bad[:4]], ref[bad[:4]])
     assert np.array_equal(osc.trace_closest(rays, threads=THREADS), ref)  # the oracle's own filter too
-    # through the render kernels (fused slab test, persistent traversal): one path vertex per ray is not reachable
-    # from the ABI, so the render-side check is tree independence of a full frame looking along the walls
+    # (trace_closest above already ran k_extend itself); a full frame looking along the walls is tree independent too
     prof = pt.Profile(width=256, height=144, samples=2, bounces=2)
     r1 = pt.Renderer(profile=prof)
     r1.render(sc, keep_accum=True)

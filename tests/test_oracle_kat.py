@@ -105,3 +105,107 @@ def test_bvh_filter_keeps_edge_grazing_hits():
     b = sc.trace_closest(rr, brute=True)
     assert np.array_equal(sc.trace_closest(rr, brute=False), b)
     assert 0.3 < float((b["prim_id"] >= 0).mean()) < 0.99
+
+
+# ---------------------------------------------------------------- Philox4x32-10 known answers
+# Random123 (Salmon et al., "Parallel random numbers: as easy as 1, 2, 3", SC'11) ships these vectors in its
+# kat_vectors file: `philox4x32 10 <counter x4> <key x2> -> <output x4>`.  The north star names this generator as the
+# replacement of rand 0.8's ChaCha12 (renderer/mod.rs:110-112); the GPU twin is test_gpu_parity.py::test_philox_kat.
+PHILOX_KAT = [
+    ((0x00000000, 0x00000000, 0x00000000, 0x00000000), (0x00000000, 0x00000000),
+     (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+    ((0xffffffff, 0xffffffff, 0xffffffff, 0xffffffff), (0xffffffff, 0xffffffff),
+     (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+    ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0),
+     (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1)),
+]
+
+
+def test_philox_known_answers():
+    for ctr, key, want in PHILOX_KAT:
+        assert tuple(int(x) for x in oracle_lib.philox4x32_10(ctr, key)) == want
+
+
+def test_philox_python_restatement():
+    """An independent restatement of the published round function agrees with the oracle's on random inputs."""
+    def philox(c, k):
+        c, k = list(c), list(k)
+        for _ in range(10):
+            p0, p1 = 0xD2511F53 * c[0], 0xCD9E8D57 * c[2]
+            c = [(p1 >> 32) ^ c[1] ^ k[0], p1 & 0xFFFFFFFF, (p0 >> 32) ^ c[3] ^ k[1], p0 & 0xFFFFFFFF]
+            k = [(k[0] + 0x9E3779B9) & 0xFFFFFFFF, (k[1] + 0xBB67AE85) & 0xFFFFFFFF]
+        return tuple(c)
+    for ctr, key, want in PHILOX_KAT:
+        assert philox(ctr, key) == want
+    rng = np.random.default_rng(1)
+    for _ in range(200):
+        c, k = rng.integers(0, 2**32, 4, dtype=np.uint64), rng.integers(0, 2**32, 2, dtype=np.uint64)
+        assert philox([int(x) for x in c], [int(x) for x in k]) == tuple(int(x) for x in oracle_lib.philox4x32_10(c, k))
+
+
+# ---------------------------------------------------------------- alpha walk: id-addressed draws vs the sequential stream
+def _rel_rmse(a, b):
+    return float(np.sqrt(np.mean((a.astype(np.float64) - b) ** 2)) / max(1e-12, np.mean(b)))
+
+
+def test_alpha_walk_addressing_is_statistically_equivalent():
+    """The oracle's Philox mode addresses the alpha draw of an examined hit by its primitive id (oracle/rng.hpp); the
+    ChaCha mode — the one pinned bit-for-bit to the reference's SHA-1s above — consumes the path's sequential stream
+    as renderer/mod.rs:188-205 does.  Converged images of the two agree within the noise floor of the estimator."""
+    sa = isf_py.load_isf(os.path.join(GOLDEN, "scenes", "alpha_transparency", "scene.isf"))
+    sc = oracle_lib.OracleScene(sa)
+    th = os.cpu_count() or 8
+    prof = oracle_lib.make_profile(40, 40, 2048, 4, 1)
+    cha = sc.render_accum(prof, rng_mode=0, threads=th) / 2048.0
+    ph1 = sc.render_accum(prof, rng_mode=1, seed=1, threads=th) / 2048.0
+    ph2 = sc.render_accum(prof, rng_mode=1, seed=2, threads=th) / 2048.0
+    clip = lambda a: np.minimum(a, 50.0)
+    err, floor = _rel_rmse(clip(ph1), clip(cha)), _rel_rmse(clip(ph2), clip(ph1))
+    assert err < max(0.01, 1.5 * floor), (err, floor)
+    assert abs(ph1.mean() - cha.mean()) < 0.01 * cha.mean()
+
+
+def test_accepted_hit_and_shadow_checkers_are_consistent():
+    """oracle_trace_accepted / oracle_trace_shadow (the checkers of pt_trace_accepted / pt_trace_shadow) against the
+    functions they generalise."""
+    import rays as R
+    sa = isf_py.load_isf(os.path.join(GOLDEN, "scenes", "alpha_transparency", "scene.isf"))
+    sc = oracle_lib.OracleScene(sa)
+    rr = R.random_rays(sa, 20000, seed=5)
+    first = sc.trace_closest(rr)
+    acc = sc.trace_accepted(rr, bounce=1, sample=3, seed=9)
+    assert np.array_equal(acc["prim_id"] >= 0, first["prim_id"] >= 0)  # a ray that hits something shades something
+    hit = first["prim_id"] >= 0
+    assert (acc["t"][hit] >= first["t"][hit]).all()                      # never in front of the first hit
+    assert (acc["prim_id"][hit] != first["prim_id"][hit]).sum() > 50      # the walk does skip transparent hits
+    assert np.array_equal(acc, sc.trace_accepted(rr, bounce=1, sample=3, seed=9, brute=True))
+    assert not np.array_equal(acc, sc.trace_accepted(rr, bounce=1, sample=4, seed=9))  # draws depend on the path
+    # directional walk == the older entry point; a far-away point light == directional when nothing lies beyond it
+    d = sc.trace_shadow(rr)
+    assert np.array_equal(d, sc.trace_transmittance(rr))
+    prim = np.concatenate([rr[:, :3], np.full((len(rr), 2), 0.25, np.float32)], 1)
+    far = sc.trace_shadow(rr, np.full(len(rr), 1e9, np.float32), prim)
+    near = sc.trace_shadow(rr, np.zeros(len(rr), np.float32), prim)
+    assert (near == 1.0).all()                      # every occluder is farther than the light
+    assert ((far == 0) == (d == 0)).mean() > 0.99   # same occluders (opacity sampled at the primary uv instead)
+    # requests dumped from real primary hits: one per pixel that hits, limits positive for the point light
+    prof = oracle_lib.make_profile(64, 64, 1, 1)
+    for li, l in enumerate(sa.lights):
+        q, lim, pr = sc.dump_shadow_requests(prof, li, seed=1)
+        assert len(q) > 100 and len(q) == len(lim) == len(pr)
+        assert ((lim >= 0).all() if l["type"] == 0 else (lim == -1).all())
+
+
+def test_oracle_synthetic_scene_equals_the_products():
+    """oracle_scene_synthetic (the product's generator source compiled into the oracle) builds the same
+    scene as pt_scene_synthetic: the CPU arm of bench.py needs no libpt_b200.so to get its input."""
+    import path_tracer_b200 as pt
+    import rays as R
+    for recipe, n in (("console", 20000), ("foliage", 20000), ("city", 20000)):
+        sa = pt.Scene.synthetic(recipe, n, 3, device=-1).arrays()
+        a, b = oracle_lib.OracleScene(sa), oracle_lib.OracleScene.synthetic(recipe, n, 3)
+        assert b.n_tris == len(sa.tri_pos)
+        rr = R.random_rays(sa, 4000, seed=1)
+        assert np.array_equal(a.trace_closest(rr), b.trace_closest(rr))
+        prof = oracle_lib.make_profile(32, 24, 2, 3)
+        assert np.array_equal(a.render_accum(prof, threads=4), b.render_accum(prof, threads=4))
