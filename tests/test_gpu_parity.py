@@ -367,7 +367,9 @@ def test_image_same_streams(loaded, name):
 # oracle-vs-oracle noise floor of the 48x48 / 4096 spp comparison, measured with tools/noise_floor.py:
 # where it is under 0.7 % the plain 1 % bar of the north star applies; above it (fireflies of the reference's pdf()=1
 # estimator) the bar is 1.5x the floor measured in the same test.
-NOISE_FLOOR_UNDER_0_7 = {"cube", "spheres", "white_furnace_direct", "white_furnace_indirect", "alpha_transparency"}
+# profiles/noise_floor_4096spp.json: cube 0.66 %, white_furnace_direct 0.54 %, white_furnace_indirect 0.59 %;
+# head 1.3 %, alpha_transparency 1.6 %, reflection 2.7 %, spheres 4.6 %.
+NOISE_FLOOR_UNDER_0_7 = {"cube", "white_furnace_direct", "white_furnace_indirect"}
 
 
 @pytest.mark.parametrize("name", SCENES)
