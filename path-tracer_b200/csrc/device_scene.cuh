@@ -66,7 +66,7 @@ struct DevScene {
   const uint8_t *texels;
   const DevLight *lights;
   const float *tri_pos9;  // original-order positions; only uploaded when a normal map exists
-  const float *srgb_lut;  // 256 entries: powf(i / 255, 2.2), the sRGB -> linear step of material.rs:132-146
+  const float *srgb_lut;  // [0,256): powf(i / 255, 2.2), the sRGB -> linear step of material.rs:132-146; [256,512): i / 255
   uint32_t n_tris, n_spheres, n_lights, n_nodes;
   uint32_t root_is_valid;
   uint32_t any_alpha;  // some material may be non-opaque

@@ -266,7 +266,6 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     W.counters[CTR_QUEUE(outb)] = 0;  // the queues k_shade(bounce) appends to
     W.counters[CTR_SHADOW(outb)] = 0;
-    W.counters[CTR_WORK_SHADOW] = 0;
     W.counters[CTR_HITS] = 0;  // filled by k_hit_list after this kernel
     stat_add(W.counters, CTR_STAT_EXTEND, n);
   }
@@ -414,7 +413,12 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
 #else
   const uint32_t n = W.counters[CTR_QUEUE(in)];
 #endif
-  if (blockIdx.x == 0 && threadIdx.x == 0) W.counters[CTR_WORK_EXTEND] = 0;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    W.counters[CTR_WORK_EXTEND] = 0;
+    // the shadow kernel's cursor is reset here, not in k_extend: k_shadow(bounce - 1) may still be running beside
+    // k_extend(bounce) on another stream (render.cu), but it has always finished before this kernel starts
+    W.counters[CTR_WORK_SHADOW] = 0;
+  }
   uint32_t *pair = &W.counters[CTR_QUEUE(outb)];
   const uint32_t warps = gridDim.x * (blockDim.x >> 5), warp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   for (uint32_t base = warp * 32u; base < n; base += warps * 32u) {
@@ -719,7 +723,11 @@ __global__ void __launch_bounds__(256) k_accum_add(float *__restrict__ dst, cons
 }
 
 // sRGB -> linear table: the albedo texel conversion of material.rs:132-146, evaluated once per texel value.
-__global__ void k_init_srgb_lut(float *lut) { lut[threadIdx.x] = powf((float)threadIdx.x / 255.0f, 2.2f); }
+// Second half: texel / 255 (the metalness / roughness / opacity / emissive scalings of material.rs:152-214).
+__global__ void k_init_srgb_lut(float *lut) {
+  lut[threadIdx.x] = powf((float)threadIdx.x / 255.0f, 2.2f);
+  lut[256 + threadIdx.x] = (float)threadIdx.x / 255.0f;
+}
 
 // ------------------------------------------------------------------------------------------------
 // host-side launchers
@@ -792,10 +800,15 @@ void launch_shade(const DevScene &S, const WaveParams &P, const WaveState &W, ui
     grid = resident_grid(k_shade, 128);
     cache[dev].store(grid, std::memory_order_relaxed);
   }
+  k_shade<<<grid, 128, 0, st>>>(S, P, W, bounce);
+}
+// the scan pass between k_extend and k_shade (a no-op build without PTB_HIT_LIST)
+void launch_hit_list(const DevScene &S, const WaveState &W, uint32_t bounce, cudaStream_t st) {
 #if PTB_HIT_LIST
   k_hit_list<<<sm_count() * 8, 256, 0, st>>>(S, W, bounce);
+#else
+  (void)S; (void)W; (void)bounce; (void)st;
 #endif
-  k_shade<<<grid, 128, 0, st>>>(S, P, W, bounce);
 }
 int shade_launches() { return 1 + PTB_HIT_LIST; }
 void launch_shadow(const DevScene &S, const WaveState &W, uint32_t bounce, cudaStream_t st) {

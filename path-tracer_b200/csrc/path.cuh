@@ -91,10 +91,15 @@ __device__ __forceinline__ bool light_request(const DevScene &S, const ShadeCtx 
     dir = mk3(L.vec[0], L.vec[1], L.vec[2]);
   } else {
     V3 dv = c.sf.position - mk3(L.vec[0], L.vec[1], L.vec[2]);
+    // the distance limit of the shadow walk stays IEEE (it decides which occluders count, mod.rs:320-323)
     limit = length3(dv);
+#if PTB_SHADE_FAST
+    dir = dv * sh_div(1.0f, limit);
+#else
     dir = normalize3(dv);
+#endif
     float dissipation = 4.0f * PTB_PI * limit * limit;
-    lc = lc / dissipation;
+    lc = sh_vdiv(lc, dissipation);
   }
   sd = -1.0f * dir;
   so = c.sf.position + c.sf.normal * NORMAL_BIAS;
@@ -121,7 +126,7 @@ __device__ __forceinline__ bool shade_finish(const WaveParams &P, const RngKey &
   if (dot3(thr, thr) < 0.00001f) return false;  // mod.rs:219-221
   if (bounce > 3) {                             // utils.rs:23-31
     float p = fmaxf(fmaxf(thr.x, thr.y), thr.z);
-    thr = thr * (1.0f / p);
+    thr = thr * sh_div(1.0f, p);
     if (u32_to_unit(rb.z) > p) return false;
   }
   return more;

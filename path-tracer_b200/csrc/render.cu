@@ -79,6 +79,9 @@ struct pt_scene {
   // Recorded at the end of every call that used the wave buffers, waited on at the start of the next one: calls on
   // one scene from different streams are serialised on the device (the host side is serialised by `mu`).
   cudaEvent_t busy = nullptr;
+  // second stream + events of the overlapped schedule (k_shadow of bounce b beside k_extend of bounce b + 1)
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_shade = nullptr, ev_shadow = nullptr;
   // frame buffers of pt_render / pt_render_multi and staging buffers of the host-pointer trace entry points, kept
   // between calls (cudaFree synchronises the device: not once per frame)
   struct FrameBuf {
@@ -225,7 +228,7 @@ int build_device_scene(pt_scene *sc) {
     if ((rc = upload(sc, h.pos, &D.tri_pos9))) return rc;
   {
     float *lut = nullptr;
-    CUDA_TRY(cudaMalloc(&lut, 256 * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&lut, 512 * sizeof(float)));
     sc->allocs.push_back(lut);
     launch_init_srgb_lut(lut, nullptr);
     CUDA_TRY(cudaGetLastError());
@@ -313,6 +316,17 @@ struct WaveLock {
     if (sc->busy) cudaEventRecord(sc->busy, st);
   }
 };
+
+// $PT_B200_OVERLAP (default on): k_shadow(b) only adds to the radiance sums, so it runs on a second stream beside
+// k_hit_list / k_extend of bounce b + 1 and the tails of the persistent kernels overlap; k_shade(b + 1), which refills
+// the shadow queue, waits for it.  Off while per-kernel timing is requested (one event timeline).
+bool overlap_enabled() {
+  static const int on = [] {
+    const char *e = std::getenv("PT_B200_OVERLAP");
+    return e ? std::atoi(e) : 1;
+  }();
+  return on != 0;
+}
 
 int no_device() {
   set_error("scene was created host-only (device -1): no CPU fallback exists for tracing or rendering");
@@ -432,6 +446,9 @@ void pt_scene_destroy(pt_scene *sc) {
   for (pt_scene::FrameBuf *b : {&sc->multi_accum, &sc->multi_tmp, &sc->multi_rgb, &sc->trace_in, &sc->trace_aux, &sc->trace_out})
     cudaFree(b->p);
   if (sc->busy) cudaEventDestroy(sc->busy);
+  if (sc->ev_shade) cudaEventDestroy(sc->ev_shade);
+  if (sc->ev_shadow) cudaEventDestroy(sc->ev_shadow);
+  if (sc->side) cudaStreamDestroy(sc->side);
   for (void *p : sc->allocs) cudaFree(p);
   for (auto &s : sc->staged) cudaFreeHost(s.host);
   for (cudaEvent_t e : sc->events) cudaEventDestroy(e);
@@ -795,6 +812,16 @@ int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t
     marks.push_back(cls);
   };
   mark(3);
+  bool overlap = overlap_enabled() && !timing && sc->dev.n_lights > 0;
+  if (overlap && !sc->side) {
+    if (cudaStreamCreateWithFlags(&sc->side, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&sc->ev_shade, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&sc->ev_shadow, cudaEventDisableTiming) != cudaSuccess) {
+      cudaGetLastError();
+      overlap = false;
+    }
+  }
+  bool shadow_pending = false;  // a k_shadow on the side stream that the main stream has not waited for yet
   for (uint32_t done = 0; done < n_samples; done += spw) {
     WaveParams P;
     P.width = prof->width;
@@ -812,17 +839,34 @@ int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t
     for (uint32_t b = 0; b <= prof->bounces; ++b) {
       launch_extend(sc->dev, P, W, b, sc->dev.any_alpha != 0, nullptr, st);
       mark(0);
+      launch_hit_list(sc->dev, W, b, st);
+      if (shadow_pending) {  // k_shade refills the shadow queue the previous bounce's k_shadow reads
+        CUDA_TRY(cudaStreamWaitEvent(st, sc->ev_shadow, 0));
+        shadow_pending = false;
+      }
       launch_shade(sc->dev, P, W, b, st);
       mark(1);
       launches += 1 + shade_launches();
       ++n_ext;
       ++n_shade;
       if (sc->dev.n_lights) {
-        launch_shadow(sc->dev, W, b, st);
+        if (overlap) {
+          CUDA_TRY(cudaEventRecord(sc->ev_shade, st));
+          CUDA_TRY(cudaStreamWaitEvent(sc->side, sc->ev_shade, 0));
+          launch_shadow(sc->dev, W, b, sc->side);
+          CUDA_TRY(cudaEventRecord(sc->ev_shadow, sc->side));
+          shadow_pending = true;
+        } else {
+          launch_shadow(sc->dev, W, b, st);
+        }
         mark(2);
         ++launches;
         ++n_shadow;
       }
+    }
+    if (shadow_pending) {  // the radiance sums are complete only after the last k_shadow
+      CUDA_TRY(cudaStreamWaitEvent(st, sc->ev_shadow, 0));
+      shadow_pending = false;
     }
     launch_resolve(P, W, accum_dev, st);
     mark(3);

@@ -16,6 +16,45 @@ namespace ptb {
 
 #define PTB_PI 3.14159265358979323846f
 
+// Arithmetic of the SHADING functions (Cook-Torrance, light set-up, GGX sampling).  PTB_SHADE_FAST = 0 evaluates them
+// with IEEE division / square root and libm-style sinf / cosf / acosf in the reference's operand order (bit-identical
+// to the CPU oracle up to the last ulp of the transcendental functions).  PTB_SHADE_FAST = 1 uses the hardware
+// approximations (div.approx / rsqrt.approx / sqrt.approx, <= 2 ulp) and an algebraically equivalent form of the GGX
+// sample that needs no inverse trigonometry.  Intersection arithmetic (Moller-Trumbore, spheres, raygen, hit points,
+// ray origins) is never touched by this switch: hit ids and t/u/v stay bit-exact; only shading VALUES move, by ~1e-7
+// relative, far inside the image tolerance of the north star (1 % rel-RMSE) and of tests/test_gpu_parity.py.
+// Why: the 34 IEEE divisions and 10 square roots of the shading code expand to ~600 of k_shade's ~2900 instructions
+// and sinf / cosf / acosf with their large-argument slow paths to another ~350; the kernel's top stall was
+// instruction fetch (52 KB of code against a 32 KB instruction cache).
+#ifndef PTB_SHADE_FAST
+#define PTB_SHADE_FAST 1
+#endif
+__device__ __forceinline__ float sh_div(float a, float b) {
+#if PTB_SHADE_FAST
+  return __fdividef(a, b);
+#else
+  return a / b;
+#endif
+}
+__device__ __forceinline__ float sh_sqrt(float a) {
+#if PTB_SHADE_FAST
+  float r;
+  asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(a));
+  return r;
+#else
+  return sqrtf(a);
+#endif
+}
+
+__device__ __forceinline__ V3 sh_vdiv(V3 a, float s) { return {sh_div(a.x, s), sh_div(a.y, s), sh_div(a.z, s)}; }
+__device__ __forceinline__ V3 sh_normalize(V3 a) {
+#if PTB_SHADE_FAST
+  return a * rsqrtf(dot3(a, a));
+#else
+  return a * (1.0f / length3(a));
+#endif
+}
+
 // ---------------- Philox4x32-10 (counter-based; replaces rand's ChaCha12 StdRng) ----------------
 // key = (pixel, sample), counter = (block, tag, seed_lo, seed_hi).  Draw names:
 //   tag 0 block 0: [jitter x, jitter y, -, -]
@@ -87,7 +126,17 @@ __device__ __forceinline__ uint32_t texel_index(float c, uint32_t n) {
   }
   return texel_index_wide(c, n);
 }
-__device__ __forceinline__ const uint8_t *get_pixel(const DevScene &S, int tex, float u, float v) {
+#ifndef PTB_TEX_INLINE
+#define PTB_TEX_INLINE 0
+#endif
+#if PTB_TEX_INLINE
+__device__ __forceinline__
+#else
+// one copy per kernel instead of one per texture slot (six in k_shade): the shading kernel's code no longer fits the
+// instruction cache when every slot carries its own two texel_index expansions
+__device__ __noinline__
+#endif
+const uint8_t *get_pixel(const DevScene &S, int tex, float u, float v) {
   const DevTexture t = S.textures[tex];
   float cx = u * (float)t.width, cy = v * (float)t.height;
   const uint32_t x = texel_index(cx, t.width), y = texel_index(cy, t.height);
@@ -99,9 +148,13 @@ struct MatSample {
   V3 albedo, emissive;
 };
 
+// `texel as f32 / 255.` (material.rs:152-214) from the second half of the scene's 512-entry table (k_init_srgb_lut
+// fills it with that very IEEE division): bit-identical, one load instead of a division sequence per texel
+__device__ __forceinline__ float unit_of(const DevScene &S, uint8_t texel) { return __ldg(S.srgb_lut + 256 + texel); }
+
 __device__ __forceinline__ float eval_opacity(const DevScene &S, int model, bool simple, float u, float v) {
   const DevMaterial &m = S.materials[model];
-  if (!simple && m.opacity_tex >= 0) return (float)get_pixel(S, m.opacity_tex, u, v)[0] / 255.0f * m.opacity;
+  if (!simple && m.opacity_tex >= 0) return unit_of(S, get_pixel(S, m.opacity_tex, u, v)[0]) * m.opacity;
   return m.opacity;
 }
 
@@ -116,17 +169,17 @@ __device__ __forceinline__ MatSample material_sample(const DevScene &S, int mode
   r.emissive = ef;
   r.opacity = m.opacity;
   if (!simple) {
-    if (m.metalness_tex >= 0) r.metalness = (float)get_pixel(S, m.metalness_tex, u, v)[0] / 255.0f * m.metalness;
-    if (m.roughness_tex >= 0) rough = (float)get_pixel(S, m.roughness_tex, u, v)[0] / 255.0f * m.roughness;
+    if (m.metalness_tex >= 0) r.metalness = unit_of(S, get_pixel(S, m.metalness_tex, u, v)[0]) * m.metalness;
+    if (m.roughness_tex >= 0) rough = unit_of(S, get_pixel(S, m.roughness_tex, u, v)[0]) * m.roughness;
     if (m.albedo_tex >= 0) {
       const uint8_t *p = get_pixel(S, m.albedo_tex, u, v);
       // powf(texel / 255, 2.2) through a 256-entry table filled by k_init_srgb_lut with the very same expression
       r.albedo = mul_el(mk3(__ldg(S.srgb_lut + p[0]), __ldg(S.srgb_lut + p[1]), __ldg(S.srgb_lut + p[2])), af);
     }
-    if (m.opacity_tex >= 0) r.opacity = (float)get_pixel(S, m.opacity_tex, u, v)[0] / 255.0f * m.opacity;
+    if (m.opacity_tex >= 0) r.opacity = unit_of(S, get_pixel(S, m.opacity_tex, u, v)[0]) * m.opacity;
     if (m.emissive_tex >= 0) {
       const uint8_t *p = get_pixel(S, m.emissive_tex, u, v);
-      r.emissive = mul_el(mk3((float)p[0] / 255.0f, (float)p[1] / 255.0f, (float)p[2] / 255.0f), ef);
+      r.emissive = mul_el(mk3(unit_of(S, p[0]), unit_of(S, p[1]), unit_of(S, p[2])), ef);
     }
   }
   r.roughness = fmaxf(rough, 0.0001f);
@@ -146,12 +199,12 @@ struct Surface {
 // hit.rs:60-69 + :116-127.  e1,e2 = triangle edges, d1,d2 = uv deltas.
 __device__ __forceinline__ V3 normal_from_map(V3 hit_normal, V3 e1, V3 e2, float d1x, float d1y, float d2x, float d2y,
                                               const uint8_t *p) {
-  float f = 1.0f / (d1x * d2y - d2x * d1y);
-  V3 tangent = normalize3(mk3(f * (d2y * e1.x - d1y * e2.x), f * (d2y * e1.y - d1y * e2.y), f * (d2y * e1.z - d1y * e2.z)));
-  V3 nm = mk3((float)p[0] / 127.5f - 1.0f, (float)p[1] / 127.5f - 1.0f, (float)p[2] / 127.5f - 1.0f);
+  float f = sh_div(1.0f, d1x * d2y - d2x * d1y);
+  V3 tangent = sh_normalize(mk3(f * (d2y * e1.x - d1y * e2.x), f * (d2y * e1.y - d1y * e2.y), f * (d2y * e1.z - d1y * e2.z)));
+  V3 nm = mk3(sh_div((float)p[0], 127.5f) - 1.0f, sh_div((float)p[1], 127.5f) - 1.0f, sh_div((float)p[2], 127.5f) - 1.0f);
   V3 bit = cross3(hit_normal, tangent);
   V3 w = (tangent * nm.x + bit * nm.y) + hit_normal * nm.z;
-  return normalize3(w);
+  return sh_normalize(w);
 }
 
 __device__ __forceinline__ Surface make_surface(const DevScene &S, const Ray &r, float dist, float bu, float bv, int idx) {
@@ -228,11 +281,11 @@ __device__ __forceinline__ Brdf make_brdf(const MatSample &s) {
 __device__ __forceinline__ V3 fresnel(const Brdf &b, float c) {
   return b.f0 + mk3(1.0f - b.f0.x, 1.0f - b.f0.y, 1.0f - b.f0.z) * powi5(1.0f - c);
 }
-__device__ __forceinline__ float g1(float ndv, float k) { return ndv / (ndv * (1.0f - k) + k); }
+__device__ __forceinline__ float g1(float ndv, float k) { return sh_div(ndv, ndv * (1.0f - k) + k); }
 __device__ __forceinline__ float geometry(const Brdf &b, V3 n, V3 v, V3 l) {
   float ndv = fmaxf(dot3(n, v), 0.0f), ndl = fmaxf(dot3(n, l), 0.0f);
   float a1 = b.roughness + 1.0f;
-  float k = (a1 * a1) / 8.0f;
+  float k = (a1 * a1) / 8.0f;  // exact either way: a division by a power of two
   return g1(ndv, k) * g1(ndl, k);
 }
 __device__ __forceinline__ float ndf(const Brdf &b, V3 n, V3 h) {
@@ -240,17 +293,22 @@ __device__ __forceinline__ float ndf(const Brdf &b, V3 n, V3 h) {
   float ndh = fmaxf(dot3(n, h), 0.0f);
   float denom = (ndh * ndh) * (a2 - 1.0f) + 1.0f;
   denom = PTB_PI * denom * denom;
-  return a2 / denom;
+  return sh_div(a2, denom);
 }
 __device__ __forceinline__ V3 diffuse(const Brdf &b, V3 ks, V3 n, V3 l) {
   V3 kd = mk3(1.0f - ks.x, 1.0f - ks.y, 1.0f - ks.z) * (1.0f - b.metalness);
-  V3 dif = mul_el(kd, b.albedo) / PTB_PI;
+  V3 dif = sh_vdiv(mul_el(kd, b.albedo), PTB_PI);
   return dif * fmaxf(dot3(n, l), 0.0f);
 }
 __device__ __forceinline__ V3 transform_to_world(V3 vec, V3 n) {
   V3 nt;
+#if PTB_SHADE_FAST
+  if (fabsf(n.x) > fabsf(n.y)) nt = mk3(n.z, 0.0f, -n.x) * rsqrtf(n.x * n.x + n.z * n.z);
+  else nt = mk3(0.0f, -n.z, n.y) * rsqrtf(n.y * n.y + n.z * n.z);
+#else
   if (fabsf(n.x) > fabsf(n.y)) nt = mk3(n.z, 0.0f, -n.x) / sqrtf(n.x * n.x + n.z * n.z);
   else nt = mk3(0.0f, -n.z, n.y) / sqrtf(n.y * n.y + n.z * n.z);
+#endif
   V3 nb = cross3(n, nt);
   return mk3(vec.x * nb.x + vec.y * n.x + vec.z * nt.x, vec.x * nb.y + vec.y * n.y + vec.z * nt.y,
              vec.x * nb.z + vec.y * n.z + vec.z * nt.z);
@@ -259,31 +317,41 @@ __device__ __forceinline__ V3 reflection(V3 i, V3 n) { return (2.0f * fmaxf(dot3
 
 __device__ __forceinline__ V3 brdf_sample(Brdf &b, V3 n, V3 v, float r1, float r2) {
   float a = b.roughness * b.roughness, a2 = a * a;
+#if PTB_SHADE_FAST
+  // cook_torrance.rs:119-133 with theta eliminated: cos^2 = (1 - r1) / den, hence sin^2 = 1 - cos^2 = r1 a2 / den
+  // (no cancellation, no acos / sin / cos of theta); phi = 2 pi r2 through sincospi (exact range reduction)
+  const float inv_den = sh_div(1.0f, r1 * (a2 - 1.0f) + 1.0f);
+  const float ct = sh_sqrt((1.0f - r1) * inv_den), st = sh_sqrt((r1 * a2) * inv_den);
+  float sp, cp;
+  sincospif(2.0f * r2, &sp, &cp);
+  V3 ml = sh_normalize(mk3(st * cp, ct, st * sp));
+#else
   float theta = acosf(sqrtf((1.0f - r1) / (r1 * (a2 - 1.0f) + 1.0f)));
   float phi = 2.0f * PTB_PI * r2;
   float st = sinf(theta);
   V3 ml = normalize3(mk3(st * cosf(phi), cosf(theta), st * sinf(phi)));
-  b.m = normalize3(transform_to_world(ml, n));
-  return normalize3(reflection(v, b.m));
+#endif
+  b.m = sh_normalize(transform_to_world(ml, n));
+  return sh_normalize(reflection(v, b.m));
 }
 __device__ __forceinline__ V3 eval_direct(const Brdf &b, V3 n, V3 v, V3 l) {
-  V3 h = normalize3(v + l);
+  V3 h = sh_normalize(v + l);
   float d = ndf(b, n, h);
   V3 f = fresnel(b, fmaxf(dot3(h, v), 0.0f));
   float g = geometry(b, n, v, l);
-  V3 spec = ((d * f) * g) / fmaxf((4.0f * fmaxf(dot3(n, v), 0.0f)) * fmaxf(dot3(n, l), 0.0f), 0.0001f);
+  V3 spec = sh_vdiv((d * f) * g, fmaxf((4.0f * fmaxf(dot3(n, v), 0.0f)) * fmaxf(dot3(n, l), 0.0f), 0.0001f));
   spec = spec * fmaxf(dot3(n, l), 0.0f);
   return (diffuse(b, f, n, l) + spec) + b.emissive;
 }
 __device__ __forceinline__ V3 eval_indirect(const Brdf &b, V3 n, V3 v, V3 l) {
-  V3 h = normalize3(v + l);
+  V3 h = sh_normalize(v + l);
   V3 f = fresnel(b, fmaxf(dot3(h, v), 0.0f));
   float g = geometry(b, n, v, l);
   V3 spec = mk3(0.f, 0.f, 0.f);
   if (dot3(n, l) > 0.0f) {
     float num = fabsf(dot3(v, b.m));
     float den = fabsf(dot3(v, n)) * fabsf(dot3(b.m, n));
-    spec = (f * g) * (num / den);
+    spec = (f * g) * sh_div(num, den);
   }
   return diffuse(b, f, n, l) + spec;
 }

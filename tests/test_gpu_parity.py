@@ -305,8 +305,9 @@ def test_philox_kat():
 # ---------------------------------------------------------------- render_pixel, vertex by vertex (mod.rs:172-228)
 @pytest.mark.parametrize("name", SCENES)
 def test_path_records(loaded, name):
-    """One path per pixel, recorded bounce by bounce.  Primary segments are bit-identical; later ones differ only
-    through the last-ulp differences between CUDA's and glibc's sinf/cosf/acosf/powf ("Numerics")."""
+    """One path per pixel, recorded bounce by bounce.  Primary segments are bit-identical (intersection arithmetic is
+    IEEE and un-fused everywhere); later ones differ through the shading arithmetic, which the product evaluates with
+    the hardware's <= 2 ulp division / square root (shade.cuh, PTB_SHADE_FAST) where the oracle uses glibc."""
     sa, osc, gsc = loaded[name]
     bounces = 0 if name == "white_furnace_direct" else 5
     prof = pt.Profile(width=160, height=120, samples=1, bounces=bounces)
@@ -328,8 +329,9 @@ def test_path_records(loaded, name):
     close = (np.abs(last_g - last_o) <= tol).all(1)
     # mirror-like GGX lobes (roughness clamped to 1e-4) amplify one-ulp differences: allow a small tail
     assert close.mean() > 0.97, close.mean()
-    bit = np.array([gv[i].tobytes() == ov[i].tobytes() for i in range(len(pix))])
-    assert bit.mean() > 0.5, bit.mean()  # diagnostic: most paths do not differ in a single bit
+    thr_g = gv[np.arange(len(pix)), gc - 1]["throughput"][same_prims]
+    thr_o = ov[np.arange(len(pix)), oc - 1]["throughput"][same_prims]
+    assert (np.abs(thr_g - thr_o) <= 1e-4 * np.maximum(np.abs(thr_o), 1e-3)).all(1).mean() > 0.97
 
 
 # ---------------------------------------------------------------- Renderer::render (mod.rs:76-169)
