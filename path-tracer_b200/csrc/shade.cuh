@@ -126,14 +126,16 @@ __device__ __forceinline__ uint32_t texel_index(float c, uint32_t n) {
   }
   return texel_index_wide(c, n);
 }
+// PTB_TEX_INLINE = 0 keeps ONE out-of-line copy of the texel addressing per kernel instead of one per texture slot
+// (six in k_shade, -430 instructions).  Measured (profiles/r07/ab_s1.jsonl): the call costs more than the smaller
+// footprint gains wherever textures are actually fetched (k_shade +19 % on the console scene, +8 % on foliage), so
+// the default stays inline.
 #ifndef PTB_TEX_INLINE
-#define PTB_TEX_INLINE 0
+#define PTB_TEX_INLINE 1
 #endif
 #if PTB_TEX_INLINE
 __device__ __forceinline__
 #else
-// one copy per kernel instead of one per texture slot (six in k_shade): the shading kernel's code no longer fits the
-// instruction cache when every slot carries its own two texel_index expansions
 __device__ __noinline__
 #endif
 const uint8_t *get_pixel(const DevScene &S, int tex, float u, float v) {
@@ -152,6 +154,12 @@ struct MatSample {
 // fills it with that very IEEE division): bit-identical, one load instead of a division sequence per texel
 __device__ __forceinline__ float unit_of(const DevScene &S, uint8_t texel) { return __ldg(S.srgb_lut + 256 + texel); }
 
+// the rarely used texture slots share one out-of-line copy of the texel addressing; albedo and opacity (every textured
+// hit / every examined transparent hit) keep theirs inline
+__device__ __noinline__ const uint8_t *get_pixel_cold(const DevScene &S, int tex, float u, float v) {
+  return get_pixel(S, tex, u, v);
+}
+
 __device__ __forceinline__ float eval_opacity(const DevScene &S, int model, bool simple, float u, float v) {
   const DevMaterial &m = S.materials[model];
   if (!simple && m.opacity_tex >= 0) return unit_of(S, get_pixel(S, m.opacity_tex, u, v)[0]) * m.opacity;
@@ -169,16 +177,16 @@ __device__ __forceinline__ MatSample material_sample(const DevScene &S, int mode
   r.emissive = ef;
   r.opacity = m.opacity;
   if (!simple) {
-    if (m.metalness_tex >= 0) r.metalness = unit_of(S, get_pixel(S, m.metalness_tex, u, v)[0]) * m.metalness;
-    if (m.roughness_tex >= 0) rough = unit_of(S, get_pixel(S, m.roughness_tex, u, v)[0]) * m.roughness;
+    if (m.metalness_tex >= 0) r.metalness = unit_of(S, get_pixel_cold(S, m.metalness_tex, u, v)[0]) * m.metalness;
+    if (m.roughness_tex >= 0) rough = unit_of(S, get_pixel_cold(S, m.roughness_tex, u, v)[0]) * m.roughness;
     if (m.albedo_tex >= 0) {
       const uint8_t *p = get_pixel(S, m.albedo_tex, u, v);
       // powf(texel / 255, 2.2) through a 256-entry table filled by k_init_srgb_lut with the very same expression
       r.albedo = mul_el(mk3(__ldg(S.srgb_lut + p[0]), __ldg(S.srgb_lut + p[1]), __ldg(S.srgb_lut + p[2])), af);
     }
-    if (m.opacity_tex >= 0) r.opacity = unit_of(S, get_pixel(S, m.opacity_tex, u, v)[0]) * m.opacity;
+    if (m.opacity_tex >= 0) r.opacity = unit_of(S, get_pixel_cold(S, m.opacity_tex, u, v)[0]) * m.opacity;
     if (m.emissive_tex >= 0) {
-      const uint8_t *p = get_pixel(S, m.emissive_tex, u, v);
+      const uint8_t *p = get_pixel_cold(S, m.emissive_tex, u, v);
       r.emissive = mul_el(mk3(unit_of(S, p[0]), unit_of(S, p[1]), unit_of(S, p[2])), ef);
     }
   }
@@ -249,7 +257,7 @@ __device__ __forceinline__ Surface make_surface(const DevScene &S, const Ray &r,
     V3 e1 = mk3(pp[3] - pp[0], pp[4] - pp[1], pp[5] - pp[2]);
     V3 e2 = mk3(pp[6] - pp[0], pp[7] - pp[1], pp[8] - pp[2]);
     n = normal_from_map(sf.normal, e1, e2, u1x - u0x, u1y - u0y, u2x - u0x, u2y - u0y,
-                        get_pixel(S, m.normal_tex, sf.tu, sf.tv));
+                        get_pixel_cold(S, m.normal_tex, sf.tu, sf.tv));
   }
   if (idx & HIT_BACKFACE) n = -n;
   sf.shading_n = n;

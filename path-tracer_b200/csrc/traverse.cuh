@@ -180,7 +180,13 @@ struct ClosestTrav {
 };
 
 #ifndef PTB_SHADOW_ORDERED
-#define PTB_SHADOW_ORDERED 0  // 1: k_shadow visits the children of a node nearest-first (A/B knob)
+// 1: k_shadow visits the children of a node nearest-first.  Measured (profiles/r07/ab_s1.jsonl): k_shadow +19 % on the
+// console scene, +7 % on foliage, +10 % on city — the sorting network costs more than finding an occluder earlier
+// saves (most shadow rays of these scenes are unoccluded and visit every node on their way anyway).  Off.
+#define PTB_SHADOW_ORDERED 0
+#endif
+#ifndef PTB_SHADOW_NOPUSH
+#define PTB_SHADOW_NOPUSH 1  // 1: the last entered child becomes current without going through the stack
 #endif
 
 struct ShadowTrav {
@@ -241,11 +247,36 @@ struct ShadowTrav {
     if (t2 < CUDART_INF_F) stk[sp++] = r2;
     if (t1 < CUDART_INF_F) stk[sp++] = r1;
     if (t0 < CUDART_INF_F) stk[sp++] = r0;
-#else
+#elif !PTB_SHADOW_NOPUSH
     if (slab_fma(nd.lo_x.x, nd.lo_y.x, nd.lo_z.x, nd.hi_x.x, nd.hi_y.x, nd.hi_z.x, pre, no, t_max, ch.x) < CUDART_INF_F) stk[sp++] = ch.x;
     if (slab_fma(nd.lo_x.y, nd.lo_y.y, nd.lo_z.y, nd.hi_x.y, nd.hi_y.y, nd.hi_z.y, pre, no, t_max, ch.y) < CUDART_INF_F) stk[sp++] = ch.y;
     if (slab_fma(nd.lo_x.z, nd.lo_y.z, nd.lo_z.z, nd.hi_x.z, nd.hi_y.z, nd.hi_z.z, pre, no, t_max, ch.z) < CUDART_INF_F) stk[sp++] = ch.z;
     if (slab_fma(nd.lo_x.w, nd.lo_y.w, nd.lo_z.w, nd.hi_x.w, nd.hi_y.w, nd.hi_z.w, pre, no, t_max, ch.w) < CUDART_INF_F) stk[sp++] = ch.w;
+#else
+    // every child the ray enters is visited (in no particular order): the last one found becomes current directly,
+    // only the others go through the local-memory stack (one STL + one LDL fewer per node visit)
+    const bool h0 = slab_fma(nd.lo_x.x, nd.lo_y.x, nd.lo_z.x, nd.hi_x.x, nd.hi_y.x, nd.hi_z.x, pre, no, t_max, ch.x) < CUDART_INF_F;
+    const bool h1 = slab_fma(nd.lo_x.y, nd.lo_y.y, nd.lo_z.y, nd.hi_x.y, nd.hi_y.y, nd.hi_z.y, pre, no, t_max, ch.y) < CUDART_INF_F;
+    const bool h2 = slab_fma(nd.lo_x.z, nd.lo_y.z, nd.lo_z.z, nd.hi_x.z, nd.hi_y.z, nd.hi_z.z, pre, no, t_max, ch.z) < CUDART_INF_F;
+    const bool h3 = slab_fma(nd.lo_x.w, nd.lo_y.w, nd.lo_z.w, nd.hi_x.w, nd.hi_y.w, nd.hi_z.w, pre, no, t_max, ch.w) < CUDART_INF_F;
+    uint32_t nxt = DONE;
+    if (h0) nxt = ch.x;
+    if (h1) {
+      if (nxt != DONE) stk[sp++] = nxt;
+      nxt = ch.y;
+    }
+    if (h2) {
+      if (nxt != DONE) stk[sp++] = nxt;
+      nxt = ch.z;
+    }
+    if (h3) {
+      if (nxt != DONE) stk[sp++] = nxt;
+      nxt = ch.w;
+    }
+    if (nxt != DONE) {
+      cur = nxt;
+      return;
+    }
 #endif
     pop(stk);
   }
