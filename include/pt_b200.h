@@ -161,10 +161,12 @@ void pt_scene_destroy(pt_scene *scene);
  * value of $PT_B200_ACCEL = sah|lbvh|auto).  Replaces KDTree::build of the kdtree-ray crate (call sites
  * scene/internal/model.rs:96, scene/internal/mod.rs:42).  Either tree is a conservative candidate filter: traced
  * results are identical.  SAH: binned-SAH build on the host cores (best traversal speed).  LBVH: Morton-code radix
- * sort + Karras hierarchy on the GPU (fastest build, for large meshes).  AUTO: LBVH from 4 M primitives up. */
-enum { PT_ACCEL_SAH = 0, PT_ACCEL_LBVH = 1, PT_ACCEL_AUTO = 2 };
+ * sort + Karras hierarchy on the GPU (fastest build, for large meshes).  PLOC: the same Morton order, but the hierarchy
+ * is built bottom-up by merging mutual nearest neighbours (smallest surface area of the union) — SAH-like traversal
+ * speed at GPU build speed.  AUTO: a GPU builder from 4 M primitives up.  ($PT_B200_ACCEL = sah|lbvh|ploc|auto.) */
+enum { PT_ACCEL_SAH = 0, PT_ACCEL_LBVH = 1, PT_ACCEL_AUTO = 2, PT_ACCEL_PLOC = 3 };
 int pt_set_accel_builder(int accel);
-/* What the scene was built with: *accel = PT_ACCEL_SAH or PT_ACCEL_LBVH, *build_ms = acceleration-structure build
+/* What the scene was built with: *accel = PT_ACCEL_SAH, PT_ACCEL_LBVH or PT_ACCEL_PLOC, *build_ms = acceleration-structure build
  * time (host wall clock for SAH; device time for LBVH), *max_depth = levels of 4-wide nodes. */
 int pt_scene_accel_info(const pt_scene *scene, int *accel, double *build_ms, int *max_depth);
 /* Re-sends every device array of the scene (nodes, triangles, shading records, materials, texels, lights) from

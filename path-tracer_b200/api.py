@@ -98,14 +98,14 @@ def device_count():
     return lib().pt_device_count()
 
 
-ACCEL_SAH, ACCEL_LBVH, ACCEL_AUTO = 0, 1, 2
+ACCEL_SAH, ACCEL_LBVH, ACCEL_AUTO, ACCEL_PLOC = 0, 1, 2, 3
 
 
 def set_accel_builder(accel):
     """Acceleration-structure builder of the scenes created from now on: "sah" (host binned SAH, default), "lbvh"
-    (GPU Morton/radix-sort LBVH) or "auto".  Replaces KDTree::build (scene/internal/model.rs:96, internal/mod.rs:42)."""
+    (GPU Morton/radix-sort LBVH), "ploc" (GPU Morton order + nearest-neighbour agglomeration) or "auto".  Replaces KDTree::build (scene/internal/model.rs:96, internal/mod.rs:42)."""
     if isinstance(accel, str):
-        accel = {"sah": ACCEL_SAH, "lbvh": ACCEL_LBVH, "auto": ACCEL_AUTO}[accel]
+        accel = {"sah": ACCEL_SAH, "lbvh": ACCEL_LBVH, "auto": ACCEL_AUTO, "ploc": ACCEL_PLOC}[accel]
     _check(lib().pt_set_accel_builder(accel))
 
 
@@ -196,7 +196,7 @@ class Scene:
     def accel_info(self):
         a, ms, d = C.c_int(), C.c_double(), C.c_int()
         _check(lib().pt_scene_accel_info(self.h, C.byref(a), C.byref(ms), C.byref(d)))
-        return dict(accel=("sah", "lbvh")[a.value], build_ms=ms.value, max_depth=d.value)
+        return dict(accel={0: "sah", 1: "lbvh", 3: "ploc"}[a.value], build_ms=ms.value, max_depth=d.value)
 
     def save_binary(self, path, with_accel=True):
         """Write the scene as an isfb file (raw arrays, optionally with its BVH); Scene.load reads it back."""

@@ -14,12 +14,16 @@
 #include "traverse.cuh"
 
 #ifndef PTB_EXTEND_MINB
-#define PTB_EXTEND_MINB 7
+// 64 registers / 8 CTAs per SM (28 B spilled) since the alpha walk lost its restart state (round 2): k_extend -2.5 %
+// (console), -3 % (foliage) against 72 registers / 7 CTAs (profiles/r07/ab_s2.jsonl); in round 1 it was +-0
+#define PTB_EXTEND_MINB 8
 #endif
 #ifndef PTB_SHADE_MINB
-// 64 registers, 8 CTAs per SM (164 B spilled): k_shade is latency-bound on the chain hit -> shading record -> material
-// -> texel, so resident warps beat registers: 5 / 6 / 7 / 8 / 9 CTAs = +9 % / ref / -8 % / -11 % / -8 % (console)
-#define PTB_SHADE_MINB 8
+// Round 1 (IEEE shading arithmetic, 3 360 instructions): 64 registers / 8 CTAs per SM won (resident warps beat
+// registers: 5 / 6 / 7 / 8 / 9 CTAs = +9 % / ref / -8 % / -11 % / -8 % on console).  With PTB_SHADE_FAST the kernel is a
+// third shorter and the 140 B it spills at 64 registers dominate: 72 registers / 7 CTAs per SM is -36 % on console
+// (3.10 -> 1.99 ms per 16 spp), +-1 % on foliage and city (profiles/r07/ab_s2.jsonl).
+#define PTB_SHADE_MINB 7
 #endif
 #ifndef PTB_SHADOW_MINB
 // 90 -> 72 registers: k_shadow -2 % (console) ... -18 % (foliage); 72 -> 64 registers / 8 CTAs per SM (40 B spilled):
@@ -111,19 +115,58 @@ __global__ void __launch_bounds__(256) k_store_transmittance(WaveState W, uint32
 }
 
 // ------------------------------------------------------------------------------------------------
-// raygen: one thread per slot; writes queue buffer 0 in slot order (already compact).
+// raygen: one thread per queue position of buffer 0 (already compact).  PTB_TILE_RAYGEN: consecutive queue positions
+// walk 8x4 pixel tiles of one sample instead of image rows, so the 32 primary rays of a warp - and, because the queues
+// keep their order through k_hit_list / k_shade, the bounce-1 rays that start where those hit - cover a compact patch
+// of the image: fewer distinct BVH nodes and texels per warp.  Pixels outside the largest 8x4-aligned rectangle keep
+// row order.  The slot (pixel + sample * W*H) is what names the path, so results do not depend on this order.
+#ifndef PTB_TILE_RAYGEN
+#define PTB_TILE_RAYGEN 1
+#endif
+__device__ __forceinline__ uint32_t queue_to_slot(const WaveParams &P, uint32_t q) {
+#if PTB_TILE_RAYGEN
+  const uint32_t W = P.width, H = P.height, npix = W * H;
+  const uint32_t k = q / npix, p = q - k * npix;
+  const uint32_t W8 = W & ~7u, H4 = H & ~3u, n_main = W8 * H4;
+  uint32_t x, y;
+  if (p < n_main) {
+    const uint32_t tile = p >> 5, in = p & 31u, tiles_x = W8 >> 3;
+    const uint32_t ty = tile / tiles_x, tx = tile - ty * tiles_x;
+    x = tx * 8u + (in & 7u);
+    y = ty * 4u + (in >> 3);
+  } else {
+    uint32_t r = p - n_main;
+    const uint32_t ws = W - W8;  // right strip (ws columns x H4 rows), then the bottom rows
+    if (r < ws * H4) {
+      y = r / ws;
+      x = W8 + (r - y * ws);
+    } else {
+      r -= ws * H4;
+      y = r / W;
+      x = r - y * W;
+      y += H4;
+    }
+  }
+  return k * npix + y * W + x;
+#else
+  (void)P;
+  return q;
+#endif
+}
+
 __global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
                                                 WaveState W) {
-  uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
-  if (slot == 0) {
+  const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q == 0) {
     W.counters[CTR_QUEUE(0)] = P.n_paths;
     W.counters[CTR_WORK_EXTEND] = 0;
   }
-  if (slot >= P.n_paths) return;
+  if (q >= P.n_paths) return;
+  const uint32_t slot = queue_to_slot(P, q);
   Ray r = generate_ray(S, P, make_key(P, slot));
-  W.ray_o[0][slot] = make_float4(r.o.x, r.o.y, r.o.z, 0.f);
-  W.ray_d[0][slot] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float((int)slot));
-  W.thr[0][slot] = make_float4(1.f, 1.f, 1.f, 0.f);
+  W.ray_o[0][q] = make_float4(r.o.x, r.o.y, r.o.z, 0.f);
+  W.ray_d[0][q] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float((int)slot));
+  W.thr[0][q] = make_float4(1.f, 1.f, 1.f, 0.f);
   W.radiance[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 

@@ -412,6 +412,151 @@ __global__ void __launch_bounds__(256) k_fit(int n, const uint32_t *__restrict__
   }
 }
 
+// ---- 4b/5b. PLOC (Meister & Bittner 2018, "Parallel Locally-Ordered Clustering"): bottom-up agglomeration in Morton
+// order.  Every cluster looks for the neighbour within PLOC_R positions whose union with it has the smallest surface
+// area; mutual nearest neighbours merge; the survivors are compacted and the search repeats until one cluster is
+// left.  Unlike the radix tree, which splits where the Morton codes differ, the merges minimise the very quantity
+// the SAH measures, so the tree traces like a top-down SAH tree while the build stays a handful of streaming passes.
+// Output: the same arrays the radix-tree path produces (left / right / rlo / rhi / boxes, root = internal node 0, leaf
+// references = positions in a primitive order in which every subtree is contiguous), so collapse and leaf ordering
+// are shared.
+constexpr int PLOC_R = 16;
+constexpr uint32_t NONE32 = 0xFFFFFFFFu;
+
+__global__ void __launch_bounds__(256) k_ploc_init(uint32_t n, const uint32_t *__restrict__ sorted_prim,
+                                                   const float4 *__restrict__ blo, const float4 *__restrict__ bhi,
+                                                   uint32_t *__restrict__ cref, float4 *__restrict__ clo, float4 *__restrict__ chi) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t p = sorted_prim[i];
+  cref[i] = PRIM | i;
+  clo[i] = blo[p];
+  chi[i] = bhi[p];
+}
+
+__device__ __forceinline__ float union_half_area(float4 alo, float4 ahi, float4 blo, float4 bhi) {
+  const float dx = fmaxf(ahi.x, bhi.x) - fminf(alo.x, blo.x), dy = fmaxf(ahi.y, bhi.y) - fminf(alo.y, blo.y),
+              dz = fmaxf(ahi.z, bhi.z) - fminf(alo.z, blo.z);
+  return dx * dy + dy * dz + dz * dx;
+}
+
+// nearest neighbour of every cluster within +-PLOC_R positions (ties: the lower position)
+__global__ void __launch_bounds__(256) k_ploc_nn(uint32_t c, const float4 *__restrict__ clo, const float4 *__restrict__ chi,
+                                                 uint32_t *__restrict__ nn) {
+  __shared__ float4 slo[256 + 2 * PLOC_R], shi[256 + 2 * PLOC_R];
+  const int base = (int)(blockIdx.x * 256u) - PLOC_R;
+  for (int k = threadIdx.x; k < 256 + 2 * PLOC_R; k += 256) {
+    const int j = base + k;
+    if (j >= 0 && j < (int)c) {
+      slo[k] = clo[j];
+      shi[k] = chi[j];
+    }
+  }
+  __syncthreads();
+  const int i = (int)(blockIdx.x * 256u + threadIdx.x);
+  if (i >= (int)c) return;
+  const float4 mlo = slo[threadIdx.x + PLOC_R], mhi = shi[threadIdx.x + PLOC_R];
+  float best = CUDART_INF_F;
+  int bj = -1;
+  for (int d = -PLOC_R; d <= PLOC_R; ++d) {
+    const int j = i + d;
+    if (d == 0 || j < 0 || j >= (int)c) continue;
+    const float a = union_half_area(mlo, mhi, slo[threadIdx.x + PLOC_R + d], shi[threadIdx.x + PLOC_R + d]);
+    if (a < best || bj < 0) {  // bj < 0: NaN / inf areas still yield a neighbour
+      best = a;
+      bj = j;
+    }
+  }
+  nn[i] = (uint32_t)bj;
+}
+
+struct PlocTree {
+  uint32_t *left, *right, *cnt, *par_i, *par_p;  // par_*: parent internal node | side << 31
+  float4 *nlo, *nhi;
+  uint32_t n;  // primitives
+};
+__device__ __forceinline__ uint32_t ref_count(const PlocTree &T, uint32_t ref) { return (ref & PRIM) ? 1u : T.cnt[ref]; }
+
+// mutual nearest neighbours merge into a new internal node (the lower position keeps the merged cluster)
+__global__ void __launch_bounds__(256) k_ploc_merge(uint32_t c, uint32_t *__restrict__ cref, float4 *__restrict__ clo,
+                                                    float4 *__restrict__ chi, const uint32_t *__restrict__ nn, PlocTree T,
+                                                    uint32_t *__restrict__ merge_ctr, uint32_t *__restrict__ keep) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= c) return;
+  const uint32_t j = nn[i];
+  if (nn[j] != i) {
+    keep[i] = 1u;
+    return;
+  }
+  if (i > j) {
+    keep[i] = 0u;
+    return;
+  }
+  const uint32_t k = atomicAdd(merge_ctr, 1u);
+  const uint32_t idx = (T.n - 2u) - k;  // n - 1 merges in total: the last one is internal node 0, the root
+  const uint32_t a = cref[i], b = cref[j];
+  const float4 alo = clo[i], ahi = chi[i], blo_ = clo[j], bhi_ = chi[j];
+  const float4 lo = make_float4(fminf(alo.x, blo_.x), fminf(alo.y, blo_.y), fminf(alo.z, blo_.z), 0.f);
+  const float4 hi = make_float4(fmaxf(ahi.x, bhi_.x), fmaxf(ahi.y, bhi_.y), fmaxf(ahi.z, bhi_.z), 0.f);
+  T.left[idx] = a;
+  T.right[idx] = b;
+  T.nlo[idx] = lo;
+  T.nhi[idx] = hi;
+  T.cnt[idx] = ref_count(T, a) + ref_count(T, b);
+  if (a & PRIM) T.par_p[a & ~PRIM] = idx; else T.par_i[a] = idx;
+  if (b & PRIM) T.par_p[b & ~PRIM] = idx | 0x80000000u; else T.par_i[b] = idx | 0x80000000u;
+  cref[i] = idx;
+  clo[i] = lo;
+  chi[i] = hi;
+  keep[i] = 1u;
+}
+
+__global__ void __launch_bounds__(256) k_ploc_compact(uint32_t c, const uint32_t *__restrict__ keep,
+                                                      const uint32_t *__restrict__ pos, const uint32_t *__restrict__ cref,
+                                                      const float4 *__restrict__ clo, const float4 *__restrict__ chi,
+                                                      uint32_t *__restrict__ cref2, float4 *__restrict__ clo2,
+                                                      float4 *__restrict__ chi2) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= c || !keep[i]) return;
+  const uint32_t p = pos[i];
+  cref2[p] = cref[i];
+  clo2[p] = clo[i];
+  chi2[p] = chi[i];
+}
+
+// Depth-first position of a subtree's first primitive: the sizes of the left siblings on the way to the root.
+__device__ __forceinline__ uint32_t dfs_offset(const PlocTree &T, uint32_t parent) {
+  uint32_t off = 0;
+  while (parent != NONE32) {
+    const uint32_t idx = parent & 0x7FFFFFFFu;
+    if (parent & 0x80000000u) off += ref_count(T, T.left[idx]);
+    parent = T.par_i[idx];
+  }
+  return off;
+}
+__global__ void __launch_bounds__(256) k_ploc_leaf_pos(PlocTree T, const uint32_t *__restrict__ sorted_in,
+                                                       uint32_t *__restrict__ sorted_out, uint32_t *__restrict__ newpos) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= T.n) return;
+  const uint32_t off = dfs_offset(T, T.par_p[i]);
+  newpos[i] = off;
+  sorted_out[off] = sorted_in[i];
+}
+__global__ void __launch_bounds__(256) k_ploc_node_range(PlocTree T, uint32_t *__restrict__ rlo, uint32_t *__restrict__ rhi) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i + 1 >= T.n) return;
+  const uint32_t off = dfs_offset(T, T.par_i[i]);
+  rlo[i] = off;
+  rhi[i] = off + T.cnt[i] - 1u;
+}
+__global__ void __launch_bounds__(256) k_ploc_fix_refs(PlocTree T, const uint32_t *__restrict__ newpos) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i + 1 >= T.n) return;
+  const uint32_t l = T.left[i], r = T.right[i];
+  if (l & PRIM) T.left[i] = PRIM | newpos[l & ~PRIM];
+  if (r & PRIM) T.right[i] = PRIM | newpos[r & ~PRIM];
+}
+
 // ---- 6. collapse to 4-wide nodes, one tree level per launch ----
 struct CollapseArgs {
   const uint32_t *left, *right, *rlo, *rhi;
@@ -531,8 +676,9 @@ __global__ void __launch_bounds__(256) k_leaf_order(uint32_t n, uint32_t nt, con
 
 // Builds `out` for scene `s` on the current CUDA device.  Returns PT_OK, or PT_ERR_INVALID with *too_deep = 1 when the
 // radix tree is deeper than the traversal stack allows (the caller then falls back to the host SAH build).
-int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_deep) {
+int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_deep, int method) {
   if (too_deep) *too_deep = 0;
+  const bool ploc = method == 1;
   const uint32_t nt = (uint32_t)s.n_tris(), ns = (uint32_t)s.sphere_models.size(), n = nt + ns;
   if (n < 16) {
     set_error("LBVH build needs at least 16 primitives");
@@ -547,6 +693,9 @@ int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_dee
   uint32_t *par_p = nullptr, *visits = nullptr, *tri_rank = nullptr, *leaf_tris = nullptr, *ctr = nullptr;
   uint2 *work[2] = {nullptr, nullptr};
   Bvh4Node *nodes = nullptr;
+  // PLOC only: cluster arrays (ping-pong), nearest neighbours, keep flags / positions, subtree sizes, new leaf positions
+  uint32_t *cref[2] = {nullptr, nullptr}, *nn = nullptr, *keep = nullptr, *kpos = nullptr, *cnt = nullptr, *newpos = nullptr;
+  float4 *clo[2] = {nullptr, nullptr}, *chi[2] = {nullptr, nullptr};
   const uint32_t rs_blocks = (n + RS_TILE - 1) / RS_TILE;
   const uint32_t node_cap = n;  // every 4-wide node has >= 2 children, so there are fewer nodes than leaves
   LB_TRY(B.alloc(&d_pos, (size_t)nt * 9));
@@ -575,6 +724,18 @@ int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_dee
   LB_TRY(B.alloc(&work[0], n));
   LB_TRY(B.alloc(&work[1], n));
   LB_TRY(B.alloc(&nodes, node_cap));
+  if (ploc) {
+    for (int k = 0; k < 2; ++k) {
+      LB_TRY(B.alloc(&cref[k], n));
+      LB_TRY(B.alloc(&clo[k], n));
+      LB_TRY(B.alloc(&chi[k], n));
+    }
+    LB_TRY(B.alloc(&nn, n));
+    LB_TRY(B.alloc(&keep, (size_t)n + 1));
+    LB_TRY(B.alloc(&kpos, (size_t)n + 1));
+    LB_TRY(B.alloc(&cnt, n));
+    LB_TRY(B.alloc(&newpos, n));
+  }
   LB_TRY(cudaMemcpyAsync(d_pos, s.pos.data(), (size_t)nt * 9 * sizeof(float), cudaMemcpyHostToDevice, st));
   if (ns) {
     std::vector<float4> sph(ns);
@@ -599,17 +760,54 @@ int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_dee
   k_pad_boxes<<<g256, 256, 0, st>>>(d_pos, nt, d_sph, ns, blo, bhi, cb, cam);  // symmetric: centroids unchanged
   int rc = radix_sort_pairs(keys, vals, keys2, vals2, n, 32, counts, scan_tmp, st);
   if (rc) return rc;
+  uint32_t *sorted = vals;  // sorted position -> primitive
+  if (ploc) {
+    PlocTree T{left, right, cnt, par_i, par_p, nlo, nhi, n};
+    LB_TRY(cudaMemsetAsync(par_i, 0xFF, (size_t)n * sizeof(uint32_t), st));
+    LB_TRY(cudaMemsetAsync(par_p, 0xFF, (size_t)n * sizeof(uint32_t), st));
+    LB_TRY(cudaMemsetAsync(ctr + 2, 0, sizeof(uint32_t), st));  // merge counter
+    k_ploc_init<<<g256, 256, 0, st>>>(n, vals, blo, bhi, cref[0], clo[0], chi[0]);
+    uint32_t c = n;
+    int iters = 0;
+    while (c > 1) {
+      if (++iters > 512) {  // every pass merges at least the globally closest pair; hundreds of passes mean a degenerate input
+        if (too_deep) *too_deep = 1;
+        set_error("PLOC did not converge");
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        return PT_ERR_INVALID;
+      }
+      const uint32_t gc = (c + 255) / 256;
+      k_ploc_nn<<<gc, 256, 0, st>>>(c, clo[0], chi[0], nn);
+      k_ploc_merge<<<gc, 256, 0, st>>>(c, cref[0], clo[0], chi[0], nn, T, ctr + 2, keep);
+      LB_TRY(cudaMemsetAsync(keep + c, 0, sizeof(uint32_t), st));
+      if ((rc = exclusive_scan_u32(keep, kpos, c + 1, scan_tmp, st))) return rc;
+      k_ploc_compact<<<gc, 256, 0, st>>>(c, keep, kpos, cref[0], clo[0], chi[0], cref[1], clo[1], chi[1]);
+      LB_TRY(cudaMemcpyAsync(&c, kpos + c, sizeof c, cudaMemcpyDeviceToHost, st));
+      LB_TRY(cudaStreamSynchronize(st));
+      std::swap(cref[0], cref[1]);
+      std::swap(clo[0], clo[1]);
+      std::swap(chi[0], chi[1]);
+    }
+    // depth-first primitive order (every subtree contiguous), node ranges, leaf references in the new order
+    k_ploc_leaf_pos<<<g256, 256, 0, st>>>(T, vals, vals2, newpos);
+    k_ploc_node_range<<<g256, 256, 0, st>>>(T, rlo, rhi);
+    k_ploc_fix_refs<<<g256, 256, 0, st>>>(T, newpos);
+    sorted = vals2;
+  }
   // triangle ranks in sorted order (n + 1 entries: the last one is the triangle count)
-  k_leaf_order<<<g256, 256, 0, st>>>(n, nt, vals, nullptr, nullptr, tri_rank);
+  k_leaf_order<<<g256, 256, 0, st>>>(n, nt, sorted, nullptr, nullptr, tri_rank);
   LB_TRY(cudaMemsetAsync(tri_rank + n, 0, sizeof(uint32_t), st));
   if ((rc = exclusive_scan_u32(tri_rank, tri_rank, n + 1, scan_tmp, st))) return rc;
-  k_leaf_order<<<g256, 256, 0, st>>>(n, nt, vals, tri_rank, leaf_tris, nullptr);
-  k_radix_tree<<<g256, 256, 0, st>>>(keys, (int)n, left, right, rlo, rhi, par_i, par_p);
-  LB_TRY(cudaMemsetAsync(visits, 0, (size_t)n * sizeof(uint32_t), st));
-  k_fit<<<g256, 256, 0, st>>>((int)n, vals, blo, bhi, left, right, par_i, par_p, nlo, nhi, visits);
+  k_leaf_order<<<g256, 256, 0, st>>>(n, nt, sorted, tri_rank, leaf_tris, nullptr);
+  if (!ploc) {
+    k_radix_tree<<<g256, 256, 0, st>>>(keys, (int)n, left, right, rlo, rhi, par_i, par_p);
+    LB_TRY(cudaMemsetAsync(visits, 0, (size_t)n * sizeof(uint32_t), st));
+    k_fit<<<g256, 256, 0, st>>>((int)n, vals, blo, bhi, left, right, par_i, par_p, nlo, nhi, visits);
+  }
   LB_TRY(cudaGetLastError());
   // level-by-level collapse; the root of the radix tree (internal node 0) becomes 4-wide node 0
-  CollapseArgs A{left, right, rlo, rhi, nlo, nhi, blo, bhi, vals, tri_rank, nt, bvh_max_leaf_tris(), nodes, ctr, node_cap, cb, cam};
+  CollapseArgs A{left, right, rlo, rhi, nlo, nhi, blo, bhi, sorted, tri_rank, nt, bvh_max_leaf_tris(), nodes, ctr, node_cap, cb, cam};
   const uint32_t one = 1;
   LB_TRY(cudaMemcpyAsync(ctr, &one, sizeof one, cudaMemcpyHostToDevice, st));  // node_count = 1 (the root)
   const uint2 root_item = make_uint2(0u, 0u);

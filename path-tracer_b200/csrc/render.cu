@@ -121,6 +121,7 @@ int accel_choice() {
   if (g_accel >= 0) return g_accel;
   if (const char *e = std::getenv("PT_B200_ACCEL")) {
     if (!std::strcmp(e, "lbvh")) return PT_ACCEL_LBVH;
+    if (!std::strcmp(e, "ploc")) return PT_ACCEL_PLOC;
     if (!std::strcmp(e, "auto")) return PT_ACCEL_AUTO;
   }
   return PT_ACCEL_SAH;
@@ -135,13 +136,13 @@ int build_device_scene(pt_scene *sc) {
   if (n_prims_geom < 16) accel = PT_ACCEL_SAH;  // the LBVH root must not be a single leaf (leaves hold <= 8 triangles)
   bool built = sc->accel_preloaded;
   if (!built) sc->accel = PT_ACCEL_SAH;
-  if (!built && accel == PT_ACCEL_LBVH) {
+  if (!built && (accel == PT_ACCEL_LBVH || accel == PT_ACCEL_PLOC)) {
     float ms = 0;
     int too_deep = 0;
-    int rc = build_bvh4_lbvh(h, sc->bvh, &ms, &too_deep);
+    int rc = build_bvh4_lbvh(h, sc->bvh, &ms, &too_deep, accel == PT_ACCEL_PLOC ? 1 : 0);
     if (rc == PT_OK) {
       built = true;
-      sc->accel = PT_ACCEL_LBVH;
+      sc->accel = accel;
       sc->build_ms = ms;
     } else if (!too_deep) {
       return rc;
@@ -370,7 +371,7 @@ int scene_from_host(HostScene &&host, int device, pt_scene **out, Bvh4 *accel, i
   auto adopt = [&](pt_scene *sc) {
     if (accel && accel_kind >= 0) {
       sc->bvh = std::move(*accel);
-      sc->accel = accel_kind == PT_ACCEL_LBVH ? PT_ACCEL_LBVH : PT_ACCEL_SAH;
+      sc->accel = accel_kind == PT_ACCEL_LBVH || accel_kind == PT_ACCEL_PLOC ? accel_kind : PT_ACCEL_SAH;
       sc->accel_preloaded = true;
     }
   };
@@ -481,7 +482,7 @@ int pt_scene_get_desc(const pt_scene *sc, pt_scene_desc *out) {
 }
 
 int pt_set_accel_builder(int accel) {
-  if (accel < PT_ACCEL_SAH || accel > PT_ACCEL_AUTO) {
+  if (accel < PT_ACCEL_SAH || accel > PT_ACCEL_PLOC) {
     set_error("unknown acceleration-structure builder %d", accel);
     return PT_ERR_INVALID;
   }

@@ -137,7 +137,9 @@ uint32_t bvh_max_leaf_tris();
 // GPU LBVH build (lbvh.cu) on the current CUDA device: Morton codes + radix sort + Karras hierarchy + bottom-up fit,
 // collapsed to the same 4-wide nodes.  *build_ms = device time of the build (CUDA events, upload excluded).
 // Returns PT_ERR_INVALID with *too_deep = 1 when the tree exceeds the traversal stack (caller falls back to SAH).
-int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_deep);
+// method 0: Karras radix tree over the Morton order (LBVH).  method 1: PLOC — mutual-nearest-neighbour agglomeration
+// in Morton order, minimising the surface area of every merge: SAH-like trees at GPU build speed.
+int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_deep, int method = 0);
 
 // Revision of the box-inflation / node-layout rules both builders follow; an isfb accel section written under another
 // revision is ignored on load (isf_binary.cpp).

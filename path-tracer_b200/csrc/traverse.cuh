@@ -186,7 +186,10 @@ struct ClosestTrav {
 #define PTB_SHADOW_ORDERED 0
 #endif
 #ifndef PTB_SHADOW_NOPUSH
-#define PTB_SHADOW_NOPUSH 1  // 1: the last entered child becomes current without going through the stack
+// 1: the last entered child becomes current without going through the stack (one STL + one LDL fewer per node visit).
+// Measured (profiles/r07/ab_s2.jsonl): k_shadow +7 % on console, +5 % on foliage, +5 % on city - the extra live
+// register costs 22 B more spills at 64 registers than the stack round trip it saves.  Off.
+#define PTB_SHADOW_NOPUSH 0
 #endif
 
 struct ShadowTrav {

@@ -129,6 +129,7 @@ def test_png_roundtrip(tmp_path):
 
 def test_accel_builder_selection_host_only():
     pt.set_accel_builder("lbvh")
+    pt.set_accel_builder("ploc")
     pt.set_accel_builder("auto")
     pt.set_accel_builder("sah")
     with pytest.raises(pt.PtError):

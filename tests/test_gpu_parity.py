@@ -674,11 +674,11 @@ def test_cli_viewer_snapshots(tmp_path):
     assert np.array_equal(pt.read_png(str(a)), pt.read_png(str(b)))
 
 
-# ---------------------------------------------------------------- GPU LBVH builder (replaces KDTree::build)
-@pytest.fixture()
-def lbvh_builder():
-    pt.set_accel_builder("lbvh")
-    yield
+# ---------------------------------------------------------------- GPU builders: LBVH and PLOC (replace KDTree::build)
+@pytest.fixture(params=["lbvh", "ploc"])
+def lbvh_builder(request):
+    pt.set_accel_builder(request.param)
+    yield request.param
     pt.set_accel_builder("sah")
 
 
@@ -687,8 +687,8 @@ def test_lbvh_closest_hit_matches_oracle(loaded, lbvh_builder, name):
     sa, osc, sah_scene = loaded[name]
     sc = pt.Scene.load(scene_path(name))
     info = sc.accel_info()
-    if sc.info()["n_prims"] >= 8:
-        assert info["accel"] == "lbvh" and info["max_depth"] >= 1
+    if sc.info()["n_prims"] >= 16:
+        assert info["accel"] == lbvh_builder and info["max_depth"] >= 1
     rr = R.random_rays(sa, 1 << 18, seed=11)
     got = sc.trace_closest(rr)
     assert np.array_equal(got, sah_scene.trace_closest(rr))  # the tree is a filter: identical records
@@ -698,7 +698,7 @@ def test_lbvh_closest_hit_matches_oracle(loaded, lbvh_builder, name):
 
 def test_lbvh_soup_brute_force_and_render(lbvh_builder):
     sc = pt.Scene.synthetic("soup", 100000, seed=9)
-    assert sc.accel_info()["accel"] == "lbvh"
+    assert sc.accel_info()["accel"] == lbvh_builder
     sa = sc.arrays()
     osc = oracle_lib.OracleScene(sa)
     rr = R.random_rays(sa, 1 << 14, seed=4)
@@ -720,7 +720,7 @@ def test_lbvh_large_scene_properties(lbvh_builder):
     triangle's centroid reports a hit no farther than that triangle) and the build is deterministic in its results."""
     sc = pt.Scene.synthetic("city", 2000000, seed=5)
     info = sc.accel_info()
-    assert info["accel"] == "lbvh" and info["max_depth"] * 3 + 4 <= 96
+    assert info["accel"] == lbvh_builder and info["max_depth"] * 3 + 4 <= 96
     sa = sc.arrays()
     rng = np.random.default_rng(0)
     pick = rng.integers(0, len(sa.tri_pos), 200000)
@@ -824,7 +824,7 @@ def test_full_size_console_properties():
 
 
 # ---------------------------------------------------------------- box margins: rays that graze triangle edges
-@pytest.mark.parametrize("accel", ["sah", "lbvh"])
+@pytest.mark.parametrize("accel", ["sah", "lbvh", "ploc"])
 def test_edge_grazing_rays_match_brute_force(accel):
     sa, targets, cam, rng = R.edge_grazing_scene()
     rays = R.edge_grazing_rays(targets, cam, rng, 1 << 17)

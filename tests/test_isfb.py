@@ -195,17 +195,18 @@ def test_isfb_scene_traces_like_json_scene(tmp_path, scene):
 
 
 @pytest.mark.gpu
-def test_isfb_keeps_an_lbvh_tree(tmp_path):
-    pt.set_accel_builder("lbvh")
+@pytest.mark.parametrize("builder", ["lbvh", "ploc"])
+def test_isfb_keeps_an_lbvh_tree(tmp_path, builder):
+    pt.set_accel_builder(builder)
     try:
         a = pt.Scene.synthetic("console", 60000, seed=3)
     finally:
         pt.set_accel_builder("sah")
-    assert a.accel_info()["accel"] == "lbvh"
+    assert a.accel_info()["accel"] == builder
     out = str(tmp_path / "console.isfb")
     a.save_binary(out)
     b = pt.Scene.load(out)
-    assert b.accel_info()["accel"] == "lbvh" and b.accel_info()["build_ms"] == 0.0
+    assert b.accel_info()["accel"] == builder and b.accel_info()["build_ms"] == 0.0
     assert b.accel_info()["max_depth"] == a.accel_info()["max_depth"]
     prof = pt.Profile(width=128, height=72, samples=2, bounces=3)
     assert np.array_equal(pt.Renderer(profile=prof).render(a), pt.Renderer(profile=prof).render(b))

@@ -10,6 +10,7 @@ name = sys.argv[1] if len(sys.argv) > 1 else "console_1080p_128spp_5b"
 recipe, n_tris, seed, w, h, spp, bounces, tm = bench.WORKLOADS[name]
 spp = int(sys.argv[2]) if len(sys.argv) > 2 else 16
 sc = pkg.Scene.synthetic(recipe, n_tris, seed)
+print(json.dumps(dict(workload=name, accel=sc.accel_info(), nodes=sc.info()["n_nodes"])), flush=True)
 prof = pkg.Profile(width=w, height=h, samples=spp, bounces=bounces, tonemap=tm)
 acc = torch.zeros(h, w, 3, device="cuda")
 for timing in (False, True):
