@@ -396,6 +396,39 @@ __device__ __forceinline__ void warp_append2(uint32_t *pair, bool want_path, boo
   pos_shadow = (uint32_t)(base >> 32) + (uint32_t)__popc(ms & lanemask_lt());
 }
 
+// The same reservation for a whole CTA: the warps add their counts into shared memory and ONE thread issues the
+// global atomic.  Every warp of every resident CTA reserving on its own is one atomic per 32 shaded paths on a
+// single 64-bit word; those serialise in the L2 slice that owns the word, and k_shade at bounce 0 (all lanes alive,
+// every warp arriving at the atomic at the same rate) ran at exactly that rate: 1.1 ns per reservation, or 2.1 ns
+// when the word happened to live in a slow slice - the address, hence the wave size and the GPU, decided whether
+// the kernel took 2.8 or 5.4 ms (profiles/r07/counter_address_s6d.txt).  Four times fewer atomics put the
+// reservation rate below the kernel's memory time again.  Must be called by all threads of the CTA.
+#ifndef PTB_SHADE_CTA_APPEND
+#define PTB_SHADE_CTA_APPEND 1
+#endif
+struct CtaAppend {  // shared-memory scratch of cta_append2, double-buffered by call parity (two barriers per call)
+  unsigned long long cnt[2][4], base[2];
+};
+__device__ __forceinline__ void cta_append2(uint32_t *pair, bool want_path, bool want_shadow, uint32_t &pos_path,
+                                            uint32_t &pos_shadow, CtaAppend &sh, uint32_t &call) {
+  const uint32_t mp = __ballot_sync(0xffffffffu, want_path), ms = __ballot_sync(0xffffffffu, want_shadow);
+  const uint32_t par = call++ & 1u, w = threadIdx.x >> 5;
+  if (lane_id() == 0) sh.cnt[par][w] = (unsigned long long)__popc(mp) | ((unsigned long long)__popc(ms) << 32);
+  __syncthreads();
+  unsigned long long off = 0ull, total = 0ull;
+#pragma unroll
+  for (uint32_t j = 0; j < 4; ++j) {
+    const unsigned long long c = sh.cnt[par][j];
+    if (j < w) off += c;
+    total += c;
+  }
+  if (threadIdx.x == 0) sh.base[par] = total ? atomicAdd(reinterpret_cast<unsigned long long *>(pair), total) : 0ull;
+  __syncthreads();
+  const unsigned long long base = sh.base[par] + off;
+  pos_path = (uint32_t)base + (uint32_t)__popc(mp & lanemask_lt());
+  pos_shadow = (uint32_t)(base >> 32) + (uint32_t)__popc(ms & lanemask_lt());
+}
+
 // PTB_HIT_LIST (on: console frame -5.9 %, foliage -0.3 ... -1.2 %, profiles/r06/ab_hitlist.jsonl): a scan pass between
 // k_extend and k_shade lists the queue positions that hit something, in queue order up to 256-position chunks, so
 // that every k_shade warp runs with 32 paths to shade instead of hits interleaved with misses (15 / 12 of 32 lanes
@@ -464,7 +497,18 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
   }
   uint32_t *pair = &W.counters[CTR_QUEUE(outb)];
   const uint32_t warps = gridDim.x * (blockDim.x >> 5), warp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+#if PTB_SHADE_CTA_APPEND
+  __shared__ CtaAppend s_app;
+  uint32_t app_call = 0;
+  // every warp runs the same number of rounds (the CTA synchronises inside cta_append2); warps past the end idle
+  const uint32_t rounds = (n + warps * 32u - 1u) / (warps * 32u);
+  for (uint32_t round = 0; round < rounds; ++round) {
+    const uint32_t base = (round * warps + warp) * 32u;
+#define PTB_APPEND2(a, b, c, d) cta_append2(pair, a, b, c, d, s_app, app_call)
+#else
   for (uint32_t base = warp * 32u; base < n; base += warps * 32u) {
+#define PTB_APPEND2(a, b, c, d) warp_append2(pair, a, b, c, d)
+#endif
 #if PTB_HIT_LIST
     const bool active = base + lane_id() < n;
     uint32_t q = 0;
@@ -497,7 +541,7 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
       if (ctx.lit) want = light_request(S, ctx, thr, li, so, sd, c, limit);
       if (li + 1 == nl) break;
       uint32_t pp, ps;
-      warp_append2(pair, false, want, pp, ps);
+      PTB_APPEND2(false, want, pp, ps);
       if (want && ps >= W.shadow_capacity) atomicAdd(&W.counters[CTR_DROPPED], 1u);
       if (want && ps < W.shadow_capacity) {
         st_wave(&W.sh_o[ps], make_float4(so.x, so.y, so.z, limit));
@@ -512,7 +556,7 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
     bool alive = false;
     if (active) alive = shade_finish(P, make_key(P, slot), bounce, ctx, thr, next);
     uint32_t pp, ps;
-    warp_append2(pair, alive, want, pp, ps);
+    PTB_APPEND2(alive, want, pp, ps);
     if (want && ps >= W.shadow_capacity) atomicAdd(&W.counters[CTR_DROPPED], 1u);
     if (want && ps < W.shadow_capacity) {
       st_wave(&W.sh_o[ps], make_float4(so.x, so.y, so.z, limit));
@@ -526,6 +570,7 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
       st_wave(&W.thr[outb][pp], make_float4(thr.x, thr.y, thr.z, 0.f));
     }
   }
+#undef PTB_APPEND2
 }
 
 // One thread follows one whole path (render_pixel, mod.rs:172-228) and records every bounce: the per-vertex

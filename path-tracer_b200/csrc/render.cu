@@ -255,14 +255,9 @@ void free_wave(pt_scene *sc) {
   sc->wave = WaveState{};
 }
 
-template <typename T>
-int wave_alloc(pt_scene *sc, T **out, size_t count) {
-  void *p = nullptr;
-  CUDA_TRY(cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T)));
-  sc->wave_allocs.push_back(p);
-  *out = reinterpret_cast<T *>(p);
-  return PT_OK;
-}
+// The wave state lives in ONE device allocation carved into its arrays (2 MiB-aligned pieces), counters first.
+constexpr size_t WAVE_ALIGN = (size_t)2 << 20;
+size_t wave_piece(size_t count, size_t elem) { return (std::max<size_t>(count, 1) * elem + WAVE_ALIGN - 1) & ~(WAVE_ALIGN - 1); }
 
 int ensure_wave(pt_scene *sc, uint32_t n_paths) {
   // queue positions are 32-bit and the shadow queue holds up to n_lights entries per path
@@ -275,20 +270,39 @@ int ensure_wave(pt_scene *sc, uint32_t n_paths) {
   const uint32_t shadow_cap = (uint32_t)shadow_cap64;
   if (sc->wave.capacity >= n_paths && sc->wave.shadow_capacity >= shadow_cap) return PT_OK;
   free_wave(sc);
-  WaveState &W = sc->wave;
-  int rc;
-  for (int b = 0; b < 2; ++b) {
-    if ((rc = wave_alloc(sc, &W.ray_o[b], n_paths))) return rc;
-    if ((rc = wave_alloc(sc, &W.ray_d[b], n_paths))) return rc;
-    if ((rc = wave_alloc(sc, &W.thr[b], n_paths))) return rc;
+  const size_t bytes = wave_piece(CTR_COUNT, sizeof(uint32_t)) + 8 * wave_piece(n_paths, sizeof(float4)) +
+                       4 * wave_piece(shadow_cap, sizeof(float4));
+  void *mem = nullptr;
+  if (cudaMalloc(&mem, bytes) != cudaSuccess) {
+    cudaGetLastError();
+    set_error("out of device memory: %.1f GB of wave state for %u paths", bytes / 1e9, n_paths);
+    return PT_ERR_NOMEM;
   }
-  if ((rc = wave_alloc(sc, &W.hit, n_paths))) return rc;
-  if ((rc = wave_alloc(sc, &W.radiance, n_paths))) return rc;
-  if ((rc = wave_alloc(sc, &W.sh_o, shadow_cap))) return rc;
-  if ((rc = wave_alloc(sc, &W.sh_d, shadow_cap))) return rc;
-  if ((rc = wave_alloc(sc, &W.sh_c, shadow_cap))) return rc;
-  if ((rc = wave_alloc(sc, &W.sh_p, shadow_cap))) return rc;
-  if ((rc = wave_alloc(sc, &W.counters, (size_t)CTR_COUNT))) return rc;
+  sc->wave_allocs.push_back(mem);
+  char *base = static_cast<char *>(mem);
+  size_t off = 0;
+  auto take = [&](size_t count, size_t elem) {
+    char *p = base + off;
+    off += wave_piece(count, elem);
+    return p;
+  };
+  WaveState &W = sc->wave;
+  // $PT_B200_CTR_OFFSET moves the counters inside their 2 MiB piece: the A/B knob behind the note at cta_append2
+  // (kernels.cu) - which L2 slice owns the queue counters decided k_shade's speed while every warp reserved on its own
+  size_t ctr_off = 0;
+  if (const char *e = std::getenv("PT_B200_CTR_OFFSET")) ctr_off = ((size_t)std::strtoull(e, nullptr, 0) & ~(size_t)255) % (WAVE_ALIGN - 4096);
+  W.counters = reinterpret_cast<uint32_t *>(take(CTR_COUNT, sizeof(uint32_t)) + ctr_off);
+  for (int b = 0; b < 2; ++b) {
+    W.ray_o[b] = reinterpret_cast<float4 *>(take(n_paths, sizeof(float4)));
+    W.ray_d[b] = reinterpret_cast<float4 *>(take(n_paths, sizeof(float4)));
+    W.thr[b] = reinterpret_cast<float4 *>(take(n_paths, sizeof(float4)));
+  }
+  W.hit = reinterpret_cast<float4 *>(take(n_paths, sizeof(float4)));
+  W.radiance = reinterpret_cast<float4 *>(take(n_paths, sizeof(float4)));
+  W.sh_o = reinterpret_cast<float4 *>(take(shadow_cap, sizeof(float4)));
+  W.sh_d = reinterpret_cast<float4 *>(take(shadow_cap, sizeof(float4)));
+  W.sh_c = reinterpret_cast<float4 *>(take(shadow_cap, sizeof(float4)));
+  W.sh_p = reinterpret_cast<float4 *>(take(shadow_cap, sizeof(float4)));
   W.capacity = n_paths;
   W.shadow_capacity = shadow_cap;
   return PT_OK;
@@ -841,6 +855,7 @@ int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t
       launch_extend(sc->dev, P, W, b, sc->dev.any_alpha != 0, nullptr, st);
       mark(0);
       launch_hit_list(sc->dev, W, b, st);
+      mark(4);  // the scan pass: reported with the shade class, listed on its own by $PT_B200_DUMP_MARKS
       if (shadow_pending) {  // k_shade refills the shadow queue the previous bounce's k_shadow reads
         CUDA_TRY(cudaStreamWaitEvent(st, sc->ev_shadow, 0));
         shadow_pending = false;
@@ -895,12 +910,16 @@ int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t
     stats_out->shade_launches = n_shade;
     stats_out->shadow_launches = n_shadow;
     if (timing) {
-      float acc[4] = {0, 0, 0, 0};
+      float acc[5] = {0, 0, 0, 0, 0};
+      const bool dump = std::getenv("PT_B200_DUMP_MARKS") != nullptr;
+      static const char *cls[5] = {"extend", "shade", "shadow", "other", "hit_list"};
       for (size_t i = 1; i < marks.size(); ++i) {
         float ms = 0;
         cudaEventElapsedTime(&ms, sc->events[i - 1], sc->events[i]);
         acc[marks[i]] += ms;
+        if (dump) std::fprintf(stderr, "mark %zu %s %.4f ms\n", i, cls[marks[i]], ms);
       }
+      acc[1] += acc[4];
       stats_out->ms_extend = acc[0];
       stats_out->ms_shade = acc[1];
       stats_out->ms_shadow = acc[2];
