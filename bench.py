@@ -36,9 +36,9 @@ WORKLOADS = {
 }
 DEFAULT_WORKLOAD = "console_1080p_128spp_5b"
 SUB_WORKLOADS = ["foliage_1080p_256spp_4b", "city_4k_1024spp_8b"]  # BASELINE.json configs[3], configs[4]
-# acceleration-structure builder per workload: the 20 M-triangle city is built on the GPU (LBVH, ~10 ms, traces as fast
-# as the host SAH tree, profiles/r03) so that N ranks do not run N host SAH builds of 6 s each side by side
-ACCEL = {"city_4k_1024spp_8b": "lbvh"}
+# acceleration-structure builder per workload: the 20 M-triangle city is built on the GPU (PLOC: 20 ms instead of 6 s of
+# host SAH build per rank, and the tree traces 15 % faster than the SAH one on this scene, profiles/r07/builders_s7.jsonl)
+ACCEL = {"city_4k_1024spp_8b": "ploc"}
 CANON_FILE = os.path.join(ROOT, "profiles", "canonical_counts.json")
 NCU_FILE = os.path.join(ROOT, "profiles", "ncu_traffic.json")
 

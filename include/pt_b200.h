@@ -163,7 +163,7 @@ void pt_scene_destroy(pt_scene *scene);
  * results are identical.  SAH: binned-SAH build on the host cores (best traversal speed).  LBVH: Morton-code radix
  * sort + Karras hierarchy on the GPU (fastest build, for large meshes).  PLOC: the same Morton order, but the hierarchy
  * is built bottom-up by merging mutual nearest neighbours (smallest surface area of the union) — SAH-like traversal
- * speed at GPU build speed.  AUTO: a GPU builder from 4 M primitives up.  ($PT_B200_ACCEL = sah|lbvh|ploc|auto.) */
+ * speed at GPU build speed.  AUTO: PLOC from 4 M primitives up, SAH below.  ($PT_B200_ACCEL = sah|lbvh|ploc|auto.) */
 enum { PT_ACCEL_SAH = 0, PT_ACCEL_LBVH = 1, PT_ACCEL_AUTO = 2, PT_ACCEL_PLOC = 3 };
 int pt_set_accel_builder(int accel);
 /* What the scene was built with: *accel = PT_ACCEL_SAH, PT_ACCEL_LBVH or PT_ACCEL_PLOC, *build_ms = acceleration-structure build

@@ -87,11 +87,15 @@ constexpr int32_t HIT_INDEX_MASK = 0x3FFFFFFF;
 
 // One wave of paths, SoA.  Queue position q (compacted every bounce) owns ray/throughput;
 // `slot` = pixel + k*W*H (k-th sample of the wave) owns the radiance sum and the RNG key.
+// The bounce-0 queue of a render is IMPLICIT: position q holds the primary ray of slot queue_to_slot(q) with
+// throughput 1, and k_extend / k_hit_list / k_shade regenerate it from q (ten Philox rounds and a camera transform)
+// instead of reading 48 bytes that a raygen pass would have had to write first.
 struct WaveState {
   float4 *ray_o[2];   // xyz origin
   float4 *ray_d[2];   // xyz direction, w = slot (int bits)
   float4 *thr[2];     // xyz throughput
   float4 *hit;        // (dist, u, v, HitRec.idx bits; idx < 0 = miss)
+  uint32_t *hit_list; // queue positions that hit something, in queue order (k_hit_list -> k_shade)
   float4 *radiance;   // per slot: xyz sum of this path's contributions (zeroed by raygen, atomically added to)
   // shadow queue (one entry per light per shaded hit with a non-zero unshadowed contribution)
   float4 *sh_o;       // xyz origin, w = point-light distance (or -1 for directional)

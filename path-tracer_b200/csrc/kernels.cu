@@ -115,11 +115,12 @@ __global__ void __launch_bounds__(256) k_store_transmittance(WaveState W, uint32
 }
 
 // ------------------------------------------------------------------------------------------------
-// raygen: one thread per queue position of buffer 0 (already compact).  PTB_TILE_RAYGEN: consecutive queue positions
-// walk 8x4 pixel tiles of one sample instead of image rows, so the 32 primary rays of a warp - and, because the queues
-// keep their order through k_hit_list / k_shade, the bounce-1 rays that start where those hit - cover a compact patch
-// of the image: fewer distinct BVH nodes and texels per warp.  Pixels outside the largest 8x4-aligned rectangle keep
-// row order.  The slot (pixel + sample * W*H) is what names the path, so results do not depend on this order.
+// Order of the (implicit) bounce-0 queue.  PTB_TILE_RAYGEN: consecutive queue positions walk 8x4 pixel tiles of one
+// sample instead of image rows, so the 32 primary rays of a warp - and, because the queues keep their order through
+// k_hit_list / k_shade, the bounce-1 rays that start where those hit - cover a compact patch of the image: fewer
+// distinct BVH nodes and texels per warp (k_extend -1.8 % console, -2 % foliage, -7.3 % city, profiles/r07/ab_s3.jsonl).
+// Pixels outside the largest 8x4-aligned rectangle keep row order.  The slot (pixel + sample * W*H) is what names the
+// path, so results do not depend on this order.
 #ifndef PTB_TILE_RAYGEN
 #define PTB_TILE_RAYGEN 1
 #endif
@@ -154,20 +155,15 @@ __device__ __forceinline__ uint32_t queue_to_slot(const WaveParams &P, uint32_t 
 #endif
 }
 
-__global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
-                                                WaveState W) {
+// raygen (mod.rs:107-124) no longer writes a queue: it opens the wave - zeroes the radiance sums and sets the size of
+// the implicit bounce-0 queue - and the rays themselves are generated where they are consumed (device_scene.cuh).
+__global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ WaveParams P, WaveState W) {
   const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
   if (q == 0) {
     W.counters[CTR_QUEUE(0)] = P.n_paths;
     W.counters[CTR_WORK_EXTEND] = 0;
   }
-  if (q >= P.n_paths) return;
-  const uint32_t slot = queue_to_slot(P, q);
-  Ray r = generate_ray(S, P, make_key(P, slot));
-  W.ray_o[0][q] = make_float4(r.o.x, r.o.y, r.o.z, 0.f);
-  W.ray_d[0][q] = make_float4(r.d.x, r.d.y, r.d.z, __int_as_float((int)slot));
-  W.thr[0][q] = make_float4(1.f, 1.f, 1.f, 0.f);
-  W.radiance[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (q < P.n_paths) __stcs(&W.radiance[q], make_float4(0.f, 0.f, 0.f, 0.f));
 }
 
 // Lane-level work fetch: every idle lane of the warp takes the next queue position.  A warp reserves queue positions
@@ -314,6 +310,7 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
   }
   constexpr uint32_t NONE = 0xFFFFFFFFu;
   const bool alpha = alpha_on != 0;
+  const bool implicit0 = bounce == 0 && trace_out == nullptr;  // the bounce-0 queue of a render: rays come from q
   uint32_t n_alpha = 0;
   ClosestTrav tv;
   NodeOrder no{};
@@ -339,11 +336,16 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
 #endif
     if (nq != NONE) {
       q = nq;
-      float4 o4 = ld_wave(&W.ray_o[in][q]), d4 = ld_wave(&W.ray_d[in][q]);
       Ray r;
-      r.o = mk3(o4.x, o4.y, o4.z);
-      r.d = mk3(d4.x, d4.y, d4.z);
-      slot = (uint32_t)__float_as_int(d4.w);
+      if (implicit0) {
+        slot = queue_to_slot(P, q);
+        r = generate_ray(S, P, make_key(P, slot));
+      } else {
+        float4 o4 = ld_wave(&W.ray_o[in][q]), d4 = ld_wave(&W.ray_d[in][q]);
+        r.o = mk3(o4.x, o4.y, o4.z);
+        r.d = mk3(d4.x, d4.y, d4.z);
+        slot = (uint32_t)__float_as_int(d4.w);
+      }
       tv.begin(r, stk, alpha);
       no = node_order(tv.r, tv.pre);
     }
@@ -432,11 +434,12 @@ __device__ __forceinline__ void cta_append2(uint32_t *pair, bool want_path, bool
 // PTB_HIT_LIST (on: console frame -5.9 %, foliage -0.3 ... -1.2 %, profiles/r06/ab_hitlist.jsonl): a scan pass between
 // k_extend and k_shade lists the queue positions that hit something, in queue order up to 256-position chunks, so
 // that every k_shade warp runs with 32 paths to shade instead of hits interleaved with misses (15 / 12 of 32 lanes
-// on bounces 1 / 2 of the console scene).  Misses get their background term in the scan pass.  The list lives in the
-// unused w component of the INPUT queue's origin records (entry i in ray_o[in][i].w), which k_shade only reads; its
-// length is counters[CTR_HITS], reset by k_extend.
+// on bounces 1 / 2 of the console scene).  Misses get their background term in the scan pass.  The list is a compact
+// u32 array (WaveState::hit_list: 4 bytes per hit, written and read coalesced); its length is counters[CTR_HITS],
+// reset by k_extend.
 #if PTB_HIT_LIST
-__global__ void __launch_bounds__(256) k_hit_list(const __grid_constant__ DevScene S, WaveState W, uint32_t bounce) {
+__global__ void __launch_bounds__(256) k_hit_list(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
+                                                  WaveState W, uint32_t bounce) {
   const uint32_t in = bounce & 1u;
   const uint32_t n = W.counters[CTR_QUEUE(in)];
   const V3 bgc = mk3(S.background[0], S.background[1], S.background[2]);
@@ -457,9 +460,13 @@ __global__ void __launch_bounds__(256) k_hit_list(const __grid_constant__ DevSce
       total += (uint32_t)__popc(m[k]);
       const uint32_t q = base + k * 32u + lane_id();
       if (bg && q < n && idx[k] < 0) {  // mod.rs:184-186: color + throughput * background, and the path ends
-        const float4 t4 = ld_wave(&W.thr[in][q]);
-        const uint32_t slot = (uint32_t)__float_as_int(__ldcs(&reinterpret_cast<const float *>(&W.ray_d[in][q])[3]));
-        add_radiance(W.radiance, slot, mul_el(mk3(t4.x, t4.y, t4.z), bgc));
+        if (bounce == 0) {  // implicit queue: throughput 1
+          add_radiance(W.radiance, queue_to_slot(P, q), bgc);
+        } else {
+          const float4 t4 = ld_wave(&W.thr[in][q]);
+          const uint32_t slot = (uint32_t)__float_as_int(__ldcs(&reinterpret_cast<const float *>(&W.ray_d[in][q])[3]));
+          add_radiance(W.radiance, slot, mul_el(mk3(t4.x, t4.y, t4.z), bgc));
+        }
       }
     }
     if (total == 0) continue;
@@ -468,9 +475,7 @@ __global__ void __launch_bounds__(256) k_hit_list(const __grid_constant__ DevSce
     pos = __shfl_sync(0xffffffffu, pos, 0);
 #pragma unroll
     for (uint32_t k = 0; k < K; ++k) {
-      if (idx[k] >= 0)
-        reinterpret_cast<float *>(&W.ray_o[in][pos + (uint32_t)__popc(m[k] & lanemask_lt())])[3] =
-            __int_as_float((int)(base + k * 32u + lane_id()));
+      if (idx[k] >= 0) __stcs(&W.hit_list[pos + (uint32_t)__popc(m[k] & lanemask_lt())], base + k * 32u + lane_id());
       pos += (uint32_t)__popc(m[k]);
     }
   }
@@ -512,7 +517,7 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
 #if PTB_HIT_LIST
     const bool active = base + lane_id() < n;
     uint32_t q = 0;
-    if (active) q = (uint32_t)__float_as_int(__ldcs(&reinterpret_cast<const float *>(&W.ray_o[in][base + lane_id()])[3]));
+    if (active) q = __ldcs(&W.hit_list[base + lane_id()]);
 #else
     const uint32_t q = base + lane_id();
     const bool active = q < n;
@@ -522,11 +527,18 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
     ShadeCtx ctx{};
     uint32_t slot = 0;
     if (active) {
-      float4 o4 = ld_wave(&W.ray_o[in][q]), d4 = ld_wave(&W.ray_d[in][q]), t4 = ld_wave(&W.thr[in][q]), h4 = ld_wave(&W.hit[q]);
-      slot = (uint32_t)__float_as_int(d4.w);
-      r.o = mk3(o4.x, o4.y, o4.z);
-      r.d = mk3(d4.x, d4.y, d4.z);
-      thr = mk3(t4.x, t4.y, t4.z);
+      const float4 h4 = ld_wave(&W.hit[q]);
+      if (bounce == 0) {  // implicit queue (device_scene.cuh): the primary ray of slot queue_to_slot(q), throughput 1
+        slot = queue_to_slot(P, q);
+        r = generate_ray(S, P, make_key(P, slot));
+        thr = mk3(1.f, 1.f, 1.f);
+      } else {
+        const float4 o4 = ld_wave(&W.ray_o[in][q]), d4 = ld_wave(&W.ray_d[in][q]), t4 = ld_wave(&W.thr[in][q]);
+        slot = (uint32_t)__float_as_int(d4.w);
+        r.o = mk3(o4.x, o4.y, o4.z);
+        r.d = mk3(d4.x, d4.y, d4.z);
+        thr = mk3(t4.x, t4.y, t4.z);
+      }
       shade_begin(S, r, h4.x, h4.y, h4.z, __float_as_int(h4.w), thr, rad, ctx);
       add_radiance(W.radiance, slot, rad);  // background (miss) or emissive: usually zero, then no memory traffic
     }
@@ -874,7 +886,8 @@ void launch_debug_aov(const DevScene &S, uint32_t width, uint32_t height, uint8_
 }
 void launch_init_srgb_lut(float *lut, cudaStream_t st) { k_init_srgb_lut<<<1, 256, 0, st>>>(lut); }
 void launch_raygen(const DevScene &S, const WaveParams &P, const WaveState &W, cudaStream_t st) {
-  k_raygen<<<(P.n_paths + 255) / 256, 256, 0, st>>>(S, P, W);
+  (void)S;
+  k_raygen<<<(P.n_paths + 255) / 256, 256, 0, st>>>(P, W);
 }
 void launch_extend(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, bool alpha,
                    pt_hit *trace_out, cudaStream_t st) {
@@ -891,11 +904,11 @@ void launch_shade(const DevScene &S, const WaveParams &P, const WaveState &W, ui
   k_shade<<<grid, 128, 0, st>>>(S, P, W, bounce);
 }
 // the scan pass between k_extend and k_shade (a no-op build without PTB_HIT_LIST)
-void launch_hit_list(const DevScene &S, const WaveState &W, uint32_t bounce, cudaStream_t st) {
+void launch_hit_list(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st) {
 #if PTB_HIT_LIST
-  k_hit_list<<<sm_count() * 8, 256, 0, st>>>(S, W, bounce);
+  k_hit_list<<<sm_count() * 8, 256, 0, st>>>(S, P, W, bounce);
 #else
-  (void)S; (void)W; (void)bounce; (void)st;
+  (void)S; (void)P; (void)W; (void)bounce; (void)st;
 #endif
 }
 int shade_launches() { return 1 + PTB_HIT_LIST; }

@@ -19,7 +19,7 @@ void launch_raygen(const DevScene &S, const WaveParams &P, const WaveState &W, c
 // alpha = false: first element of ray_cast's list; trace_out (optional): pt_hit per queue position
 void launch_extend(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, bool alpha,
                    pt_hit *trace_out, cudaStream_t st);
-void launch_hit_list(const DevScene &S, const WaveState &W, uint32_t bounce, cudaStream_t st);
+void launch_hit_list(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st);
 void launch_shade(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st);
 int shade_launches();  // launches of launch_hit_list + launch_shade together
 void launch_shadow(const DevScene &S, const WaveState &W, uint32_t bounce, cudaStream_t st);

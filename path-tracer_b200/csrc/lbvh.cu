@@ -1,5 +1,5 @@
-// lbvh.cu — GPU acceleration-structure build for large meshes: Morton codes, a hand-written LSD radix sort, the
-// Karras 2012 radix-tree hierarchy, a bottom-up box fit and a level-by-level collapse into the same 128-byte 4-wide
+// lbvh.cu — GPU acceleration-structure builds for large meshes: 60-bit Morton codes, a hand-written LSD radix sort,
+// then either the Karras 2012 radix-tree hierarchy (LBVH) or PLOC's nearest-neighbour agglomeration, a bottom-up box fit and a level-by-level collapse into the same 128-byte 4-wide
 // nodes the host SAH builder emits (bvh_build.cpp).  Replaces KDTree::build of the reference's third-party kdtree-ray
 // crate (call sites scene/internal/model.rs:96, scene/internal/mod.rs:42) when PT_ACCEL_LBVH is selected.
 // The tree is only a conservative candidate filter (results equal brute force; tests/test_gpu_parity.py), so the two
@@ -12,6 +12,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -162,9 +163,14 @@ __device__ __forceinline__ uint32_t expand10(uint32_t v) {  // 10 bits -> every 
   return v;
 }
 
-// ---- 2. 30-bit Morton code of the box centroid ----
+// ---- 2. 60-bit Morton code of the box centroid (20 bits per axis) as two 30-bit halves ----
+// 30 bits (a 1024^3 grid over the scene box) put dozens of triangles of a detailed object into one cell when the
+// scene box is much larger than the object (the console scene: a 1 M-triangle object on a ground plane), and the
+// order inside a cell is then arbitrary - for the radix tree and for PLOC's neighbour search alike.  hi = the top 10
+// bits of every axis interleaved, lo = the next 10: sorting by (hi, lo) is two stable passes of the 32-bit sort.
 __global__ void __launch_bounds__(256) k_morton(const float4 *__restrict__ blo, const float4 *__restrict__ bhi, uint32_t n,
-                                                const uint32_t *__restrict__ cbounds, uint32_t *__restrict__ keys,
+                                                const uint32_t *__restrict__ cbounds, uint32_t *__restrict__ key_hi,
+                                                uint32_t *__restrict__ key_lo, uint32_t *__restrict__ work_keys,
                                                 uint32_t *__restrict__ vals) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -175,11 +181,20 @@ __global__ void __launch_bounds__(256) k_morton(const float4 *__restrict__ blo, 
     const float mn = o2f(cbounds[k]), mx = o2f(cbounds[3 + k]);
     const float ext = mx - mn;
     float t = ext > 0.f ? (c[k] - mn) / ext : 0.f;
-    t = fminf(fmaxf(t * 1024.f, 0.f), 1023.f);
+    t = fminf(fmaxf(t * 1048576.f, 0.f), 1048575.f);
     q[k] = (uint32_t)t;
   }
-  keys[i] = (expand10(q[0]) << 2) | (expand10(q[1]) << 1) | expand10(q[2]);
+  const uint32_t h = (expand10(q[0] >> 10) << 2) | (expand10(q[1] >> 10) << 1) | expand10(q[2] >> 10);
+  const uint32_t l = (expand10(q[0] & 1023u) << 2) | (expand10(q[1] & 1023u) << 1) | expand10(q[2] & 1023u);
+  key_hi[i] = h;
+  key_lo[i] = l;
+  work_keys[i] = l;  // the first sort pass orders by the low half
   vals[i] = i;
+}
+__global__ void __launch_bounds__(256) k_gather_u32(const uint32_t *__restrict__ src, const uint32_t *__restrict__ idx, uint32_t n,
+                                                    uint32_t *__restrict__ dst) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = src[idx[i]];
 }
 
 // ---- 3. LSD radix sort of (key, value) pairs, 8 bits per pass ----
@@ -341,31 +356,34 @@ int radix_sort_pairs(uint32_t *keys, uint32_t *vals, uint32_t *keys_alt, uint32_
 // Node references: bit31 = 1 -> sorted primitive position (a radix-tree leaf); else internal node index.
 constexpr uint32_t PRIM = 0x80000000u;
 
-__device__ __forceinline__ int delta(const uint32_t *__restrict__ keys, int n, int i, int j) {
+__device__ __forceinline__ int delta(const uint32_t *__restrict__ khi, const uint32_t *__restrict__ klo, int n, int i, int j) {
   if (j < 0 || j >= n) return -1;
-  const uint32_t a = keys[i], b = keys[j];
-  if (a == b) return 32 + __clz((uint32_t)i ^ (uint32_t)j);
-  return __clz(a ^ b);
+  const uint32_t a = khi[i], b = khi[j];
+  if (a != b) return __clz(a ^ b);
+  const uint32_t c = klo[i], d = klo[j];
+  if (c != d) return 32 + __clz(c ^ d);
+  return 64 + __clz((uint32_t)i ^ (uint32_t)j);
 }
 
-__global__ void __launch_bounds__(256) k_radix_tree(const uint32_t *__restrict__ keys, int n, uint32_t *__restrict__ left,
+__global__ void __launch_bounds__(256) k_radix_tree(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ keys_lo, int n,
+                                                    uint32_t *__restrict__ left,
                                                     uint32_t *__restrict__ right, uint32_t *__restrict__ rlo,
                                                     uint32_t *__restrict__ rhi, uint32_t *__restrict__ parent_int,
                                                     uint32_t *__restrict__ parent_prim) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n - 1) return;
-  const int d = delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1) >= 0 ? 1 : -1;
-  const int dmin = delta(keys, n, i, i - d);
+  const int d = delta(keys, keys_lo, n, i, i + 1) - delta(keys, keys_lo, n, i, i - 1) >= 0 ? 1 : -1;
+  const int dmin = delta(keys, keys_lo, n, i, i - d);
   int lmax = 2;
-  while (delta(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+  while (delta(keys, keys_lo, n, i, i + lmax * d) > dmin) lmax *= 2;
   int l = 0;
   for (int t = lmax >> 1; t >= 1; t >>= 1)
-    if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    if (delta(keys, keys_lo, n, i, i + (l + t) * d) > dmin) l += t;
   const int j = i + l * d;
-  const int dnode = delta(keys, n, i, j);
+  const int dnode = delta(keys, keys_lo, n, i, j);
   int s = 0;
   for (int t = (l + 1) >> 1;; t = (t + 1) >> 1) {
-    if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    if (delta(keys, keys_lo, n, i, i + (s + t) * d) > dnode) s += t;
     if (t == 1) break;
   }
   const int gamma = i + s * d + min(d, 0);
@@ -420,8 +438,18 @@ __global__ void __launch_bounds__(256) k_fit(int n, const uint32_t *__restrict__
 // Output: the same arrays the radix-tree path produces (left / right / rlo / rhi / boxes, root = internal node 0, leaf
 // references = positions in a primitive order in which every subtree is contiguous), so collapse and leaf ordering
 // are shared.
-constexpr int PLOC_R = 16;
 constexpr uint32_t NONE32 = 0xFFFFFFFFu;
+// Search radius 8; $PT_B200_PLOC_R = 16 | 32 for A/B runs.  Measured frame time against the host SAH tree
+// (profiles/r07/builders_s7.jsonl, radius 8 / 16 / 32): console +8 / +14 / +19 %, foliage +17 / +18 / +22 %, city
+// -15 / -12 / -2 %: on these scenes a wider search does not buy better trees, only a longer build.
+int ploc_radius() {
+  static const int r = [] {
+    const char *e = std::getenv("PT_B200_PLOC_R");
+    const int v = e ? std::atoi(e) : 8;
+    return v == 16 || v == 32 ? v : 8;
+  }();
+  return r;
+}
 
 __global__ void __launch_bounds__(256) k_ploc_init(uint32_t n, const uint32_t *__restrict__ sorted_prim,
                                                    const float4 *__restrict__ blo, const float4 *__restrict__ bhi,
@@ -441,6 +469,7 @@ __device__ __forceinline__ float union_half_area(float4 alo, float4 ahi, float4 
 }
 
 // nearest neighbour of every cluster within +-PLOC_R positions (ties: the lower position)
+template <int PLOC_R>
 __global__ void __launch_bounds__(256) k_ploc_nn(uint32_t c, const float4 *__restrict__ clo, const float4 *__restrict__ chi,
                                                  uint32_t *__restrict__ nn) {
   __shared__ float4 slo[256 + 2 * PLOC_R], shi[256 + 2 * PLOC_R];
@@ -689,6 +718,7 @@ int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_dee
   float *d_pos = nullptr;
   float4 *d_sph = nullptr, *blo = nullptr, *bhi = nullptr, *nlo = nullptr, *nhi = nullptr;
   uint32_t *cb = nullptr, *keys = nullptr, *vals = nullptr, *keys2 = nullptr, *vals2 = nullptr, *counts = nullptr;
+  uint32_t *key_hi = nullptr, *key_lo = nullptr;  // unsorted Morton halves per primitive
   uint32_t *scan_tmp = nullptr, *left = nullptr, *right = nullptr, *rlo = nullptr, *rhi = nullptr, *par_i = nullptr;
   uint32_t *par_p = nullptr, *visits = nullptr, *tri_rank = nullptr, *leaf_tris = nullptr, *ctr = nullptr;
   uint2 *work[2] = {nullptr, nullptr};
@@ -708,6 +738,8 @@ int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_dee
   LB_TRY(B.alloc(&keys, n));
   LB_TRY(B.alloc(&vals, n));
   LB_TRY(B.alloc(&keys2, n));
+  LB_TRY(B.alloc(&key_hi, n));
+  LB_TRY(B.alloc(&key_lo, n));
   LB_TRY(B.alloc(&vals2, n));
   LB_TRY(B.alloc(&counts, 256 * (size_t)rs_blocks));
   LB_TRY(B.alloc(&scan_tmp, (256 * (size_t)rs_blocks + n) / SC_TILE + 16));
@@ -756,10 +788,14 @@ int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_dee
   LB_TRY(cudaMemcpyAsync(cb, init_cb, sizeof init_cb, cudaMemcpyHostToDevice, st));
   const uint32_t g256 = (n + 255) / 256;
   k_prim_boxes<<<std::min(g256, 148u * 16u), 256, 0, st>>>(d_pos, nt, d_sph, ns, blo, bhi, cb);
-  k_morton<<<g256, 256, 0, st>>>(blo, bhi, n, cb, keys, vals);
+  k_morton<<<g256, 256, 0, st>>>(blo, bhi, n, cb, key_hi, key_lo, keys, vals);
   k_pad_boxes<<<g256, 256, 0, st>>>(d_pos, nt, d_sph, ns, blo, bhi, cb, cam);  // symmetric: centroids unchanged
+  // order by (hi, lo): sort by the low half, then a stable sort by the high half
   int rc = radix_sort_pairs(keys, vals, keys2, vals2, n, 32, counts, scan_tmp, st);
   if (rc) return rc;
+  k_gather_u32<<<g256, 256, 0, st>>>(key_hi, vals, n, keys);
+  if ((rc = radix_sort_pairs(keys, vals, keys2, vals2, n, 32, counts, scan_tmp, st))) return rc;
+  k_gather_u32<<<g256, 256, 0, st>>>(key_lo, vals, n, keys2);  // keys = sorted high halves, keys2 = their low halves
   uint32_t *sorted = vals;  // sorted position -> primitive
   if (ploc) {
     PlocTree T{left, right, cnt, par_i, par_p, nlo, nhi, n};
@@ -778,7 +814,9 @@ int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_dee
         return PT_ERR_INVALID;
       }
       const uint32_t gc = (c + 255) / 256;
-      k_ploc_nn<<<gc, 256, 0, st>>>(c, clo[0], chi[0], nn);
+      if (ploc_radius() == 8) k_ploc_nn<8><<<gc, 256, 0, st>>>(c, clo[0], chi[0], nn);
+      else if (ploc_radius() == 32) k_ploc_nn<32><<<gc, 256, 0, st>>>(c, clo[0], chi[0], nn);
+      else k_ploc_nn<16><<<gc, 256, 0, st>>>(c, clo[0], chi[0], nn);
       k_ploc_merge<<<gc, 256, 0, st>>>(c, cref[0], clo[0], chi[0], nn, T, ctr + 2, keep);
       LB_TRY(cudaMemsetAsync(keep + c, 0, sizeof(uint32_t), st));
       if ((rc = exclusive_scan_u32(keep, kpos, c + 1, scan_tmp, st))) return rc;
@@ -801,7 +839,7 @@ int build_bvh4_lbvh(const HostScene &s, Bvh4 &out, float *build_ms, int *too_dee
   if ((rc = exclusive_scan_u32(tri_rank, tri_rank, n + 1, scan_tmp, st))) return rc;
   k_leaf_order<<<g256, 256, 0, st>>>(n, nt, sorted, tri_rank, leaf_tris, nullptr);
   if (!ploc) {
-    k_radix_tree<<<g256, 256, 0, st>>>(keys, (int)n, left, right, rlo, rhi, par_i, par_p);
+    k_radix_tree<<<g256, 256, 0, st>>>(keys, keys2, (int)n, left, right, rlo, rhi, par_i, par_p);
     LB_TRY(cudaMemsetAsync(visits, 0, (size_t)n * sizeof(uint32_t), st));
     k_fit<<<g256, 256, 0, st>>>((int)n, vals, blo, bhi, left, right, par_i, par_p, nlo, nhi, visits);
   }

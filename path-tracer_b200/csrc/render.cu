@@ -132,7 +132,7 @@ int build_device_scene(pt_scene *sc) {
   unsigned hw = std::max(1u, std::thread::hardware_concurrency());
   int accel = accel_choice();
   const uint64_t n_prims_geom = h.n_tris() + h.sphere_models.size();
-  if (accel == PT_ACCEL_AUTO) accel = n_prims_geom >= (4ull << 20) ? PT_ACCEL_LBVH : PT_ACCEL_SAH;
+  if (accel == PT_ACCEL_AUTO) accel = n_prims_geom >= (4ull << 20) ? PT_ACCEL_PLOC : PT_ACCEL_SAH;
   if (n_prims_geom < 16) accel = PT_ACCEL_SAH;  // the LBVH root must not be a single leaf (leaves hold <= 8 triangles)
   bool built = sc->accel_preloaded;
   if (!built) sc->accel = PT_ACCEL_SAH;
@@ -271,7 +271,7 @@ int ensure_wave(pt_scene *sc, uint32_t n_paths) {
   if (sc->wave.capacity >= n_paths && sc->wave.shadow_capacity >= shadow_cap) return PT_OK;
   free_wave(sc);
   const size_t bytes = wave_piece(CTR_COUNT, sizeof(uint32_t)) + 8 * wave_piece(n_paths, sizeof(float4)) +
-                       4 * wave_piece(shadow_cap, sizeof(float4));
+                       wave_piece(n_paths, sizeof(uint32_t)) + 4 * wave_piece(shadow_cap, sizeof(float4));
   void *mem = nullptr;
   if (cudaMalloc(&mem, bytes) != cudaSuccess) {
     cudaGetLastError();
@@ -298,6 +298,7 @@ int ensure_wave(pt_scene *sc, uint32_t n_paths) {
     W.thr[b] = reinterpret_cast<float4 *>(take(n_paths, sizeof(float4)));
   }
   W.hit = reinterpret_cast<float4 *>(take(n_paths, sizeof(float4)));
+  W.hit_list = reinterpret_cast<uint32_t *>(take(n_paths, sizeof(uint32_t)));
   W.radiance = reinterpret_cast<float4 *>(take(n_paths, sizeof(float4)));
   W.sh_o = reinterpret_cast<float4 *>(take(shadow_cap, sizeof(float4)));
   W.sh_d = reinterpret_cast<float4 *>(take(shadow_cap, sizeof(float4)));
@@ -791,7 +792,7 @@ int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t
   {
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
-      uint64_t per_path = 224 + 64ull * std::max(1u, sc->dev.n_lights);
+      uint64_t per_path = 148 + 64ull * std::max(1u, sc->dev.n_lights);  // 8 float4 arrays + the hit list + the shadow queue
       uint64_t have = (uint64_t)sc->wave.capacity * per_path;  // already allocated wave buffers count as free
       target_paths = std::min<uint64_t>(target_paths, std::max<uint64_t>(npix, (free_b + have) / 2 / per_path));
     }
@@ -854,7 +855,7 @@ int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t
     for (uint32_t b = 0; b <= prof->bounces; ++b) {
       launch_extend(sc->dev, P, W, b, sc->dev.any_alpha != 0, nullptr, st);
       mark(0);
-      launch_hit_list(sc->dev, W, b, st);
+      launch_hit_list(sc->dev, P, W, b, st);
       mark(4);  // the scan pass: reported with the shade class, listed on its own by $PT_B200_DUMP_MARKS
       if (shadow_pending) {  // k_shade refills the shadow queue the previous bounce's k_shadow reads
         CUDA_TRY(cudaStreamWaitEvent(st, sc->ev_shadow, 0));
