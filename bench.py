@@ -387,7 +387,10 @@ def measure(env, name, wl, steps, warmup, want_weak):
             # where one frame goes (one instrumented frame, CUDA events on the stream): the slowest rank's render, then
             # the reduce and the tonemap as rank 0 sees them (the reduce figure includes waiting for that slowest rank)
             "breakdown_ms": {"render_max_over_ranks": ms_render, "reduce_rank0": phases["ms_reduce"],
-                             "tonemap_rank0": phases["ms_tonemap"], "render_rank0": phases["ms_render"]},
+                             "tonemap_rank0": phases["ms_tonemap"], "render_rank0": phases["ms_render"],
+                             "render_device_rank0": phases["ms_render_device"],
+                             "note": "per-kernel timing is on in this frame (serial schedule, an event after every launch); "
+                                     "render_* include the host's enqueue of that frame, render_device is first launch -> last launch"},
             "roofline": roofline_of(name, st, clocks, props),
         }
         if weak:

@@ -87,9 +87,6 @@ constexpr int32_t HIT_INDEX_MASK = 0x3FFFFFFF;
 
 // One wave of paths, SoA.  Queue position q (compacted every bounce) owns ray/throughput;
 // `slot` = pixel + k*W*H (k-th sample of the wave) owns the radiance sum and the RNG key.
-// The bounce-0 queue of a render is IMPLICIT: position q holds the primary ray of slot queue_to_slot(q) with
-// throughput 1, and k_extend / k_hit_list / k_shade regenerate it from q (ten Philox rounds and a camera transform)
-// instead of reading 48 bytes that a raygen pass would have had to write first.
 struct WaveState {
   float4 *ray_o[2];   // xyz origin
   float4 *ray_d[2];   // xyz direction, w = slot (int bits)

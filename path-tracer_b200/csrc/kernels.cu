@@ -155,15 +155,24 @@ __device__ __forceinline__ uint32_t queue_to_slot(const WaveParams &P, uint32_t 
 #endif
 }
 
-// raygen (mod.rs:107-124) no longer writes a queue: it opens the wave - zeroes the radiance sums and sets the size of
-// the implicit bounce-0 queue - and the rays themselves are generated where they are consumed (device_scene.cuh).
-__global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ WaveParams P, WaveState W) {
+// raygen (mod.rs:107-124): one thread per queue position of buffer 0 (already compact); zeroes the path's radiance sum.
+// The throughput of a primary ray is 1 by definition and is not stored: k_hit_list / k_shade know it at bounce 0.
+// (Regenerating the whole primary ray from q in k_extend / k_shade instead of storing it was measured: the 2 ms of this
+// kernel go away, and come back as +1.4 ms in k_extend - ray generation inside its divergent refill path - and +0.4 ms
+// in k_shade: no gain, profiles/r07/bench_s8_implicit_queue.json.)
+__global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
+                                                WaveState W) {
   const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
   if (q == 0) {
     W.counters[CTR_QUEUE(0)] = P.n_paths;
     W.counters[CTR_WORK_EXTEND] = 0;
   }
-  if (q < P.n_paths) __stcs(&W.radiance[q], make_float4(0.f, 0.f, 0.f, 0.f));
+  if (q >= P.n_paths) return;
+  const uint32_t slot = queue_to_slot(P, q);
+  const Ray r = generate_ray(S, P, make_key(P, slot));
+  __stcs(&W.ray_o[0][q], make_float4(r.o.x, r.o.y, r.o.z, 0.f));
+  __stcs(&W.ray_d[0][q], make_float4(r.d.x, r.d.y, r.d.z, __int_as_float((int)slot)));
+  __stcs(&W.radiance[slot], make_float4(0.f, 0.f, 0.f, 0.f));
 }
 
 // Lane-level work fetch: every idle lane of the warp takes the next queue position.  A warp reserves queue positions
@@ -310,7 +319,6 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
   }
   constexpr uint32_t NONE = 0xFFFFFFFFu;
   const bool alpha = alpha_on != 0;
-  const bool implicit0 = bounce == 0 && trace_out == nullptr;  // the bounce-0 queue of a render: rays come from q
   uint32_t n_alpha = 0;
   ClosestTrav tv;
   NodeOrder no{};
@@ -336,16 +344,11 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
 #endif
     if (nq != NONE) {
       q = nq;
+      const float4 o4 = ld_wave(&W.ray_o[in][q]), d4 = ld_wave(&W.ray_d[in][q]);
       Ray r;
-      if (implicit0) {
-        slot = queue_to_slot(P, q);
-        r = generate_ray(S, P, make_key(P, slot));
-      } else {
-        float4 o4 = ld_wave(&W.ray_o[in][q]), d4 = ld_wave(&W.ray_d[in][q]);
-        r.o = mk3(o4.x, o4.y, o4.z);
-        r.d = mk3(d4.x, d4.y, d4.z);
-        slot = (uint32_t)__float_as_int(d4.w);
-      }
+      r.o = mk3(o4.x, o4.y, o4.z);
+      r.d = mk3(d4.x, d4.y, d4.z);
+      slot = (uint32_t)__float_as_int(d4.w);
       tv.begin(r, stk, alpha);
       no = node_order(tv.r, tv.pre);
     }
@@ -460,13 +463,13 @@ __global__ void __launch_bounds__(256) k_hit_list(const __grid_constant__ DevSce
       total += (uint32_t)__popc(m[k]);
       const uint32_t q = base + k * 32u + lane_id();
       if (bg && q < n && idx[k] < 0) {  // mod.rs:184-186: color + throughput * background, and the path ends
-        if (bounce == 0) {  // implicit queue: throughput 1
-          add_radiance(W.radiance, queue_to_slot(P, q), bgc);
-        } else {
+        const uint32_t slot = (uint32_t)__float_as_int(__ldcs(&reinterpret_cast<const float *>(&W.ray_d[in][q])[3]));
+        V3 t = mk3(1.f, 1.f, 1.f);  // bounce 0: the throughput of a primary ray is not stored
+        if (bounce != 0) {
           const float4 t4 = ld_wave(&W.thr[in][q]);
-          const uint32_t slot = (uint32_t)__float_as_int(__ldcs(&reinterpret_cast<const float *>(&W.ray_d[in][q])[3]));
-          add_radiance(W.radiance, slot, mul_el(mk3(t4.x, t4.y, t4.z), bgc));
+          t = mk3(t4.x, t4.y, t4.z);
         }
+        add_radiance(W.radiance, slot, mul_el(t, bgc));
       }
     }
     if (total == 0) continue;
@@ -527,16 +530,13 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_cons
     ShadeCtx ctx{};
     uint32_t slot = 0;
     if (active) {
-      const float4 h4 = ld_wave(&W.hit[q]);
-      if (bounce == 0) {  // implicit queue (device_scene.cuh): the primary ray of slot queue_to_slot(q), throughput 1
-        slot = queue_to_slot(P, q);
-        r = generate_ray(S, P, make_key(P, slot));
-        thr = mk3(1.f, 1.f, 1.f);
-      } else {
-        const float4 o4 = ld_wave(&W.ray_o[in][q]), d4 = ld_wave(&W.ray_d[in][q]), t4 = ld_wave(&W.thr[in][q]);
-        slot = (uint32_t)__float_as_int(d4.w);
-        r.o = mk3(o4.x, o4.y, o4.z);
-        r.d = mk3(d4.x, d4.y, d4.z);
+      const float4 o4 = ld_wave(&W.ray_o[in][q]), d4 = ld_wave(&W.ray_d[in][q]), h4 = ld_wave(&W.hit[q]);
+      slot = (uint32_t)__float_as_int(d4.w);
+      r.o = mk3(o4.x, o4.y, o4.z);
+      r.d = mk3(d4.x, d4.y, d4.z);
+      thr = mk3(1.f, 1.f, 1.f);  // bounce 0: not stored by k_raygen
+      if (bounce != 0) {
+        const float4 t4 = ld_wave(&W.thr[in][q]);
         thr = mk3(t4.x, t4.y, t4.z);
       }
       shade_begin(S, r, h4.x, h4.y, h4.z, __float_as_int(h4.w), thr, rad, ctx);
@@ -886,8 +886,7 @@ void launch_debug_aov(const DevScene &S, uint32_t width, uint32_t height, uint8_
 }
 void launch_init_srgb_lut(float *lut, cudaStream_t st) { k_init_srgb_lut<<<1, 256, 0, st>>>(lut); }
 void launch_raygen(const DevScene &S, const WaveParams &P, const WaveState &W, cudaStream_t st) {
-  (void)S;
-  k_raygen<<<(P.n_paths + 255) / 256, 256, 0, st>>>(P, W);
+  k_raygen<<<(P.n_paths + 255) / 256, 256, 0, st>>>(S, P, W);
 }
 void launch_extend(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, bool alpha,
                    pt_hit *trace_out, cudaStream_t st) {
