@@ -170,8 +170,11 @@ int pt_set_accel_builder(int accel);
  * time (host wall clock for SAH; device time for LBVH), *max_depth = levels of 4-wide nodes. */
 int pt_scene_accel_info(const pt_scene *scene, int *accel, double *build_ms, int *max_depth);
 /* Re-sends every device array of the scene (nodes, triangles, shading records, materials, texels, lights) from
- * its pinned host image, asynchronously on `stream`: the host->device leg of a call that starts from host
- * memory (Scene::load's result living on the host).  *bytes_out = bytes copied. */
+ * its pinned host image: the host->device leg of a call that starts from host memory (Scene::load's result living on
+ * the host).  Asynchronous and double-buffered: the copies go, on the scene's own copy stream, into a second set of
+ * device arrays (allocated on the first call) that no kernel is reading, and the next render / trace call on the
+ * scene waits for them and switches to that set - so the upload for frame k+1 overlaps the rendering of frame k.
+ * `stream` is unused (kept for source compatibility).  *bytes_out = bytes copied. */
 int pt_scene_upload(pt_scene *scene, void *stream, uint64_t *bytes_out);
 /* Introspection (host copies; pointers valid until pt_scene_destroy). */
 int pt_scene_get_desc(const pt_scene *scene, pt_scene_desc *out);

@@ -65,8 +65,17 @@ struct pt_scene {
   struct Staged {  // device array + its pinned host image (pt_scene_upload re-sends it)
     void *dev, *host;
     size_t bytes;
+    void *dev2;          // second device copy: the target of the next pt_scene_upload (allocated on its first call)
+    const void **field;  // the DevScene member that points at `dev`
   };
   std::vector<Staged> staged;
+  // pt_scene_upload is double-buffered: it copies into the set of arrays the kernels are NOT reading, on its own
+  // stream, and the next render / trace call switches to that set - so the upload of the next frame's scene overlaps
+  // the rendering of the current one.  use_ev[k]: the last call that read set k; upload_ev: the pending upload.
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t upload_ev = nullptr, use_ev[2] = {nullptr, nullptr};
+  int cur_set = 0;
+  bool upload_pending = false;
   std::vector<cudaEvent_t> events;  // pool for per-kernel timing (pt_set_kernel_timing)
   uint64_t device_bytes = 0;
   double build_ms = 0;
@@ -93,6 +102,7 @@ struct pt_scene {
 
 namespace {
 
+// `out` must be a member of sc->dev (it is re-pointed when pt_scene_upload switches array sets).
 template <typename T>
 int upload(pt_scene *sc, const std::vector<T> &v, const T **out) {
   size_t bytes = std::max<size_t>(v.size(), 1) * sizeof(T);
@@ -104,7 +114,7 @@ int upload(pt_scene *sc, const std::vector<T> &v, const T **out) {
     void *hp = nullptr;
     CUDA_TRY(cudaMallocHost(&hp, v.size() * sizeof(T)));
     std::memcpy(hp, v.data(), v.size() * sizeof(T));
-    sc->staged.push_back({p, hp, v.size() * sizeof(T)});
+    sc->staged.push_back({p, hp, v.size() * sizeof(T), nullptr, reinterpret_cast<const void **>(out)});
     CUDA_TRY(cudaMemcpy(p, hp, v.size() * sizeof(T), cudaMemcpyHostToDevice));
   }
   *out = reinterpret_cast<const T *>(p);
@@ -214,9 +224,7 @@ int build_device_scene(pt_scene *sc) {
   DevScene &D = sc->dev;
   int rc;
   static_assert(sizeof(DevNode) == sizeof(Bvh4Node), "node layout");
-  const Bvh4Node *dn = nullptr;
-  if ((rc = upload(sc, sc->bvh.nodes, &dn))) return rc;
-  D.nodes = reinterpret_cast<const DevNode *>(dn);
+  if ((rc = upload(sc, sc->bvh.nodes, reinterpret_cast<const Bvh4Node **>(&D.nodes)))) return rc;
   if ((rc = upload(sc, tris, &D.tris))) return rc;
   if ((rc = upload(sc, shade, &D.shade))) return rc;
   if ((rc = upload(sc, spheres, &D.spheres))) return rc;
@@ -319,6 +327,23 @@ cudaError_t frame_buf(pt_scene::FrameBuf &b, size_t bytes) {
   return e;
 }
 
+// Called with sc->mu held at the start of every call that launches kernels on the scene: a pending pt_scene_upload
+// becomes visible (the stream waits for the copy, the DevScene pointers switch to the freshly written set).
+void apply_pending_upload(pt_scene *sc, cudaStream_t st) {
+  if (!sc->upload_pending) return;
+  cudaStreamWaitEvent(st, sc->upload_ev, 0);
+  for (auto &e : sc->staged) {
+    std::swap(e.dev, e.dev2);
+    *e.field = e.dev;
+  }
+  sc->cur_set ^= 1;
+  sc->upload_pending = false;
+}
+// ... and at its end: the array set it read stays untouched until these kernels have finished.
+void mark_scene_use(pt_scene *sc, cudaStream_t st) {
+  if (sc->use_ev[sc->cur_set]) cudaEventRecord(sc->use_ev[sc->cur_set], st);
+}
+
 // Host-side mutual exclusion on the scene's wave buffers plus device-side ordering between streams: the stream waits
 // for the previous user of the buffers before it touches them, and records itself as that user on the way out.
 struct WaveLock {
@@ -327,9 +352,11 @@ struct WaveLock {
   std::unique_lock<std::mutex> lk;
   WaveLock(pt_scene *s, cudaStream_t stream) : sc(s), st(stream), lk(s->mu) {
     if (sc->busy) cudaStreamWaitEvent(st, sc->busy, 0);
+    apply_pending_upload(sc, st);
   }
   ~WaveLock() {
     if (sc->busy) cudaEventRecord(sc->busy, st);
+    mark_scene_use(sc, st);
   }
 };
 
@@ -462,6 +489,10 @@ void pt_scene_destroy(pt_scene *sc) {
   for (pt_scene::FrameBuf *b : {&sc->multi_accum, &sc->multi_tmp, &sc->multi_rgb, &sc->trace_in, &sc->trace_aux, &sc->trace_out})
     cudaFree(b->p);
   if (sc->busy) cudaEventDestroy(sc->busy);
+  if (sc->upload_ev) cudaEventDestroy(sc->upload_ev);
+  for (int k = 0; k < 2; ++k)
+    if (sc->use_ev[k]) cudaEventDestroy(sc->use_ev[k]);
+  if (sc->copy_stream) cudaStreamDestroy(sc->copy_stream);
   if (sc->ev_shade) cudaEventDestroy(sc->ev_shade);
   if (sc->ev_shadow) cudaEventDestroy(sc->ev_shadow);
   if (sc->side) cudaStreamDestroy(sc->side);
@@ -472,17 +503,34 @@ void pt_scene_destroy(pt_scene *sc) {
 }
 
 int pt_scene_upload(pt_scene *sc, void *stream, uint64_t *bytes_out) {
+  (void)stream;  // kept for the ABI: the copies run on the scene's own copy stream (see the header)
   if (!sc) {
     set_error("null argument");
     return PT_ERR_INVALID;
   }
   if (sc->device < 0) return no_device();
   DeviceGuard g(sc->device);
-  uint64_t total = 0;
-  for (auto &s : sc->staged) {
-    CUDA_TRY(cudaMemcpyAsync(s.dev, s.host, s.bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream));
-    total += s.bytes;
+  std::lock_guard<std::mutex> lock(sc->mu);
+  if (!sc->copy_stream) {
+    CUDA_TRY(cudaStreamCreateWithFlags(&sc->copy_stream, cudaStreamNonBlocking));
+    CUDA_TRY(cudaEventCreateWithFlags(&sc->upload_ev, cudaEventDisableTiming));
+    for (int k = 0; k < 2; ++k) CUDA_TRY(cudaEventCreateWithFlags(&sc->use_ev[k], cudaEventDisableTiming));
+    for (auto &e : sc->staged) {
+      CUDA_TRY(cudaMalloc(&e.dev2, e.bytes));
+      sc->allocs.push_back(e.dev2);  // freed with the scene whichever set is current by then
+      sc->device_bytes += e.bytes;
+    }
   }
+  // the set the kernels are not reading; wait for the last kernels that did read it (two frames ago)
+  const int target = sc->cur_set ^ 1;
+  CUDA_TRY(cudaStreamWaitEvent(sc->copy_stream, sc->use_ev[target], 0));
+  uint64_t total = 0;
+  for (auto &e : sc->staged) {
+    CUDA_TRY(cudaMemcpyAsync(e.dev2, e.host, e.bytes, cudaMemcpyHostToDevice, sc->copy_stream));
+    total += e.bytes;
+  }
+  CUDA_TRY(cudaEventRecord(sc->upload_ev, sc->copy_stream));
+  sc->upload_pending = true;
   if (bytes_out) *bytes_out = total;
   return PT_OK;
 }
@@ -755,7 +803,11 @@ int pt_trace_paths(const pt_scene *sc, const pt_profile *prof, const uint32_t *p
   if (e == cudaSuccess) e = cudaMemcpy(d_pix, pixels, n_paths * sizeof(uint32_t), cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaMemset(d_out, 0, nv * sizeof(pt_path_vertex));
   if (e == cudaSuccess) {
+    pt_scene *msc = const_cast<pt_scene *>(sc);
+    std::lock_guard<std::mutex> lock(msc->mu);
+    apply_pending_upload(msc, nullptr);
     launch_trace_paths(sc->dev, P, d_pix, (uint32_t)n_paths, d_out, d_cnt, nullptr);
+    mark_scene_use(msc, nullptr);
     e = cudaGetLastError();
   }
   if (e == cudaSuccess) e = cudaMemcpy(out, d_out, nv * sizeof(pt_path_vertex), cudaMemcpyDeviceToHost);
@@ -1136,7 +1188,11 @@ int pt_debug_textures(const pt_scene *sc, uint32_t width, uint32_t height, uint8
   if (e == cudaSuccess) e = cudaMemset(d_planes, 0, bytes);
   if (e == cudaSuccess) e = cudaMemset(d_hit, 0, sizeof(uint32_t));
   if (e == cudaSuccess) {
+    pt_scene *msc = const_cast<pt_scene *>(sc);
+    std::lock_guard<std::mutex> lock(msc->mu);
+    apply_pending_upload(msc, nullptr);
     launch_debug_aov(sc->dev, width, height, d_planes, d_hit, nullptr);
+    mark_scene_use(msc, nullptr);
     e = cudaGetLastError();
   }
   uint32_t n_hit = 0;

@@ -461,6 +461,30 @@ def test_render_multi_in_process(tmp_path, loaded):
     assert np.abs(pt.read_png(str(out)).astype(np.int16) - ref.astype(np.int16)).max() <= 1
 
 
+def test_scene_upload_is_double_buffered_and_takes_effect(loaded):
+    """pt_scene_upload copies into the array set no kernel is reading and the next call switches to it: renders and
+    traces interleaved with uploads keep returning the same results (several switches back and forth)."""
+    import torch
+    sa, osc, gsc = loaded["alpha_transparency"]
+    sc = pt.Scene.load(scene_path("alpha_transparency"))
+    prof = pt.Profile(width=128, height=96, samples=6, bounces=4)
+    rr = R.random_rays(sa, 1 << 14, seed=3)
+    ref_hits = gsc.trace_closest(rr)
+    ref = torch.zeros(96, 128, 3, device="cuda")
+    pt.render_accum_device(gsc, prof, ref.data_ptr())
+    for k in range(5):
+        n = sc.upload()
+        assert n == sc.upload()  # two uploads in a row before a render: the later one wins, same bytes
+        assert n > 0
+        buf = torch.zeros(96, 128, 3, device="cuda")
+        pt.render_accum_device(sc, prof, buf.data_ptr(), want_stats=(k % 2 == 0))
+        torch.cuda.synchronize()
+        assert torch.allclose(buf, ref, rtol=1e-5, atol=1e-6), k
+        sc.upload()
+        assert np.array_equal(sc.trace_closest(rr), ref_hits), k
+    sc.close()
+
+
 def test_zero_samples_and_bad_arguments(loaded):
     import torch
     _, _, gsc = loaded["cube"]
