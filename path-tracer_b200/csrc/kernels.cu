@@ -736,6 +736,9 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
   uint32_t q = NONE, slot = 0;
   V3 c{};
   tv.cur = ShadowTrav::DONE;
+#if PTB_SHADOW_CACHE
+  uint32_t last_occ = NONE;  // the opaque triangle that shadowed this lane's previous ray
+#endif
 #if PTB_FETCH_AHEAD_SHADOW
   WorkFetch wf;
   wf.init(&W.counters[CTR_WORK_SHADOW], n);
@@ -764,6 +767,10 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
       c = mk3(c4.x, c4.y, c4.z);
       tv.begin(r, o4.w, mk3(p4.x, p4.y, p4.z), c4.w, p4.w);
       no = node_order(tv.r, tv.pre);
+#if PTB_SHADOW_CACHE
+      tv.occluder = NONE;
+      if (last_occ != NONE) tv.try_cached(S, last_occ);
+#endif
     }
     if (__ballot_sync(0xffffffffu, q != NONE) == 0) break;
     for (;;) {
@@ -774,6 +781,9 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
       const uint32_t m_inner = __ballot_sync(0xffffffffu, has && tv.at_inner());
       if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) tv.leaf_step(S, stk);
       if (has && tv.cur == ShadowTrav::DONE) {
+#if PTB_SHADOW_CACHE
+        if (tv.occluder != NONE) last_occ = tv.occluder;  // a cache hit leaves it as it is
+#endif
         if (tv.tr != 0.0f) {
           float *dst = reinterpret_cast<float *>(W.radiance + slot);
           atomicAdd(dst + 0, c.x * tv.tr);
