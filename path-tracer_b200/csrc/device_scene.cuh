@@ -120,7 +120,12 @@ enum {
   CTR_STAT_EXTEND = 8,  // 64-bit statistics start here (pairs)
   CTR_STAT_SHADOW = 10,
   CTR_STAT_ALPHA = 12,  // opacity evaluations of the alpha walk
-  CTR_COUNT = 16
+  // -DPTB_COUNT_STEPS builds only (tools/build_variant.sh steps -DPTB_COUNT_STEPS=1): node visits / primitive tests
+  CTR_STAT_EXT_NODES = 16,
+  CTR_STAT_EXT_PRIMS = 18,
+  CTR_STAT_SH_NODES = 20,
+  CTR_STAT_SH_PRIMS = 22,
+  CTR_COUNT = 24
 };
 #define CTR_QUEUE(b) (2u * (b))
 #define CTR_SHADOW(b) (2u * (b) + 1u)

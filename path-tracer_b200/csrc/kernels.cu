@@ -39,6 +39,11 @@
 #ifndef PTB_HIT_LIST
 #define PTB_HIT_LIST 1
 #endif
+// instrumented build: k_extend / k_shadow count their node visits and primitive tests (printed by
+// $PT_B200_DUMP_MARKS); never on in the shipped library (two more live registers per lane)
+#ifndef PTB_COUNT_STEPS
+#define PTB_COUNT_STEPS 0
+#endif
 
 namespace ptb {
 
@@ -320,6 +325,9 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
   constexpr uint32_t NONE = 0xFFFFFFFFu;
   const bool alpha = alpha_on != 0;
   uint32_t n_alpha = 0;
+#if PTB_COUNT_STEPS
+  uint32_t cnt_nodes = 0, cnt_prims = 0;
+#endif
   ClosestTrav tv;
   NodeOrder no{};
   ClosestStack stk;
@@ -355,10 +363,16 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
     if (__ballot_sync(0xffffffffu, q != NONE) == 0) break;
     for (;;) {
       const bool has = q != NONE;
+#if PTB_COUNT_STEPS
+      if (has && tv.at_inner()) ++cnt_nodes;
+#endif
       if (has && tv.at_inner()) tv.node_step(S, no, stk);
       const bool leaf = has && tv.at_leaf();
       const uint32_t m_leaf = __ballot_sync(0xffffffffu, leaf);
       const uint32_t m_inner = __ballot_sync(0xffffffffu, has && tv.at_inner());
+#if PTB_COUNT_STEPS
+      if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) ++cnt_prims;
+#endif
       if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0))
         tv.leaf_step(S, stk, alpha, bounce, [&]() { return make_key(P, slot); }, n_alpha);
       if (has && tv.cur == ClosestTrav::DONE) {
@@ -383,6 +397,14 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
 #undef drained
   n_alpha = __reduce_add_sync(0xffffffffu, n_alpha);
   if (lane_id() == 0 && n_alpha) stat_add(W.counters, CTR_STAT_ALPHA, n_alpha);
+#if PTB_COUNT_STEPS
+  cnt_nodes = __reduce_add_sync(0xffffffffu, cnt_nodes);
+  cnt_prims = __reduce_add_sync(0xffffffffu, cnt_prims);
+  if (lane_id() == 0) {
+    stat_add(W.counters, CTR_STAT_EXT_NODES, cnt_nodes);
+    stat_add(W.counters, CTR_STAT_EXT_PRIMS, cnt_prims);
+  }
+#endif
 }
 
 // Warp-aggregated append to the path queue AND the shadow queue filled with it: one 64-bit atomic per warp reserves
@@ -739,6 +761,9 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
 #if PTB_SHADOW_CACHE
   uint32_t last_occ = NONE;  // the opaque triangle that shadowed this lane's previous ray
 #endif
+#if PTB_COUNT_STEPS
+  uint32_t cnt_nodes = 0, cnt_prims = 0;
+#endif
 #if PTB_FETCH_AHEAD_SHADOW
   WorkFetch wf;
   wf.init(&W.counters[CTR_WORK_SHADOW], n);
@@ -775,10 +800,16 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
     if (__ballot_sync(0xffffffffu, q != NONE) == 0) break;
     for (;;) {
       const bool has = q != NONE;
+#if PTB_COUNT_STEPS
+      if (has && tv.at_inner()) ++cnt_nodes;
+#endif
       if (has && tv.at_inner()) tv.node_step(S, no, stk);
       const bool leaf = has && tv.at_leaf();
       const uint32_t m_leaf = __ballot_sync(0xffffffffu, leaf);
       const uint32_t m_inner = __ballot_sync(0xffffffffu, has && tv.at_inner());
+#if PTB_COUNT_STEPS
+      if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) ++cnt_prims;
+#endif
       if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) tv.leaf_step(S, stk);
       if (has && tv.cur == ShadowTrav::DONE) {
 #if PTB_SHADOW_CACHE
@@ -796,6 +827,14 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
       if (busy == 0 || (!drained && __popc(busy) < REFILL_THRESHOLD_SHADOW)) break;
     }
   }
+#if PTB_COUNT_STEPS
+  cnt_nodes = __reduce_add_sync(0xffffffffu, cnt_nodes);
+  cnt_prims = __reduce_add_sync(0xffffffffu, cnt_prims);
+  if (lane_id() == 0) {
+    stat_add(W.counters, CTR_STAT_SH_NODES, cnt_nodes);
+    stat_add(W.counters, CTR_STAT_SH_PRIMS, cnt_prims);
+  }
+#endif
 }
 
 #undef drained

@@ -973,6 +973,12 @@ int pt_render_accum_device(const pt_scene *csc, const pt_profile *prof, uint32_t
         if (dump) std::fprintf(stderr, "mark %zu %s %.4f ms\n", i, cls[marks[i]], ms);
       }
       acc[1] += acc[4];
+      if (dump && (u64(CTR_STAT_EXT_NODES) || u64(CTR_STAT_SH_NODES)))  // a -DPTB_COUNT_STEPS build
+        std::fprintf(stderr, "steps: extend %.3f nodes %.3f prims per ray; shadow %.3f nodes %.3f prims per ray\n",
+                     (double)u64(CTR_STAT_EXT_NODES) / std::max<uint64_t>(1, u64(CTR_STAT_EXTEND)),
+                     (double)u64(CTR_STAT_EXT_PRIMS) / std::max<uint64_t>(1, u64(CTR_STAT_EXTEND)),
+                     (double)u64(CTR_STAT_SH_NODES) / std::max<uint64_t>(1, u64(CTR_STAT_SHADOW)),
+                     (double)u64(CTR_STAT_SH_PRIMS) / std::max<uint64_t>(1, u64(CTR_STAT_SHADOW)));
       stats_out->ms_extend = acc[0];
       stats_out->ms_shade = acc[1];
       stats_out->ms_shadow = acc[2];
