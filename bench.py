@@ -334,15 +334,15 @@ def measure(env, name, wl, steps, warmup, want_weak):
     dropped = env.sum_over_ranks(st["shadow_dropped"])
     alpha_all = env.sum_over_ranks(st["alpha_tests"])
 
-    # end to end through the public API with host buffers.  One GPU: the C-ABI call a host makes (pt_scene_upload of
-    # the scene from pinned host memory + pt_render into a host image).  Several GPUs under torchrun: upload, this
-    # rank's pt_render_accum_device, the NCCL reduce, pt_tonemap_device and the read-back of the image on rank 0.
+    # end to end through the public API with host buffers.  One GPU: the C-ABI calls a host makes per frame
+    # (INTEGRATION.md): pt_scene_upload of the scene from pinned host memory + pt_render_async into a pinned host image
+    # - both asynchronous, so the upload of frame k+1 overlaps the rendering of frame k; the timed region ends with the
+    # last image on the host.  Several GPUs under torchrun: upload, this rank's pt_render_accum_device, the NCCL reduce,
+    # pt_tonemap_device and the read-back of the image on rank 0.
     if env.world == 1:
-        rend = pkg.Renderer(profile=prof)
-
         def step_e2e():
             nbytes = scene.upload(env.stream.cuda_stream)
-            rend.render(scene)
+            pkg.render_async(scene, prof, rgb_host.data_ptr(), stream=env.stream.cuda_stream)
             return nbytes
     else:
         def step_e2e():
@@ -379,7 +379,7 @@ def measure(env, name, wl, steps, warmup, want_weak):
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(w * h * 3),
                     "ms_per_step": ms_e2e / steps,
-                    "call": "pt_scene_upload + pt_render (host image out)" if env.world == 1 else
+                    "call": "pt_scene_upload + pt_render_async (pinned host image out), pipelined" if env.world == 1 else
                             "pt_scene_upload + pt_render_accum_device per rank + NCCL reduce + pt_tonemap_device + D2H on rank 0"},
             "gpu_launches": int((st["kernel_launches"] + 1) * steps),
             "rays_per_step": {"extend": ext_all, "shadow": sh_all, "alpha_tests": alpha_all,

@@ -249,6 +249,14 @@ int pt_tonemap_device(const float *accum_dev, uint32_t width, uint32_t height, u
 int pt_render(const pt_scene *scene, const pt_profile *profile, uint64_t seed, uint8_t *rgb8_out,
               float *accum_out, pt_stats *stats_out);
 
+/* pt_render without the wait: the render, the tonemap and the copy of the image into rgb8_out (host memory; pinned
+ * memory if the copy is to be asynchronous) are enqueued on `stream` and the call returns.  rgb8_out is valid after
+ * pt_stream_synchronize(device, stream) (or the caller's own cudaStreamSynchronize).  Frames issued back to back on
+ * one stream run in order, and a pt_scene_upload issued between them overlaps the frame before it: the pipelined form
+ * of a host loop that streams scene updates (bench.py's end-to-end leg at one GPU). */
+int pt_render_async(const pt_scene *scene, const pt_profile *profile, uint64_t seed, uint8_t *rgb8_out, void *stream);
+int pt_stream_synchronize(int device, void *stream);
+
 /* ---- Renderer::render over several GPUs of one box, in one process ---- */
 /* A copy of `scene` resident on `device` (-1: host-only copy).  Nothing is parsed again and the acceleration
  * structure of the source (built or loaded with it) is reused, so a replica costs one upload.  The reference shares

@@ -23,7 +23,7 @@ EXPORTS = ["pt_last_error", "pt_device_count", "pt_profile_default", "pt_profile
            "pt_trace_closest", "pt_trace_closest_device", "pt_trace_accepted", "pt_trace_shadow", "pt_trace_transmittance",
            "pt_triangle_intersect", "pt_philox4x32_10",
            "pt_trace_paths", "pt_render_accum_device", "pt_aov_name", "pt_debug_textures", "pt_render_progressive", "pt_convert_gltf", "pt_scene_save_binary",
-           "pt_tonemap_device", "pt_render", "pt_scene_replicate", "pt_render_multi", "pt_write_png", "pt_read_png", "pt_free"]
+           "pt_tonemap_device", "pt_render", "pt_render_async", "pt_stream_synchronize", "pt_scene_replicate", "pt_render_multi", "pt_write_png", "pt_read_png", "pt_free"]
 
 
 SNAPSHOT_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_uint8), C.c_uint32, C.c_uint32, C.c_uint32)
@@ -71,6 +71,8 @@ def lib():
         L.pt_render_accum_device.argtypes = [vp, C.POINTER(pt_profile), u32, u32, u32, u64, vp, vp, C.POINTER(pt_stats)]
         L.pt_tonemap_device.argtypes = [vp, u32, u32, u32, C.c_int32, vp, C.c_int, vp]
         L.pt_render.argtypes = [vp, C.POINTER(pt_profile), u64, vp, vp, C.POINTER(pt_stats)]
+        L.pt_render_async.argtypes = [vp, C.POINTER(pt_profile), u64, vp, vp]
+        L.pt_stream_synchronize.argtypes = [C.c_int, vp]
         L.pt_scene_replicate.argtypes = [vp, C.c_int, C.POINTER(vp)]
         L.pt_render_multi.argtypes = [C.POINTER(vp), u32, C.POINTER(pt_profile), u64, vp, vp, C.POINTER(pt_stats)]
         L.pt_write_png.argtypes = [C.c_char_p, vp, u32, u32]
@@ -341,6 +343,15 @@ class Renderer:
         self.last_stats = st.as_dict()
         self.last_accum = accum
         return rgb
+
+
+def render_async(scene, profile, rgb8_host_ptr, seed=0, stream=None):
+    """pt_render_async: enqueue one frame (render + tonemap + copy into host memory at rgb8_host_ptr) on `stream`."""
+    _check(lib().pt_render_async(scene.h, C.byref(profile.c), seed, rgb8_host_ptr, stream))
+
+
+def stream_synchronize(device=0, stream=None):
+    _check(lib().pt_stream_synchronize(device, stream))
 
 
 def render_multi(replicas, profile, seed=0, keep_accum=False):

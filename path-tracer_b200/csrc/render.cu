@@ -1031,6 +1031,47 @@ int pt_render(const pt_scene *csc, const pt_profile *prof, uint64_t seed, uint8_
   return PT_OK;
 }
 
+int pt_render_async(const pt_scene *csc, const pt_profile *prof, uint64_t seed, uint8_t *rgb8_out, void *stream) {
+  pt_scene *sc = const_cast<pt_scene *>(csc);
+  if (!sc || !rgb8_out) {
+    set_error("null argument");
+    return PT_ERR_INVALID;
+  }
+  int rc = check_profile(prof);
+  if (rc) return rc;
+  if (sc->device < 0) return no_device();
+  DeviceGuard g(sc->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t npix = (size_t)prof->width * prof->height;
+  std::lock_guard<std::mutex> hold(sc->multi_mu);
+  if (frame_buf(sc->multi_accum, npix * 3 * sizeof(float)) != cudaSuccess || frame_buf(sc->multi_rgb, npix * 3) != cudaSuccess) {
+    cudaGetLastError();
+    set_error("out of device memory");
+    return PT_ERR_NOMEM;
+  }
+  float *d_accum = static_cast<float *>(sc->multi_accum.p);
+  uint8_t *d_rgb = static_cast<uint8_t *>(sc->multi_rgb.p);
+  // the frame buffers are reused by the next call: stream order (same stream) or the scene's busy event (another
+  // stream) keeps a frame's tonemap + copy ahead of the next frame's memset
+  if (sc->busy) CUDA_TRY(cudaStreamWaitEvent(st, sc->busy, 0));
+  CUDA_TRY(cudaMemsetAsync(d_accum, 0, npix * 3 * sizeof(float), st));
+  rc = pt_render_accum_device(sc, prof, 0, 1, prof->samples, seed, d_accum, st, nullptr);
+  if (rc == PT_OK) rc = pt_tonemap_device(d_accum, prof->width, prof->height, prof->samples, prof->tonemap, d_rgb, sc->device, st);
+  if (rc != PT_OK) return rc;
+  CUDA_TRY(cudaMemcpyAsync(rgb8_out, d_rgb, npix * 3, cudaMemcpyDeviceToHost, st));
+  {
+    std::lock_guard<std::mutex> lock(sc->mu);
+    if (sc->busy) CUDA_TRY(cudaEventRecord(sc->busy, st));  // now covers the tonemap and the copy as well
+  }
+  return PT_OK;
+}
+
+int pt_stream_synchronize(int device, void *stream) {
+  DeviceGuard g(device);
+  CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+  return PT_OK;
+}
+
 int pt_scene_replicate(const pt_scene *src, int device, pt_scene **out) {
   if (!src || !out) {
     set_error("null argument");

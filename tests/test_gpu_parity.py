@@ -485,6 +485,25 @@ def test_scene_upload_is_double_buffered_and_takes_effect(loaded):
     sc.close()
 
 
+def test_render_async_pipelines_frames_and_uploads(loaded):
+    """pt_render_async: frames issued back to back on one stream, with a scene upload between them, each deliver the
+    image pt_render returns."""
+    import torch
+    _, _, gsc = loaded["cube"]
+    prof = pt.Profile(width=96, height=64, samples=5, bounces=3)
+    want = pt.Renderer(profile=prof).render(gsc)
+    sc = pt.Scene.load(scene_path("cube"))
+    bufs = [torch.empty(64, 96, 3, dtype=torch.uint8).pin_memory() for _ in range(4)]
+    st = torch.cuda.Stream()
+    for b in bufs:
+        sc.upload()
+        pt.render_async(sc, prof, b.data_ptr(), stream=st.cuda_stream)
+    pt.stream_synchronize(0, st.cuda_stream)
+    for b in bufs:
+        assert np.array_equal(b.numpy(), want)
+    sc.close()
+
+
 def test_zero_samples_and_bad_arguments(loaded):
     import torch
     _, _, gsc = loaded["cube"]
