@@ -69,6 +69,7 @@ struct DevScene {
   const float *srgb_lut;  // [0,256): powf(i / 255, 2.2), the sRGB -> linear step of material.rs:132-146; [256,512): i / 255
   uint32_t n_tris, n_spheres, n_lights, n_nodes;
   uint32_t root_is_valid;
+  uint32_t tree_depth;  // levels of 4-wide nodes (host-side launch heuristics only)
   uint32_t any_alpha;  // some material may be non-opaque
   float camera[16];
   float fov;

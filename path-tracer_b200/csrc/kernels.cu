@@ -312,6 +312,12 @@ constexpr int LEAF_THRESHOLD = PTB_LEAF_T;      // run the (divergent) primitive
 // nobody is at an inner node any more), so that node visits and primitive tests each run with most lanes active
 // ("while-while").  alpha_on = 0 gives the first element of ray_cast's list instead (pt_trace_closest); trace_out,
 // when not null, also receives the public hit record of every queue position (the fixed-batch parity harness).
+// POP = where the lazy pop runs (traverse.cuh, PTB_POP_MODE): 0 inline at its two call sites, 1 at one site per loop
+// iteration.  Measured (profiles/r07/ab_s14_pop_modes.jsonl): mode 1 is +0.8 % on console (5.4 node visits per ray: a
+// leaf popped after a node step joins the primitive phase one iteration later), -3 % on foliage and city (21 - 23
+// node visits per ray, many stale stack entries: the pop loop was 15 % of foliage's warp instructions at 3 lanes).
+// launch_extend picks by tree depth.
+template <int POP>
 __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
                                                 WaveState W, uint32_t bounce, uint32_t alpha_on, pt_hit *__restrict__ trace_out) {
   const uint32_t in = bounce & 1u, outb = in ^ 1u;
@@ -331,7 +337,7 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
   ClosestTrav tv;
   NodeOrder no{};
   ClosestStack stk;
-  uint32_t q = NONE, slot = 0;
+  uint32_t q = NONE;
   tv.cur = ClosestTrav::DONE;
 #if PTB_FETCH_AHEAD_EXTEND
   WorkFetch wf;
@@ -356,7 +362,6 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
       Ray r;
       r.o = mk3(o4.x, o4.y, o4.z);
       r.d = mk3(d4.x, d4.y, d4.z);
-      slot = (uint32_t)__float_as_int(d4.w);
       tv.begin(r, stk, alpha);
       no = node_order(tv.r, tv.pre);
     }
@@ -366,7 +371,7 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
 #if PTB_COUNT_STEPS
       if (has && tv.at_inner()) ++cnt_nodes;
 #endif
-      if (has && tv.at_inner()) tv.node_step(S, no, stk);
+      if (has && tv.at_inner()) tv.node_step(S, no, stk, POP != 0);
       const bool leaf = has && tv.at_leaf();
       const uint32_t m_leaf = __ballot_sync(0xffffffffu, leaf);
       const uint32_t m_inner = __ballot_sync(0xffffffffu, has && tv.at_inner());
@@ -374,7 +379,13 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
       if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) ++cnt_prims;
 #endif
       if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0))
-        tv.leaf_step(S, stk, alpha, bounce, [&]() { return make_key(P, slot); }, n_alpha);
+        tv.leaf_step(S, stk, alpha, bounce,
+                     [&]() {  // the path's slot names its RNG key; re-read from the queue record when a draw is needed
+                       return make_key(P, (uint32_t)__float_as_int(ld_wave(&W.ray_d[in][q]).w));
+                     },
+                     n_alpha, POP != 0);
+      if (POP == 1 && has && tv.cur == ClosestTrav::NEED_POP) tv.pop(stk);
+      if (POP == 2 && has && tv.cur == ClosestTrav::NEED_POP) tv.pop_one(stk);
       if (has && tv.cur == ClosestTrav::DONE) {
         tv.finish(stk, alpha);
         const bool hit = tv.st.idx >= 0;
@@ -755,8 +766,7 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
   ShadowTrav tv;
   NodeOrder no{};
   uint32_t stk[PTB_STACK];
-  uint32_t q = NONE, slot = 0;
-  V3 c{};
+  uint32_t q = NONE;
   tv.cur = ShadowTrav::DONE;
 #if PTB_SHADOW_CACHE
   uint32_t last_occ = NONE;  // the opaque triangle that shadowed this lane's previous ray
@@ -782,19 +792,33 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
 #else
     uint32_t nq = refill(&W.counters[CTR_WORK_SHADOW], q == NONE, n, drained);
 #endif
+    // the rest of the ray's record (light distance, primary hit position and uv, contribution, slot) stays in the
+    // queue and is re-read when a primitive is hit / when the walk ends: twelve registers less per lane
+    auto rec = [&]() {
+      const float4 p4 = ld_wave(&W.sh_p[q]);
+      ShadowRec R;
+      R.limit = ld_wave(&W.sh_o[q]).w;
+      R.pos = mk3(p4.x, p4.y, p4.z);
+      R.pu = ld_wave(&W.sh_c[q]).w;
+      R.pv = p4.w;
+      return R;
+    };
     if (nq != NONE) {
       q = nq;
-      float4 o4 = ld_wave(&W.sh_o[q]), d4 = ld_wave(&W.sh_d[q]), c4 = ld_wave(&W.sh_c[q]), p4 = ld_wave(&W.sh_p[q]);
+      const float4 o4 = ld_wave(&W.sh_o[q]), d4 = ld_wave(&W.sh_d[q]);
       Ray r;
       r.o = mk3(o4.x, o4.y, o4.z);
       r.d = mk3(d4.x, d4.y, d4.z);
-      slot = (uint32_t)__float_as_int(d4.w);
-      c = mk3(c4.x, c4.y, c4.z);
-      tv.begin(r, o4.w, mk3(p4.x, p4.y, p4.z), c4.w, p4.w);
+      V3 ppos = mk3(0.f, 0.f, 0.f);
+      if (o4.w >= 0.0f) {
+        const float4 p4 = ld_wave(&W.sh_p[q]);
+        ppos = mk3(p4.x, p4.y, p4.z);
+      }
+      tv.begin(r, o4.w, ppos);
       no = node_order(tv.r, tv.pre);
 #if PTB_SHADOW_CACHE
       tv.occluder = NONE;
-      if (last_occ != NONE) tv.try_cached(S, last_occ);
+      if (last_occ != NONE) tv.try_cached(S, last_occ, rec);
 #endif
     }
     if (__ballot_sync(0xffffffffu, q != NONE) == 0) break;
@@ -810,16 +834,18 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
 #if PTB_COUNT_STEPS
       if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) ++cnt_prims;
 #endif
-      if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) tv.leaf_step(S, stk);
+      if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) tv.leaf_step(S, stk, rec);
       if (has && tv.cur == ShadowTrav::DONE) {
 #if PTB_SHADOW_CACHE
         if (tv.occluder != NONE) last_occ = tv.occluder;  // a cache hit leaves it as it is
 #endif
         if (tv.tr != 0.0f) {
+          const float4 c4 = ld_wave(&W.sh_c[q]);
+          const uint32_t slot = (uint32_t)__float_as_int(ld_wave(&W.sh_d[q]).w);
           float *dst = reinterpret_cast<float *>(W.radiance + slot);
-          atomicAdd(dst + 0, c.x * tv.tr);
-          atomicAdd(dst + 1, c.y * tv.tr);
-          atomicAdd(dst + 2, c.z * tv.tr);
+          atomicAdd(dst + 0, c4.x * tv.tr);
+          atomicAdd(dst + 1, c4.y * tv.tr);
+          atomicAdd(dst + 2, c4.z * tv.tr);
         }
         q = NONE;
       }
@@ -939,7 +965,14 @@ void launch_raygen(const DevScene &S, const WaveParams &P, const WaveState &W, c
 }
 void launch_extend(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, bool alpha,
                    pt_hit *trace_out, cudaStream_t st) {
-  k_extend<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, P, W, bounce, alpha ? 1u : 0u, trace_out);
+  // deep trees (long traversals with many stale stack entries) take the merged pop site; PTB_POP_MODE forces one
+  const int grid = sm_count() * PERSIST_CTAS_PER_SM;
+#if defined(PTB_POP_MODE_FORCED)
+  k_extend<PTB_POP_MODE><<<grid, 128, 0, st>>>(S, P, W, bounce, alpha ? 1u : 0u, trace_out);
+#else
+  if (S.tree_depth >= 16) k_extend<1><<<grid, 128, 0, st>>>(S, P, W, bounce, alpha ? 1u : 0u, trace_out);
+  else k_extend<0><<<grid, 128, 0, st>>>(S, P, W, bounce, alpha ? 1u : 0u, trace_out);
+#endif
 }
 void launch_shade(const DevScene &S, const WaveParams &P, const WaveState &W, uint32_t bounce, cudaStream_t st) {
   static std::atomic<int> cache[MAX_DEVICES];

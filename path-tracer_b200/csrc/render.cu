@@ -248,6 +248,7 @@ int build_device_scene(pt_scene *sc) {
   D.n_lights = (uint32_t)lights.size();
   D.n_nodes = (uint32_t)sc->bvh.nodes.size();
   D.root_is_valid = 1;
+  D.tree_depth = (uint32_t)std::max(0, sc->bvh.max_depth);
   D.any_alpha = any_alpha ? 1u : 0u;
   std::memcpy(D.camera, h.camera, sizeof D.camera);
   D.fov = h.fov;

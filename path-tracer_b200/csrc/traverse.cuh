@@ -43,6 +43,16 @@ __device__ __noinline__ bool alpha_accepts(const DevScene &S, uint32_t pixel, ui
   return rng_alpha(k, bounce, (uint32_t)prim_id) < op;
 }
 
+// Where the lazy pop (skip stack entries behind the current best hit) runs in the persistent kernel (k_extend<POP>):
+//   0  inline at its two call sites (after a node visit that entered no child, after the last primitive of a leaf)
+//   1  one site per loop iteration for every lane that needs a pop, looping until a live entry is found
+//   2  one site, ONE stack entry per iteration: a lane that draws a stale entry tries again next iteration (measured:
+//      console +6 %, foliage -5 %, city +3 %; not used)
+// -DPTB_POP_MODE=<n> forces one mode for every scene (A/B builds).
+#ifdef PTB_POP_MODE
+#define PTB_POP_MODE_FORCED 1
+#endif
+
 struct ClosestTrav {
   Ray r;
   RayPre pre;
@@ -52,6 +62,7 @@ struct ClosestTrav {
   int sp;
 
   static constexpr uint32_t DONE = 0xFFFFFFFFu;
+  static constexpr uint32_t NEED_POP = 0xFFFFFFFEu;  // PTB_POP_MODE != 0: the kernel's pop site takes over
 
   __device__ __forceinline__ void begin(const Ray &ray, ClosestStack &stk, bool alpha) {
     r = ray;
@@ -66,7 +77,24 @@ struct ClosestTrav {
     if (alpha) stk.put(FAR_SLOT, -1.0f, 0xFFFFFFFFu);  // no rejected hit yet
   }
   __device__ __forceinline__ bool at_inner() const { return !(cur & 0x80000000u); }
-  __device__ __forceinline__ bool at_leaf() const { return (cur & 0x80000000u) && cur != DONE; }
+  __device__ __forceinline__ bool at_leaf() const { return (cur & 0x80000000u) && cur < NEED_POP; }
+  // what node_step / leaf_step do when the current subtree is exhausted
+  __device__ __forceinline__ void after(const ClosestStack &stk, bool deferred) {
+    if (deferred) cur = NEED_POP;
+    else pop(stk);
+  }
+  // PTB_POP_MODE 2: examine one stack entry
+  __device__ __forceinline__ void pop_one(const ClosestStack &stk) {
+    if (sp == 0) {
+      cur = DONE;
+      return;
+    }
+    --sp;
+    float t;
+    uint32_t ref;
+    stk.get(sp, t, ref);
+    if (t <= t_prune) cur = ref;
+  }
 
   // next stack entry that can still hold a nearer hit (entries behind the current best hit are skipped lazily)
   __device__ __forceinline__ void pop(const ClosestStack &stk) {
@@ -83,7 +111,7 @@ struct ClosestTrav {
     cur = DONE;
   }
   // Precondition: at_inner().  Visits one node: cur becomes the nearest child hit, or the next stack entry.
-  __device__ __forceinline__ void node_step(const DevScene &S, const NodeOrder &no, ClosestStack &stk) {
+  __device__ __forceinline__ void node_step(const DevScene &S, const NodeOrder &no, ClosestStack &stk, bool deferred = false) {
     const NodeData nd = load_node(S.nodes, cur);
     const uint4 ch = nd.ch;
     float t0 = slab_fma(nd.lo_x.x, nd.lo_y.x, nd.lo_z.x, nd.hi_x.x, nd.hi_y.x, nd.hi_z.x, pre, no, t_prune, ch.x);
@@ -97,7 +125,7 @@ struct ClosestTrav {
     if (t2 < CUDART_INF_F) stk.put(sp++, t2, r2);
     if (t1 < CUDART_INF_F) stk.put(sp++, t1, r1);
     if (t0 < CUDART_INF_F) cur = r0;
-    else pop(stk);
+    else after(stk, deferred);
   }
 
   // One candidate hit with key (t, id).  Without `alpha` the smallest key wins (ray_cast's first element).  With it,
@@ -135,7 +163,7 @@ struct ClosestTrav {
   // more primitives left stays current (first+1, count-1 == ref + 7).
   template <typename KeyFn>
   __device__ __forceinline__ void leaf_step(const DevScene &S, ClosestStack &stk, bool alpha, uint32_t bounce,
-                                            KeyFn key_of, uint32_t &n_alpha) {
+                                            KeyFn key_of, uint32_t &n_alpha, bool deferred = false) {
     if (cur & 0x40000000u) {
       const uint32_t si = cur & 0x3FFFFFFFu;
       const DevSphere sph = S.spheres[si];
@@ -147,7 +175,7 @@ struct ClosestTrav {
         consider(S, stk, dist[k], sph.prim_id + is_exit, 0.f, 0.f, (int)(S.n_tris + 2u * si + (uint32_t)is_exit), sph.flags,
                  alpha, bounce, key_of, n_alpha);
       }
-      pop(stk);
+      after(stk, deferred);
       return;
     }
     const float4 *tp = reinterpret_cast<const float4 *>(S.tris + ((cur & 0x3FFFFFFFu) >> 3));
@@ -157,7 +185,7 @@ struct ClosestTrav {
       consider(S, stk, t, __float_as_int(A.w), u, v, __float_as_int(B.w) | (det < 0.0f ? HIT_BACKFACE : 0),
                __float_as_uint(C.w), alpha, bounce, key_of, n_alpha);
     if (cur & 7u) cur += 7u;
-    else pop(stk);
+    else after(stk, deferred);
   }
 
   // After DONE: when nothing was accepted, the farthest rejected hit is the one the reference shades.
@@ -178,6 +206,22 @@ struct ClosestTrav {
     st.idx = (int)fi;
   }
 };
+
+// Opacity of an occluder that is not exactly opaque (mod.rs:291-297 / :319-329).  Out of line: it is reached by a few
+// lanes at a time and holds the shading-record and texture fetches the any-hit loop should not carry in its registers.
+#ifndef PTB_SHADOW_OPACITY_INLINE
+#define PTB_SHADOW_OPACITY_INLINE 0
+#endif
+#if PTB_SHADOW_OPACITY_INLINE
+__device__ __forceinline__
+#else
+__device__ __noinline__
+#endif
+float occluder_opacity(const DevScene &S, int tri, uint32_t flags, float u, float v, bool point, float pu, float pv) {
+  if (point) return eval_opacity(S, S.shade[tri].model, pu != pu, pu, pv);  // the PRIMARY hit's uv / variant (mod.rs:324)
+  if (flags & TRI_FLAG_ALPHA) return hit_opacity(S, tri, u, v);
+  return S.materials[S.shade[tri].model].opacity;
+}
 
 #ifndef PTB_SHADOW_ORDERED
 // 1: k_shadow visits the children of a node nearest-first.  Measured (profiles/r07/ab_s1.jsonl): k_shadow +19 % on the
@@ -202,11 +246,19 @@ struct ClosestTrav {
 #define PTB_SHADOW_CACHE 0
 #endif
 
+// What the shadow walk needs from the ray's queue record besides the ray itself, and only when a primitive is hit:
+// kept in memory (k_shadow re-reads the record) instead of in eight registers of every lane.
+struct ShadowRec {
+  float limit;  // < 0: directional light; else the point light's distance from the primary hit
+  V3 pos;       // primary hit position
+  float pu, pv; // primary hit texture coordinates (pu NaN: the primary hit is a sphere)
+};
+
 struct ShadowTrav {
   Ray r;
   RayPre pre;
-  float t_max, limit, pu, pv, tr;
-  V3 pos;
+  float t_max, tr;
+  bool point;
   uint32_t cur;
   int sp;
   uint32_t occluder;  // leaf-order index of the opaque triangle that ended this walk (valid when it did)
@@ -214,15 +266,12 @@ struct ShadowTrav {
   // limit < 0: directional light (every hit on the ray, occluder sampled at its own uv, mod.rs:291-297)
   // limit >= 0: point light at distance `limit` from the primary hit `p`; occluders farther than the light are
   // ignored and the occluder's material is sampled with the PRIMARY hit's uv/variant (mod.rs:319-329, u NaN = sphere)
-  __device__ __forceinline__ void begin(const Ray &ray, float lim, V3 p, float u, float v) {
+  __device__ __forceinline__ void begin(const Ray &ray, float lim, V3 p) {
     r = ray;
     pre = precompute(ray);
-    limit = lim;
-    pos = p;
-    pu = u;
-    pv = v;
+    point = lim >= 0.0f;
     t_max = CUDART_INF_F;
-    if (lim >= 0.0f) {
+    if (point) {
 #if PTB_FAST_INV
       // a culling bound with a 2e-4 allowance: approximate square roots and division are enough (the exact
       // `distance > limit` test of mod.rs:319-330 is applied per hit in leaf_step)
@@ -246,15 +295,17 @@ struct ShadowTrav {
   __device__ __forceinline__ bool at_leaf() const { return (cur & 0x80000000u) && cur != DONE; }
   __device__ __forceinline__ void pop(const uint32_t *stk) { cur = (tr == 0.0f || sp == 0) ? DONE : stk[--sp]; }
   // After begin(): if the ray hits opaque triangle `tri` (leaf order) within the light's reach, the walk is over.
-  __device__ __forceinline__ void try_cached(const DevScene &S, uint32_t tri) {
+  template <typename RecFn>
+  __device__ __forceinline__ void try_cached(const DevScene &S, uint32_t tri, RecFn rec) {
     const float4 *tp = reinterpret_cast<const float4 *>(S.tris + tri);
     const float4 A = __ldg(tp), B = __ldg(tp + 1), C = __ldg(tp + 2);
     if (!(__float_as_uint(C.w) & TRI_FLAG_OPAQUE1)) return;
     float t, u, v, det;
     if (!moller_trumbore(r, mk3(A.x, A.y, A.z), mk3(B.x, B.y, B.z), mk3(C.x, C.y, C.z), t, u, v, det)) return;
-    if (limit >= 0.0f) {
+    if (point) {
+      const ShadowRec R = rec();
       const V3 p = r.o + r.d * t;
-      if (length3(p - pos) > limit) return;
+      if (length3(p - R.pos) > R.limit) return;
     }
     tr = 0.0f;
     cur = DONE;
@@ -308,21 +359,24 @@ struct ShadowTrav {
 #endif
     pop(stk);
   }
-  // One primitive per step (see ClosestTrav::leaf_step).
-  __device__ __forceinline__ void leaf_step(const DevScene &S, const uint32_t *stk) {
-    const bool point = limit >= 0.0f;
+  // One primitive per step (see ClosestTrav::leaf_step).  rec() fetches the ShadowRec of the ray when a hit needs it.
+  template <typename RecFn>
+  __device__ __forceinline__ void leaf_step(const DevScene &S, const uint32_t *stk, RecFn rec) {
     if (cur & 0x40000000u) {
       const DevSphere s = S.spheres[cur & 0x3FFFFFFFu];
       float dist[2], tp[2];
       int exit_only = 0;
       int nh = sphere_hits(r, s, dist, tp, exit_only);
-      for (int k = 0; k < nh; ++k) {
-        if (point) {
-          V3 p = r.o + r.d * tp[k];
-          if (length3(p - pos) > limit) continue;
+      if (nh) {
+        const ShadowRec R = rec();
+        for (int k = 0; k < nh; ++k) {
+          if (point) {
+            V3 p = r.o + r.d * tp[k];
+            if (length3(p - R.pos) > R.limit) continue;
+          }
+          float op = point ? eval_opacity(S, s.model, R.pu != R.pu, R.pu, R.pv) : S.materials[s.model].opacity;
+          tr *= 1.0f - op;
         }
-        float op = point ? eval_opacity(S, s.model, pu != pu, pu, pv) : S.materials[s.model].opacity;
-        tr *= 1.0f - op;
       }
       pop(stk);
       return;
@@ -332,22 +386,19 @@ struct ShadowTrav {
     float t, u, v, det;
     if (moller_trumbore(r, mk3(A.x, A.y, A.z), mk3(B.x, B.y, B.z), mk3(C.x, C.y, C.z), t, u, v, det)) {
       const uint32_t flags = __float_as_uint(C.w);
+      ShadowRec R{};
+      if (point) R = rec();
       bool counted = true;
       if (point) {
         V3 p = r.o + r.d * t;
-        counted = !(length3(p - pos) > limit);
+        counted = !(length3(p - R.pos) > R.limit);
       }
       if (counted) {
         if (flags & TRI_FLAG_OPAQUE1) {
           tr = 0.0f;  // opacity is exactly 1 whatever uv it is sampled at: tr * (1 - 1); no material fetch
           occluder = (cur & 0x3FFFFFFFu) >> 3;
         } else {
-          const int tri = __float_as_int(B.w);
-          float op;
-          if (point) op = eval_opacity(S, S.shade[tri].model, pu != pu, pu, pv);
-          else if (flags & TRI_FLAG_ALPHA) op = hit_opacity(S, tri, u, v);
-          else op = S.materials[S.shade[tri].model].opacity;
-          tr *= 1.0f - op;
+          tr *= 1.0f - occluder_opacity(S, __float_as_int(B.w), flags, u, v, point, R.pu, R.pv);
         }
       }
     }
@@ -378,11 +429,13 @@ __device__ __forceinline__ float trace_transmittance(const DevScene &S, const Ra
                                                      float pv) {
   uint32_t stk[PTB_STACK];
   ShadowTrav tv;
-  tv.begin(r, limit, pos, pu, pv);
+  tv.begin(r, limit, pos);
   const NodeOrder no = node_order(tv.r, tv.pre);
+  const ShadowRec R{limit, pos, pu, pv};
+  auto rec = [&]() { return R; };
   while (tv.cur != ShadowTrav::DONE) {
     if (tv.at_inner()) tv.node_step(S, no, stk);
-    else tv.leaf_step(S, stk);
+    else tv.leaf_step(S, stk, rec);
   }
   return tv.tr;
 }

@@ -26,7 +26,7 @@ for r in rows[2:]:
     for i, n in idx:
         v = r[i]
         if n == "kernel":
-            v = v.split("(")[0].replace("ptb::", "")
+            v = v.split("(")[0].replace("ptb::", "").replace("void ", "")
         else:
             try:
                 v = "%.3g" % float(v.replace(",", ""))

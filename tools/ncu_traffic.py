@@ -13,6 +13,7 @@ import csv
 import io
 import json
 import os
+import re
 import subprocess
 import sys
 
@@ -33,7 +34,7 @@ def main():
     rays = line["rays_per_step"]
     per = {}
     for r in rows[2:]:
-        name = r[col["Kernel Name"]].split("(")[0].replace("ptb::", "")
+        name = re.sub(r"<.*", "", r[col["Kernel Name"]].split("(")[0].replace("ptb::", "").replace("void ", ""))
         f = lambda k: float(r[col[k]].replace(",", "")) if k in col and r[col[k]] not in ("", "n/a") else 0.0
         unit = lambda k: rows[1][col[k]]
         scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
