@@ -766,7 +766,8 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
   ShadowTrav tv;
   NodeOrder no{};
   uint32_t stk[PTB_STACK];
-  uint32_t q = NONE;
+  uint32_t q = NONE, slot = 0;
+  V3 c{};
   tv.cur = ShadowTrav::DONE;
 #if PTB_SHADOW_CACHE
   uint32_t last_occ = NONE;  // the opaque triangle that shadowed this lane's previous ray
@@ -792,33 +793,19 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
 #else
     uint32_t nq = refill(&W.counters[CTR_WORK_SHADOW], q == NONE, n, drained);
 #endif
-    // the rest of the ray's record (light distance, primary hit position and uv, contribution, slot) stays in the
-    // queue and is re-read when a primitive is hit / when the walk ends: twelve registers less per lane
-    auto rec = [&]() {
-      const float4 p4 = ld_wave(&W.sh_p[q]);
-      ShadowRec R;
-      R.limit = ld_wave(&W.sh_o[q]).w;
-      R.pos = mk3(p4.x, p4.y, p4.z);
-      R.pu = ld_wave(&W.sh_c[q]).w;
-      R.pv = p4.w;
-      return R;
-    };
     if (nq != NONE) {
       q = nq;
-      const float4 o4 = ld_wave(&W.sh_o[q]), d4 = ld_wave(&W.sh_d[q]);
+      float4 o4 = ld_wave(&W.sh_o[q]), d4 = ld_wave(&W.sh_d[q]), c4 = ld_wave(&W.sh_c[q]), p4 = ld_wave(&W.sh_p[q]);
       Ray r;
       r.o = mk3(o4.x, o4.y, o4.z);
       r.d = mk3(d4.x, d4.y, d4.z);
-      V3 ppos = mk3(0.f, 0.f, 0.f);
-      if (o4.w >= 0.0f) {
-        const float4 p4 = ld_wave(&W.sh_p[q]);
-        ppos = mk3(p4.x, p4.y, p4.z);
-      }
-      tv.begin(r, o4.w, ppos);
+      slot = (uint32_t)__float_as_int(d4.w);
+      c = mk3(c4.x, c4.y, c4.z);
+      tv.begin(r, o4.w, mk3(p4.x, p4.y, p4.z), c4.w, p4.w);
       no = node_order(tv.r, tv.pre);
 #if PTB_SHADOW_CACHE
       tv.occluder = NONE;
-      if (last_occ != NONE) tv.try_cached(S, last_occ, rec);
+      if (last_occ != NONE) tv.try_cached(S, last_occ);
 #endif
     }
     if (__ballot_sync(0xffffffffu, q != NONE) == 0) break;
@@ -834,18 +821,16 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
 #if PTB_COUNT_STEPS
       if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) ++cnt_prims;
 #endif
-      if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) tv.leaf_step(S, stk, rec);
+      if (leaf && (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0)) tv.leaf_step(S, stk);
       if (has && tv.cur == ShadowTrav::DONE) {
 #if PTB_SHADOW_CACHE
         if (tv.occluder != NONE) last_occ = tv.occluder;  // a cache hit leaves it as it is
 #endif
         if (tv.tr != 0.0f) {
-          const float4 c4 = ld_wave(&W.sh_c[q]);
-          const uint32_t slot = (uint32_t)__float_as_int(ld_wave(&W.sh_d[q]).w);
           float *dst = reinterpret_cast<float *>(W.radiance + slot);
-          atomicAdd(dst + 0, c4.x * tv.tr);
-          atomicAdd(dst + 1, c4.y * tv.tr);
-          atomicAdd(dst + 2, c4.z * tv.tr);
+          atomicAdd(dst + 0, c.x * tv.tr);
+          atomicAdd(dst + 1, c.y * tv.tr);
+          atomicAdd(dst + 2, c.z * tv.tr);
         }
         q = NONE;
       }

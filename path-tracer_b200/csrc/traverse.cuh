@@ -207,22 +207,6 @@ struct ClosestTrav {
   }
 };
 
-// Opacity of an occluder that is not exactly opaque (mod.rs:291-297 / :319-329).  Out of line: it is reached by a few
-// lanes at a time and holds the shading-record and texture fetches the any-hit loop should not carry in its registers.
-#ifndef PTB_SHADOW_OPACITY_INLINE
-#define PTB_SHADOW_OPACITY_INLINE 0
-#endif
-#if PTB_SHADOW_OPACITY_INLINE
-__device__ __forceinline__
-#else
-__device__ __noinline__
-#endif
-float occluder_opacity(const DevScene &S, int tri, uint32_t flags, float u, float v, bool point, float pu, float pv) {
-  if (point) return eval_opacity(S, S.shade[tri].model, pu != pu, pu, pv);  // the PRIMARY hit's uv / variant (mod.rs:324)
-  if (flags & TRI_FLAG_ALPHA) return hit_opacity(S, tri, u, v);
-  return S.materials[S.shade[tri].model].opacity;
-}
-
 #ifndef PTB_SHADOW_ORDERED
 // 1: k_shadow visits the children of a node nearest-first.  Measured (profiles/r07/ab_s1.jsonl): k_shadow +19 % on the
 // console scene, +7 % on foliage, +10 % on city — the sorting network costs more than finding an occluder earlier
@@ -246,19 +230,11 @@ float occluder_opacity(const DevScene &S, int tri, uint32_t flags, float u, floa
 #define PTB_SHADOW_CACHE 0
 #endif
 
-// What the shadow walk needs from the ray's queue record besides the ray itself, and only when a primitive is hit:
-// kept in memory (k_shadow re-reads the record) instead of in eight registers of every lane.
-struct ShadowRec {
-  float limit;  // < 0: directional light; else the point light's distance from the primary hit
-  V3 pos;       // primary hit position
-  float pu, pv; // primary hit texture coordinates (pu NaN: the primary hit is a sphere)
-};
-
 struct ShadowTrav {
   Ray r;
   RayPre pre;
-  float t_max, tr;
-  bool point;
+  float t_max, limit, pu, pv, tr;
+  V3 pos;
   uint32_t cur;
   int sp;
   uint32_t occluder;  // leaf-order index of the opaque triangle that ended this walk (valid when it did)
@@ -266,12 +242,15 @@ struct ShadowTrav {
   // limit < 0: directional light (every hit on the ray, occluder sampled at its own uv, mod.rs:291-297)
   // limit >= 0: point light at distance `limit` from the primary hit `p`; occluders farther than the light are
   // ignored and the occluder's material is sampled with the PRIMARY hit's uv/variant (mod.rs:319-329, u NaN = sphere)
-  __device__ __forceinline__ void begin(const Ray &ray, float lim, V3 p) {
+  __device__ __forceinline__ void begin(const Ray &ray, float lim, V3 p, float u, float v) {
     r = ray;
     pre = precompute(ray);
-    point = lim >= 0.0f;
+    limit = lim;
+    pos = p;
+    pu = u;
+    pv = v;
     t_max = CUDART_INF_F;
-    if (point) {
+    if (lim >= 0.0f) {
 #if PTB_FAST_INV
       // a culling bound with a 2e-4 allowance: approximate square roots and division are enough (the exact
       // `distance > limit` test of mod.rs:319-330 is applied per hit in leaf_step)
@@ -295,17 +274,15 @@ struct ShadowTrav {
   __device__ __forceinline__ bool at_leaf() const { return (cur & 0x80000000u) && cur != DONE; }
   __device__ __forceinline__ void pop(const uint32_t *stk) { cur = (tr == 0.0f || sp == 0) ? DONE : stk[--sp]; }
   // After begin(): if the ray hits opaque triangle `tri` (leaf order) within the light's reach, the walk is over.
-  template <typename RecFn>
-  __device__ __forceinline__ void try_cached(const DevScene &S, uint32_t tri, RecFn rec) {
+  __device__ __forceinline__ void try_cached(const DevScene &S, uint32_t tri) {
     const float4 *tp = reinterpret_cast<const float4 *>(S.tris + tri);
     const float4 A = __ldg(tp), B = __ldg(tp + 1), C = __ldg(tp + 2);
     if (!(__float_as_uint(C.w) & TRI_FLAG_OPAQUE1)) return;
     float t, u, v, det;
     if (!moller_trumbore(r, mk3(A.x, A.y, A.z), mk3(B.x, B.y, B.z), mk3(C.x, C.y, C.z), t, u, v, det)) return;
-    if (point) {
-      const ShadowRec R = rec();
+    if (limit >= 0.0f) {
       const V3 p = r.o + r.d * t;
-      if (length3(p - R.pos) > R.limit) return;
+      if (length3(p - pos) > limit) return;
     }
     tr = 0.0f;
     cur = DONE;
@@ -359,24 +336,21 @@ struct ShadowTrav {
 #endif
     pop(stk);
   }
-  // One primitive per step (see ClosestTrav::leaf_step).  rec() fetches the ShadowRec of the ray when a hit needs it.
-  template <typename RecFn>
-  __device__ __forceinline__ void leaf_step(const DevScene &S, const uint32_t *stk, RecFn rec) {
+  // One primitive per step (see ClosestTrav::leaf_step).
+  __device__ __forceinline__ void leaf_step(const DevScene &S, const uint32_t *stk) {
+    const bool point = limit >= 0.0f;
     if (cur & 0x40000000u) {
       const DevSphere s = S.spheres[cur & 0x3FFFFFFFu];
       float dist[2], tp[2];
       int exit_only = 0;
       int nh = sphere_hits(r, s, dist, tp, exit_only);
-      if (nh) {
-        const ShadowRec R = rec();
-        for (int k = 0; k < nh; ++k) {
-          if (point) {
-            V3 p = r.o + r.d * tp[k];
-            if (length3(p - R.pos) > R.limit) continue;
-          }
-          float op = point ? eval_opacity(S, s.model, R.pu != R.pu, R.pu, R.pv) : S.materials[s.model].opacity;
-          tr *= 1.0f - op;
+      for (int k = 0; k < nh; ++k) {
+        if (point) {
+          V3 p = r.o + r.d * tp[k];
+          if (length3(p - pos) > limit) continue;
         }
+        float op = point ? eval_opacity(S, s.model, pu != pu, pu, pv) : S.materials[s.model].opacity;
+        tr *= 1.0f - op;
       }
       pop(stk);
       return;
@@ -386,19 +360,22 @@ struct ShadowTrav {
     float t, u, v, det;
     if (moller_trumbore(r, mk3(A.x, A.y, A.z), mk3(B.x, B.y, B.z), mk3(C.x, C.y, C.z), t, u, v, det)) {
       const uint32_t flags = __float_as_uint(C.w);
-      ShadowRec R{};
-      if (point) R = rec();
       bool counted = true;
       if (point) {
         V3 p = r.o + r.d * t;
-        counted = !(length3(p - R.pos) > R.limit);
+        counted = !(length3(p - pos) > limit);
       }
       if (counted) {
         if (flags & TRI_FLAG_OPAQUE1) {
           tr = 0.0f;  // opacity is exactly 1 whatever uv it is sampled at: tr * (1 - 1); no material fetch
           occluder = (cur & 0x3FFFFFFFu) >> 3;
         } else {
-          tr *= 1.0f - occluder_opacity(S, __float_as_int(B.w), flags, u, v, point, R.pu, R.pv);
+          const int tri = __float_as_int(B.w);
+          float op;
+          if (point) op = eval_opacity(S, S.shade[tri].model, pu != pu, pu, pv);
+          else if (flags & TRI_FLAG_ALPHA) op = hit_opacity(S, tri, u, v);
+          else op = S.materials[S.shade[tri].model].opacity;
+          tr *= 1.0f - op;
         }
       }
     }
@@ -429,13 +406,11 @@ __device__ __forceinline__ float trace_transmittance(const DevScene &S, const Ra
                                                      float pv) {
   uint32_t stk[PTB_STACK];
   ShadowTrav tv;
-  tv.begin(r, limit, pos);
+  tv.begin(r, limit, pos, pu, pv);
   const NodeOrder no = node_order(tv.r, tv.pre);
-  const ShadowRec R{limit, pos, pu, pv};
-  auto rec = [&]() { return R; };
   while (tv.cur != ShadowTrav::DONE) {
     if (tv.at_inner()) tv.node_step(S, no, stk);
-    else tv.leaf_step(S, stk, rec);
+    else tv.leaf_step(S, stk);
   }
   return tv.tr;
 }
