@@ -192,6 +192,18 @@ int pt_trace_closest(const pt_scene *scene, const float *rays, size_t n, pt_hit 
  * (a cudaStream_t passed as void*; NULL = default stream). */
 int pt_trace_closest_device(const pt_scene *scene, const float *rays_dev, size_t n, pt_hit *out_dev,
                             void *stream);
+/* pt_trace_closest_device for callers that cannot allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same inputs, same results (bit-identical: the same k_extend kernel), but the per-ray wave scratch lives in a static
+ * device array of the library - 48 bytes per ray for PT_TRACE_NOALLOC_MAX_RAYS rays + 256 B = 3 MiB + 256 B held on
+ * every GPU that loads the library until exit - so the call makes no cudaMalloc / cudaFree / allocating library call.
+ * n > PT_TRACE_NOALLOC_MAX_RAYS fails with PT_ERR_INVALID (pt_last_error names the limit); nothing is launched.
+ * All calls on a GPU, whatever the scene, share the one array: calls on the same stream are ordered, calls that
+ * overlap on the GPU (different streams, no dependency between them) race and return garbage.  Asynchronous on
+ * `stream` like pt_trace_closest_device. */
+#define PT_TRACE_NOALLOC_MAX_RAYS 65536
+int pt_trace_closest_device_noalloc(const pt_scene *scene, const float *rays_dev, size_t n, pt_hit *out_dev,
+                                    void *stream);
 /* The hit render_pixel shades after its alpha walk (renderer/mod.rs:188-205): the first hit of the sorted list with
  * opacity >= 1, or with opacity > 0.001 and a uniform draw below it; the farthest hit when none is accepted.  Ray i
  * uses the draws of path (pixel = i, sample, seed) at `bounce` (the Philox addressing of DESIGN.md).  n < 2^31. */

@@ -20,7 +20,7 @@ _LIB = None
 
 EXPORTS = ["pt_last_error", "pt_device_count", "pt_profile_default", "pt_profile_load_yaml", "pt_scene_load_isf",
            "pt_scene_create", "pt_scene_synthetic", "pt_scene_destroy", "pt_set_accel_builder", "pt_scene_accel_info", "pt_scene_upload", "pt_set_kernel_timing", "pt_scene_get_desc", "pt_scene_info",
-           "pt_trace_closest", "pt_trace_closest_device", "pt_trace_accepted", "pt_trace_shadow", "pt_trace_transmittance",
+           "pt_trace_closest", "pt_trace_closest_device", "pt_trace_closest_device_noalloc", "pt_trace_accepted", "pt_trace_shadow", "pt_trace_transmittance",
            "pt_triangle_intersect", "pt_philox4x32_10",
            "pt_trace_paths", "pt_render_accum_device", "pt_aov_name", "pt_debug_textures", "pt_render_progressive", "pt_convert_gltf", "pt_scene_save_binary",
            "pt_tonemap_device", "pt_render", "pt_render_async", "pt_stream_synchronize", "pt_scene_replicate", "pt_render_multi", "pt_write_png", "pt_read_png", "pt_free"]
@@ -62,6 +62,7 @@ def lib():
         L.pt_scene_info.argtypes = [vp, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]
         L.pt_trace_closest.argtypes = [vp, vp, C.c_size_t, vp]
         L.pt_trace_closest_device.argtypes = [vp, vp, C.c_size_t, vp, vp]
+        L.pt_trace_closest_device_noalloc.argtypes = [vp, vp, C.c_size_t, vp, vp]
         L.pt_trace_transmittance.argtypes = [vp, vp, C.c_size_t, vp]
         L.pt_trace_accepted.argtypes = [vp, vp, C.c_size_t, u32, u32, u64, vp]
         L.pt_trace_shadow.argtypes = [vp, vp, vp, vp, C.c_size_t, vp]
@@ -101,6 +102,7 @@ def device_count():
 
 
 ACCEL_SAH, ACCEL_LBVH, ACCEL_AUTO, ACCEL_PLOC = 0, 1, 2, 3
+TRACE_NOALLOC_MAX_RAYS = 65536  # PT_TRACE_NOALLOC_MAX_RAYS of include/pt_b200.h
 
 
 def set_accel_builder(accel):
@@ -239,6 +241,15 @@ class Scene:
         out = np.zeros(rays.shape[0], HIT_DTYPE)
         _check(lib().pt_trace_closest(self.h, rays.ctypes.data, rays.shape[0], out.ctypes.data))
         return out
+
+    # device pointers (e.g. torch_tensor.data_ptr()) on the scene's device: n*6 float32 rays in, n pt_hit (16 B) out;
+    # asynchronous on `stream` (a raw cudaStream_t value, None = default stream)
+    def trace_closest_device(self, rays_ptr, n, out_ptr, stream=None):
+        _check(lib().pt_trace_closest_device(self.h, rays_ptr, n, out_ptr, stream))
+
+    # the same with the wave scratch in the library's static device array: no allocation, n <= TRACE_NOALLOC_MAX_RAYS
+    def trace_closest_device_noalloc(self, rays_ptr, n, out_ptr, stream=None):
+        _check(lib().pt_trace_closest_device_noalloc(self.h, rays_ptr, n, out_ptr, stream))
 
     def trace_transmittance(self, rays):
         rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)

@@ -9,6 +9,7 @@
 //   k_resolve  renderer/mod.rs:130 ; k_tonemap renderer/mod.rs:150-162,335-353
 #include <atomic>
 #include <cstdlib>
+#include <mutex>
 
 #include "kernels.cuh"
 #include "traverse.cuh"
@@ -990,6 +991,68 @@ void launch_accum_add(float *dst, const float *src, uint32_t n, cudaStream_t st)
 }
 void launch_tonemap(const float *accum, uint32_t npix, uint32_t total_samples, int tonemap, uint8_t *rgb8, cudaStream_t st) {
   k_tonemap<<<(npix * 3 + 255) / 256, 256, 0, st>>>(accum, npix, (float)total_samples, tonemap, rgb8);
+}
+
+// ------------------------------------------------------------------------------------------------
+// pt_trace_closest_device_noalloc: the closest-hit batch of pt_trace_closest_device for callers that must not allocate
+// (CUDA graph capture, serving loops).  k_extend needs wave scratch per ray - the queue record (origin, direction +
+// slot) it reads, the internal hit record it writes beside the public one - plus the queue counters; here that
+// scratch is a file-scope device array instead of the scene's cudaMalloc'ed wave arena: 48 bytes per ray for at most
+// PT_TRACE_NOALLOC_MAX_RAYS rays + 256 bytes of counters = 3 MiB + 256 B, held by every GPU that loads the library
+// until the process exits.  Every call (any scene, any stream) uses the same array, so calls that overlap on the GPU
+// race; calls on one stream are ordered.  The array keeps the previous call's contents: the counters are cleared on
+// the stream before the batch is loaded, the ray records of [0, n) are rewritten, the rest is never read.
+constexpr size_t TRACE_STATIC_CTR_BYTES = 256;  // CTR_COUNT uint32 counters, padded to the array's alignment
+static_assert(CTR_COUNT * sizeof(uint32_t) <= TRACE_STATIC_CTR_BYTES, "counter block too small");
+constexpr size_t TRACE_STATIC_BYTES = TRACE_STATIC_CTR_BYTES + 3 * sizeof(float4) * (size_t)PT_TRACE_NOALLOC_MAX_RAYS;
+static __device__ __align__(256) unsigned char g_trace_scratch[TRACE_STATIC_BYTES];
+
+// In host code `g_trace_scratch` is only a handle of the symbol: its device address comes from cudaGetSymbolAddress,
+// looked up once per device with that device current (each device has its own instance of the array).
+static cudaError_t trace_scratch_address(unsigned char **out) {
+  static std::mutex mu;
+  static unsigned char *addr[MAX_DEVICES];
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= MAX_DEVICES) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> hold(mu);
+  if (!addr[dev]) {
+    void *p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_trace_scratch);
+    if (e != cudaSuccess) return e;
+    if (!p) return cudaErrorInvalidSymbol;
+    addr[dev] = static_cast<unsigned char *>(p);
+  }
+  *out = addr[dev];
+  return cudaSuccess;
+}
+
+// Current device = the scene's.  No allocation: one memset node, k_load_rays and the production k_extend on `st`.
+cudaError_t launch_trace_closest_static(const DevScene &S, const float *rays_dev, uint32_t n, pt_hit *out_dev, cudaStream_t st) {
+  if (n == 0) return cudaSuccess;
+  if (n > (uint32_t)PT_TRACE_NOALLOC_MAX_RAYS) return cudaErrorInvalidValue;
+  unsigned char *base = nullptr;
+  cudaError_t e = trace_scratch_address(&base);
+  if (e != cudaSuccess) return e;
+  float4 *rec = reinterpret_cast<float4 *>(base + TRACE_STATIC_CTR_BYTES);
+  WaveState W{};
+  W.counters = reinterpret_cast<uint32_t *>(base);
+  W.ray_o[0] = W.ray_o[1] = rec;
+  W.ray_d[0] = W.ray_d[1] = rec + (size_t)PT_TRACE_NOALLOC_MAX_RAYS;
+  W.hit = rec + 2 * (size_t)PT_TRACE_NOALLOC_MAX_RAYS;
+  W.capacity = (uint32_t)PT_TRACE_NOALLOC_MAX_RAYS;
+  WaveParams P{};
+  P.width = 0x80000000u;  // make_key: pixel = slot (not used without the alpha walk)
+  P.height = 1;
+  P.spp_in_wave = 1;
+  P.sample_stride = 1;
+  P.n_paths = n;
+  e = cudaMemsetAsync(base, 0, TRACE_STATIC_CTR_BYTES, st);  // queue sizes, work cursor, statistics of the last call
+  if (e != cudaSuccess) return e;
+  launch_load_rays(rays_dev, n, 0, W, 0, st);
+  launch_extend(S, P, W, 0, false, out_dev, st);
+  return cudaGetLastError();
 }
 
 }  // namespace ptb

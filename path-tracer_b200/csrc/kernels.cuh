@@ -26,4 +26,7 @@ void launch_shadow(const DevScene &S, const WaveState &W, uint32_t bounce, cudaS
 void launch_resolve(const WaveParams &P, const WaveState &W, float *accum, cudaStream_t st);
 void launch_accum_add(float *dst, const float *src, uint32_t n, cudaStream_t st);
 void launch_tonemap(const float *accum, uint32_t npix, uint32_t total_samples, int tonemap, uint8_t *rgb8, cudaStream_t st);
+// pt_trace_closest_device_noalloc: closest hits of n <= PT_TRACE_NOALLOC_MAX_RAYS rays with the wave scratch in a
+// static device array (kernels.cu); allocates nothing
+cudaError_t launch_trace_closest_static(const DevScene &S, const float *rays_dev, uint32_t n, pt_hit *out_dev, cudaStream_t st);
 }  // namespace ptb

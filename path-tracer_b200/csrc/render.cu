@@ -630,6 +630,27 @@ int pt_trace_closest_device(const pt_scene *sc, const float *rays_dev, size_t n,
   return trace_closest_dev(const_cast<pt_scene *>(sc), rays_dev, n, 0, out_dev, false, 0, 0, 0, (cudaStream_t)stream);
 }
 
+// The same query without any allocation: the wave scratch is the static device array of kernels.cu (3 MiB + 256 B per
+// GPU) instead of the scene's wave arena, so n is limited and overlapping calls race (include/pt_b200.h).
+int pt_trace_closest_device_noalloc(const pt_scene *sc, const float *rays_dev, size_t n, pt_hit *out_dev, void *stream) {
+  if (!sc || (n && (!rays_dev || !out_dev))) {
+    set_error("bad argument");
+    return PT_ERR_INVALID;
+  }
+  if (n > (size_t)PT_TRACE_NOALLOC_MAX_RAYS) {
+    set_error("pt_trace_closest_device_noalloc: n = %zu exceeds PT_TRACE_NOALLOC_MAX_RAYS = %d (the static scratch array); "
+              "split the batch or use pt_trace_closest_device", n, PT_TRACE_NOALLOC_MAX_RAYS);
+    return PT_ERR_INVALID;
+  }
+  if (n == 0) return PT_OK;
+  if (sc->device < 0) return no_device();
+  DeviceGuard g(sc->device);
+  pt_scene *msc = const_cast<pt_scene *>(sc);
+  WaveLock lock(msc, (cudaStream_t)stream);  // ordering against pt_scene_upload and the scene's other users; no allocation
+  CUDA_TRY(launch_trace_closest_static(msc->dev, rays_dev, (uint32_t)n, out_dev, (cudaStream_t)stream));
+  return PT_OK;
+}
+
 // Host-pointer batches: staged chunk by chunk through buffers cached on the scene.
 static int trace_closest_host(const pt_scene *csc, const float *rays, size_t n, pt_hit *out, bool alpha, uint32_t bounce,
                               uint32_t sample, uint64_t seed) {
