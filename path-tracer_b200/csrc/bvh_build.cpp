@@ -293,4 +293,68 @@ void build_bvh4(const HostScene &s, Bvh4 &out, int threads) {
   }
 }
 
+// Bvh4Node -> Bvh4QNode (scene_host.hpp).  Per axis: step = (extent of the union of the child boxes) / 250 rounded up,
+// origin two steps below the union, so every plane lands in 1..254 after the guard.
+void quantise_bvh4(const Bvh4 &bvh, uint32_t empty_ref, int threads, std::vector<Bvh4QNode> &out) {
+  const size_t n = bvh.nodes.size();
+  out.assign(n, Bvh4QNode{});
+  auto work = [&](size_t begin, size_t end) {
+    for (size_t i = begin; i < end; ++i) {
+      const Bvh4Node &nd = bvh.nodes[i];
+      Bvh4QNode qn{};
+      const float *lo[3] = {nd.lo_x, nd.lo_y, nd.lo_z}, *hi[3] = {nd.hi_x, nd.hi_y, nd.hi_z};
+      for (int a = 0; a < 3; ++a) {
+        double nlo = INFINITY, nhi = -INFINITY;
+        for (int k = 0; k < 4; ++k)
+          if (nd.child[k] != BVH_EMPTY) {
+            nlo = std::min(nlo, (double)lo[a][k]);
+            nhi = std::max(nhi, (double)hi[a][k]);
+          }
+        if (!(nlo <= nhi)) nlo = nhi = 0.0;  // no children (cannot happen in a built tree)
+        const double mag = std::max(std::fabs(nlo), std::fabs(nhi));
+        double step_d = std::max((nhi - nlo) / 250.0, mag * 0x1p-18 + 1e-30);  // >= 32 ulp of the coordinate
+        float step = std::nextafterf((float)step_d, INFINITY);
+        float origin = std::nextafterf((float)(nlo - 2.0 * (double)step), -INFINITY);
+        uint32_t wlo = 0, whi = 0;
+        int tries = 0;
+        for (bool fits = false; !fits;) {  // repeats only if a plane left 0..255 (never, given the two spare steps)
+          fits = ++tries > 200;  // non-finite boxes (rejected by HostScene::finalize) must not hang the build
+          if (fits) break;
+          fits = true;
+          wlo = whi = 0;
+          for (int k = 0; k < 4; ++k) {
+            int ql = 255, qh = 0;
+            if (nd.child[k] != BVH_EMPTY) {
+              ql = (int)std::floor(((double)lo[a][k] - (double)origin) / (double)step - 0.05);
+              qh = (int)std::ceil(((double)hi[a][k] - (double)origin) / (double)step + 0.05);
+              if (ql < 0 || qh > 255) fits = false;
+              // the decoded planes must enclose the float box with most of the guard left
+              if ((double)origin + ql * (double)step > (double)lo[a][k] - 0.04 * (double)step ||
+                  (double)origin + qh * (double)step < (double)hi[a][k] + 0.04 * (double)step)
+                fits = false;
+            }
+            wlo |= (uint32_t)(ql & 255) << (8 * k);
+            whi |= (uint32_t)(qh & 255) << (8 * k);
+          }
+          if (!fits) {
+            step = std::nextafterf(step * 1.01f, INFINITY);
+            origin = std::nextafterf((float)(nlo - 2.0 * (double)step), -INFINITY);
+          }
+        }
+        qn.origin[a] = origin;
+        qn.scale[a] = step * 32768.0f;  // exact (power of two)
+        qn.q[2 * a] = wlo;
+        qn.q[2 * a + 1] = whi;
+      }
+      for (int k = 0; k < 4; ++k) qn.child[k] = nd.child[k] == BVH_EMPTY ? empty_ref : nd.child[k];
+      out[i] = qn;
+    }
+  };
+  const int nt = (int)std::max<size_t>(1, std::min<size_t>((size_t)std::max(1, threads), n / 4096 + 1));
+  std::vector<std::thread> pool;
+  for (int t = 0; t < nt; ++t) pool.emplace_back(work, n * t / nt, n * (t + 1) / nt);
+  for (auto &th : pool) th.join();
+}
+
+
 }  // namespace ptb

@@ -56,8 +56,25 @@ struct DevNode {  // == ptb::Bvh4Node, one 128-byte line = four 32-byte chunks: 
   uint4 pad;
 };
 
+// PTB_QNODE 1: the traversal kernels read the 64-byte quantised node (== ptb::Bvh4QNode, scene_host.hpp) - two
+// 256-bit loads per node visit instead of four; 0: the 128-byte float node.
+// Measured (profiles/r07/ab_s19_quantised_nodes.jsonl, all 104 GPU parity tests green on the quantised nodes):
+// k_extend +22 % on console, +10 % on foliage, +30 % on city; k_shadow +7 % / +5 % / +13 %.  Halving the node's load
+// instructions does not pay for the 24 byte permutes + 9 per-node set-up operations of the decode, three more spilled
+// registers and the looser boxes (steps of 1/250 of the parent's extent).  Off; the float node stays.
+#ifndef PTB_QNODE
+#define PTB_QNODE 0
+#endif
+struct DevQNode {
+  float ox, oy, oz, sx, sy, sz;             // origin, step * 2^15 per axis
+  uint32_t qlx, qhx, qly, qhy, qlz, qhz;    // byte k = child slot k
+  uint4 child;
+};
+static_assert(sizeof(DevQNode) == 64, "quantised node layout");
+
 struct DevScene {
-  const DevNode *nodes;
+  const DevNode *nodes;    // float nodes (PTB_QNODE 0 builds only; null otherwise)
+  const DevQNode *qnodes;  // quantised nodes
   const DevTri *tris;
   const DevTriShade *shade;
   const DevSphere *spheres;
@@ -71,6 +88,7 @@ struct DevScene {
   uint32_t root_is_valid;
   uint32_t tree_depth;  // levels of 4-wide nodes (host-side launch heuristics only)
   uint32_t any_alpha;  // some material may be non-opaque
+  uint32_t f32_one_bits;  // 0x3F800000, kept in the parameter bank so that the plane decode (isect.cuh qplane) reads it as a constant-bank operand and its byte selector stays an immediate
   float camera[16];
   float fov;
   float tan_half_fov;  // (fov / 2).tan() of mod.rs:117,121, evaluated once on the host

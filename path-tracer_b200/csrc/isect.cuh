@@ -149,18 +149,44 @@ __device__ __forceinline__ NodeOrder node_order(const Ray &r, const RayPre &p) {
   n.oiz = -(r.o.z * p.iz);
   return n;
 }
+#ifndef PTB_SLAB_FOLD
+#define PTB_SLAB_FOLD 1
+#endif
+__device__ __forceinline__ float fmin_nan(float a, float b) {
+  float r;
+  asm("min.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+  return r;
+}
+// The slab test on the six plane parameters of a box: entry parameter, or +inf when the ray misses the box within
+// [0, t_max].  Empty child slots of the float node carry NaN planes (bvh_build.cpp, lbvh.cu): every t is NaN, fminf /
+// fmaxf then leave tf = NaN and the comparison is false, so no test of the child reference is needed.
+__device__ __forceinline__ bool slab_test(float t0x, float t1x, float t0y, float t1y, float t0z, float t1z, float t_max,
+                                          float &tn) {
+  tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.0f));
+  const float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
+#if PTB_SLAB_FOLD
+  // one comparison: the widened exit and the pruning bound are merged with a NaN-propagating minimum first (an empty
+  // slot's NaN exit must survive the merge for the comparison to fail)
+  return tn <= fmin_nan(__fmaf_rn(tf, 1.000002f, 1e-7f), t_max);
+#else
+  return tn <= __fmaf_rn(tf, 1.000002f, 1e-7f) && tn <= t_max;
+#endif
+}
 __device__ __forceinline__ float slab_fma(float lox, float loy, float loz, float hix, float hiy, float hiz, const RayPre &p,
                                           const NodeOrder &n, float t_max, uint32_t child) {
-  float t0x = __fmaf_rn(lox, p.ix, n.oix), t1x = __fmaf_rn(hix, p.ix, n.oix);
-  float t0y = __fmaf_rn(loy, p.iy, n.oiy), t1y = __fmaf_rn(hiy, p.iy, n.oiy);
-  float t0z = __fmaf_rn(loz, p.iz, n.oiz), t1z = __fmaf_rn(hiz, p.iz, n.oiz);
-  float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.0f));
-  float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
-  // Empty child slots carry NaN planes (bvh_build.cpp, lbvh.cu): every t is NaN, fminf/fmaxf then leave tf = NaN and the
-  // first comparison is false, so no test of `child` against the empty marker is needed.
   (void)child;
-  bool hit = tn <= __fmaf_rn(tf, 1.000002f, 1e-7f) && tn <= t_max;
+  float tn;
+  const bool hit = slab_test(__fmaf_rn(lox, p.ix, n.oix), __fmaf_rn(hix, p.ix, n.oix), __fmaf_rn(loy, p.iy, n.oiy),
+                             __fmaf_rn(hiy, p.iy, n.oiy), __fmaf_rn(loz, p.iz, n.oiz), __fmaf_rn(hiz, p.iz, n.oiz), t_max, tn);
   return hit ? tn : CUDART_INF_F;
+}
+// The same test as a predicate (any-hit walks need no entry distance).  Conservative like slab_fma: a ray with
+// non-finite slab parameters may be let into a box it misses, never kept out of one it hits.
+__device__ __forceinline__ bool slab_hit(float lox, float loy, float loz, float hix, float hiy, float hiz, const RayPre &p,
+                                         const NodeOrder &n, float t_max) {
+  float tn;
+  return slab_test(__fmaf_rn(lox, p.ix, n.oix), __fmaf_rn(hix, p.ix, n.oix), __fmaf_rn(loy, p.iy, n.oiy),
+                   __fmaf_rn(hiy, p.iy, n.oiy), __fmaf_rn(loz, p.iz, n.oiz), __fmaf_rn(hiz, p.iz, n.oiz), t_max, tn);
 }
 
 // One node = four 256-bit read-only loads (LDG.E.256): a lane whose ray is alone in its node touches the node's
@@ -185,12 +211,86 @@ __device__ __forceinline__ NodeData load_node(const DevNode *nodes, uint32_t idx
   return n;
 }
 
+// The quantised node (DevQNode): two 256-bit loads.  Plane byte q of child K decodes to origin + q * step; its slab
+// parameter (origin + q step - o) * inv is evaluated as fma(1 + q 2^-15, A, B) with A = (step 2^15) * inv and
+// B = (origin - o) * inv - A per axis and node, and the float 1 + q 2^-15 built from the byte by one byte permute
+// (0x3F80qq00): no integer-to-float conversion, one PRMT per plane.  Rounding: 2^-8 step (scene_host.hpp keeps a guard
+// of 0.05 step) plus the rounding of o * inv that the float node had as well.
+struct QNodeData {
+  float ox, oy, oz, sx, sy, sz;
+  uint32_t qlx, qhx, qly, qhy, qlz, qhz;
+  uint4 ch;
+};
+__device__ __forceinline__ QNodeData load_qnode(const DevQNode *nodes, uint32_t idx) {
+  const char *p = reinterpret_cast<const char *>(nodes + idx);
+  QNodeData n;
+  uint32_t a0, a1, a2, a3, a4, a5;
+  asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(a0), "=r"(a1), "=r"(a2), "=r"(a3), "=r"(a4), "=r"(a5), "=r"(n.qlx), "=r"(n.qhx)
+               : "l"(p));
+  asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(n.qly), "=r"(n.qhy), "=r"(n.qlz), "=r"(n.qhz), "=r"(n.ch.x), "=r"(n.ch.y), "=r"(n.ch.z), "=r"(n.ch.w)
+               : "l"(p + 32));
+  n.ox = __uint_as_float(a0);
+  n.oy = __uint_as_float(a1);
+  n.oz = __uint_as_float(a2);
+  n.sx = __uint_as_float(a3);
+  n.sy = __uint_as_float(a4);
+  n.sz = __uint_as_float(a5);
+  return n;
+}
+struct QNodeRay {  // A and B of the three axes for one (ray, node) pair
+  float ax, ay, az, bx, by, bz;
+  uint32_t one;  // DevScene::f32_one_bits
+};
+__device__ __forceinline__ QNodeRay qnode_ray(const QNodeData &n, const RayPre &p, const NodeOrder &o, uint32_t one) {
+  QNodeRay r;
+  r.one = one;
+  r.ax = n.sx * p.ix;
+  r.ay = n.sy * p.iy;
+  r.az = n.sz * p.iz;
+  r.bx = __fmaf_rn(n.ox, p.ix, o.oix) - r.ax;
+  r.by = __fmaf_rn(n.oy, p.iy, o.oiy) - r.ay;
+  r.bz = __fmaf_rn(n.oz, p.iz, o.oiz) - r.az;
+  return r;
+}
+template <int K>
+__device__ __forceinline__ float qplane(uint32_t w, uint32_t one) {  // 1 + q 2^-15, q = byte K of w
+  return __uint_as_float(__byte_perm(w, one, 0x7604u | (K << 4)));
+}
+template <int K>
+__device__ __forceinline__ bool qslab_test(const QNodeData &n, const QNodeRay &r, float t_max, float &tn) {
+  return slab_test(__fmaf_rn(qplane<K>(n.qlx, r.one), r.ax, r.bx), __fmaf_rn(qplane<K>(n.qhx, r.one), r.ax, r.bx),
+                   __fmaf_rn(qplane<K>(n.qly, r.one), r.ay, r.by), __fmaf_rn(qplane<K>(n.qhy, r.one), r.ay, r.by),
+                   __fmaf_rn(qplane<K>(n.qlz, r.one), r.az, r.bz), __fmaf_rn(qplane<K>(n.qhz, r.one), r.az, r.bz), t_max, tn);
+}
+template <int K>
+__device__ __forceinline__ float qslab(const QNodeData &n, const QNodeRay &r, float t_max) {
+  float tn;
+  return qslab_test<K>(n, r, t_max, tn) ? tn : CUDART_INF_F;
+}
+
 #define PTB_STACK 96
 
+#ifndef PTB_CSWAP_SELECT
+#define PTB_CSWAP_SELECT 1
+#endif
+#if PTB_CSWAP_SELECT
+// branch-free exchange: one comparison, min / max of the keys, two selects of the references (the entry distances
+// are never NaN here: misses are +inf)
+#define PTB_CSWAP(ta, ra, tb, rb)                    \
+  {                                                  \
+    const bool _p = tb < ta;                         \
+    const float _lo = fminf(ta, tb), _hi = fmaxf(ta, tb); \
+    const uint32_t _rl = _p ? rb : ra, _rh = _p ? ra : rb; \
+    ta = _lo; tb = _hi; ra = _rl; rb = _rh;          \
+  }
+#else
 #define PTB_CSWAP(ta, ra, tb, rb) \
   if (tb < ta) {                  \
     float _t = ta; ta = tb; tb = _t; \
     uint32_t _r = ra; ra = rb; rb = _r; \
   }
+#endif
 
 }  // namespace ptb

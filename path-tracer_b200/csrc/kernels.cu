@@ -766,7 +766,7 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
   constexpr uint32_t NONE = 0xFFFFFFFFu;
   ShadowTrav tv;
   NodeOrder no{};
-  uint32_t stk[PTB_STACK];
+  uint32_t stk[PTB_STACK + 1];  // + the sentinel
   uint32_t q = NONE, slot = 0;
   V3 c{};
   tv.cur = ShadowTrav::DONE;
@@ -802,7 +802,7 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
       r.d = mk3(d4.x, d4.y, d4.z);
       slot = (uint32_t)__float_as_int(d4.w);
       c = mk3(c4.x, c4.y, c4.z);
-      tv.begin(r, o4.w, mk3(p4.x, p4.y, p4.z), c4.w, p4.w);
+      tv.begin(r, o4.w, mk3(p4.x, p4.y, p4.z), c4.w, p4.w, stk);
       no = node_order(tv.r, tv.pre);
 #if PTB_SHADOW_CACHE
       tv.occluder = NONE;

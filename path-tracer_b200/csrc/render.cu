@@ -173,8 +173,12 @@ int build_device_scene(pt_scene *sc) {
     any_alpha |= material_may_be_transparent(m);
     any_normal_map |= m.normal_tex >= 0;
   }
-  std::vector<DevTri> tris(sc->bvh.leaf_tris.size());
-  for (size_t i = 0; i < tris.size(); ++i) {
+  // one extra record at the end: the degenerate triangle behind the empty child slots of the quantised nodes
+  // (all-zero edges: |det| < 1e-6 rejects it for every ray)
+  const size_t n_leaf_tris = sc->bvh.leaf_tris.size();
+  std::vector<DevTri> tris(n_leaf_tris + 1);
+  tris[n_leaf_tris].a = tris[n_leaf_tris].b = tris[n_leaf_tris].c = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (size_t i = 0; i < n_leaf_tris; ++i) {
     uint32_t t = sc->bvh.leaf_tris[i];
     const float *p = &h.pos[(size_t)t * 9];
     int model = h.tri_model[t];
@@ -224,7 +228,27 @@ int build_device_scene(pt_scene *sc) {
   DevScene &D = sc->dev;
   int rc;
   static_assert(sizeof(DevNode) == sizeof(Bvh4Node), "node layout");
-  if ((rc = upload(sc, sc->bvh.nodes, reinterpret_cast<const Bvh4Node **>(&D.nodes)))) return rc;
+  static_assert(sizeof(DevQNode) == sizeof(Bvh4QNode), "quantised node layout");
+  D.nodes = nullptr;
+  D.qnodes = nullptr;
+#if PTB_QNODE && !defined(PTB_BOTH_NODE_FORMATS)
+  const bool want_float = false, want_q = true;
+#elif PTB_QNODE
+  const bool want_float = true, want_q = true;  // A/B builds: one host library under kernels of either kind
+#else
+  const bool want_float = true, want_q = false;
+#endif
+  if (want_float)
+    if ((rc = upload(sc, sc->bvh.nodes, reinterpret_cast<const Bvh4Node **>(&D.nodes)))) return rc;
+  if (want_q) {
+    if (n_leaf_tris >= (1u << 27)) {
+      set_error("too many triangles for the leaf reference encoding");
+      return PT_ERR_INVALID;
+    }
+    std::vector<Bvh4QNode> qn;
+    quantise_bvh4(sc->bvh, BVH_LEAF | ((uint32_t)n_leaf_tris << 3), (int)std::min(hw, 32u), qn);
+    if ((rc = upload(sc, qn, reinterpret_cast<const Bvh4QNode **>(&D.qnodes)))) return rc;
+  }
   if ((rc = upload(sc, tris, &D.tris))) return rc;
   if ((rc = upload(sc, shade, &D.shade))) return rc;
   if ((rc = upload(sc, spheres, &D.spheres))) return rc;
@@ -250,6 +274,7 @@ int build_device_scene(pt_scene *sc) {
   D.root_is_valid = 1;
   D.tree_depth = (uint32_t)std::max(0, sc->bvh.max_depth);
   D.any_alpha = any_alpha ? 1u : 0u;
+  D.f32_one_bits = 0x3F800000u;
   std::memcpy(D.camera, h.camera, sizeof D.camera);
   D.fov = h.fov;
   D.tan_half_fov = std::tan(h.fov / 2.0f);  // f32 tanf of the C library == Rust's f32::tan

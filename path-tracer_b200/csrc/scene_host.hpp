@@ -128,6 +128,25 @@ PTB_HD inline float plane_pad(float lo, float hi, float S) {
 // A/B knob: $PT_B200_MARGIN_SCALE multiplies D and S (0 = the coordinate-relative rules of revision 1).
 float bvh_margin_scale();
 
+// ---- the node the traversal kernels read: 64 bytes, child boxes quantised to 8 bits per plane -------------------
+// Plane q of an axis decodes to origin + q * step (q in 0..255); `scale` stores step * 2^15 because the kernels build
+// the float 1 + q * 2^-15 from the byte with one byte permute and evaluate the slab parameter of the plane as
+// fma(1 + q 2^-15, scale * inv, (origin - o) * inv - scale * inv) (isect.cuh).  q_lo is rounded down and q_hi up with
+// a guard of 0.05 step (the rounding of that expression is 2^-8 step), so the decoded box always contains the float
+// box the builders produced (margins above) - quantisation only ever makes the filter less tight.
+// Words q[0..5] = lo_x, hi_x, lo_y, hi_y, lo_z, hi_z; byte k of a word = child slot k.  An empty slot has
+// lo = 255 > hi = 0 on every axis and child = `empty_ref`: a leaf holding one degenerate triangle that nothing can
+// hit (appended to the leaf-ordered triangle array), so a ray that passes an inverted box through rounding (flat
+// nodes, extreme directions) costs one rejected primitive test instead of a bad reference.
+struct alignas(64) Bvh4QNode {
+  float origin[3];
+  float scale[3];
+  uint32_t q[6];
+  uint32_t child[4];
+};
+static_assert(sizeof(Bvh4QNode) == 64, "quantised node is half a cache line");
+void quantise_bvh4(const Bvh4 &bvh, uint32_t empty_ref, int threads, std::vector<Bvh4QNode> &out);
+
 // Binned-SAH BVH2 build over triangles + spheres, collapsed to 4-wide.  Boxes carry the margins above
 // so a box cull can never drop a primitive Möller–Trumbore would accept.
 void build_bvh4(const HostScene &s, Bvh4 &out, int threads);

@@ -17,7 +17,7 @@ namespace ptb {
 // ((t, prim id) (u, v) (idx, -)): it is the hit that is shaded when no hit is accepted (mod.rs:188-205 leaves `hit`
 // at the last examined element), touched only when a transparent hit is rejected.
 struct ClosestStack {
-  uint2 e[PTB_STACK + 3];
+  uint2 e[PTB_STACK + 1 + 3];  // sentinel + entries + the farthest rejected hit
   __device__ __forceinline__ void put(int i, float t, uint32_t r) { e[i] = make_uint2(__float_as_uint(t), r); }
   __device__ __forceinline__ void get(int i, float &t, uint32_t &r) const {
     const uint2 v = e[i];
@@ -25,7 +25,7 @@ struct ClosestStack {
     r = v.y;
   }
 };
-constexpr int FAR_SLOT = PTB_STACK;
+constexpr int FAR_SLOT = PTB_STACK + 1;
 
 // One examined hit of the alpha walk (mod.rs:196-204): accepted when opacity >= 1, or when opacity > 0.001 and the
 // hit's own draw is below it.  Out of line: it is reached by a few lanes at a time and holds a texture fetch and ten
@@ -53,16 +53,50 @@ __device__ __noinline__ bool alpha_accepts(const DevScene &S, uint32_t pixel, ui
 #define PTB_POP_MODE_FORCED 1
 #endif
 
+// PTB_STACK_PTR 1: the traversals keep the address of the next free stack word instead of an index (a push is one
+// predicated STL + one predicated add, without the index -> address LEA of every push and pop).
+#ifndef PTB_STACK_PTR
+#define PTB_STACK_PTR 1
+#endif
+// PTB_SORT3 1: the four children are ordered by a three-exchange network instead of the full five-exchange sort: the
+// nearest child is exact (it is visited next), two entered children are pushed in exact order, three are pushed with
+// the nearer of the two pair-minima on top.  Results do not depend on the visiting order (candidate keys decide).
+// Measured (profiles/r07/ab_s18_node_step_diet.jsonl): k_extend -0.6 % on console, +8 % on foliage, +3.4 % on city -
+// the ten instructions it saves per node visit buy nothing (the kernel waits on the L1 data pipe, not on issue
+// slots), the worse visiting order costs node visits.  Off.
+#ifndef PTB_SORT3
+#define PTB_SORT3 0
+#endif
+
 struct ClosestTrav {
   Ray r;
   RayPre pre;
   TraceState st;   // nearest accepted hit so far
   float t_prune;   // slab-parameter bound derived from it
   uint32_t cur;
-  int sp;
-
   static constexpr uint32_t DONE = 0xFFFFFFFFu;
   static constexpr uint32_t NEED_POP = 0xFFFFFFFEu;  // PTB_POP_MODE != 0: the kernel's pop site takes over
+#if PTB_STACK_PTR
+  uint2 *top;      // next free stack word
+  __device__ __forceinline__ void stack_reset(ClosestStack &stk) {
+    stk.e[0] = make_uint2(0u, DONE);  // sentinel: passes every pruning test and ends the walk, so no pop tests for "empty"
+    top = stk.e + 1;
+  }
+  __device__ __forceinline__ void push(ClosestStack &, float t, uint32_t ref) { *top++ = make_uint2(__float_as_uint(t), ref); }
+  __device__ __forceinline__ void take(const ClosestStack &, float &t, uint32_t &ref) {
+    const uint2 v = *--top;
+    t = __uint_as_float(v.x);
+    ref = v.y;
+  }
+#else
+  int sp;
+  __device__ __forceinline__ void stack_reset(ClosestStack &stk) {
+    stk.put(0, 0.0f, DONE);
+    sp = 1;
+  }
+  __device__ __forceinline__ void push(ClosestStack &stk, float t, uint32_t ref) { stk.put(sp++, t, ref); }
+  __device__ __forceinline__ void take(const ClosestStack &stk, float &t, uint32_t &ref) { stk.get(--sp, t, ref); }
+#endif
 
   __device__ __forceinline__ void begin(const Ray &ray, ClosestStack &stk, bool alpha) {
     r = ray;
@@ -73,7 +107,7 @@ struct ClosestTrav {
     st.u = st.v = 0.f;
     t_prune = CUDART_INF_F;
     cur = 0;
-    sp = 0;
+    stack_reset(stk);
     if (alpha) stk.put(FAR_SLOT, -1.0f, 0xFFFFFFFFu);  // no rejected hit yet
   }
   __device__ __forceinline__ bool at_inner() const { return !(cur & 0x80000000u); }
@@ -85,45 +119,53 @@ struct ClosestTrav {
   }
   // PTB_POP_MODE 2: examine one stack entry
   __device__ __forceinline__ void pop_one(const ClosestStack &stk) {
-    if (sp == 0) {
-      cur = DONE;
-      return;
-    }
-    --sp;
     float t;
     uint32_t ref;
-    stk.get(sp, t, ref);
+    take(stk, t, ref);
     if (t <= t_prune) cur = ref;
   }
 
   // next stack entry that can still hold a nearer hit (entries behind the current best hit are skipped lazily)
   __device__ __forceinline__ void pop(const ClosestStack &stk) {
-    while (sp > 0) {
-      --sp;
+    for (;;) {  // ends at the sentinel at the latest (t = 0, ref = DONE)
       float t;
       uint32_t ref;
-      stk.get(sp, t, ref);
+      take(stk, t, ref);
       if (t <= t_prune) {
         cur = ref;
         return;
       }
     }
-    cur = DONE;
   }
   // Precondition: at_inner().  Visits one node: cur becomes the nearest child hit, or the next stack entry.
   __device__ __forceinline__ void node_step(const DevScene &S, const NodeOrder &no, ClosestStack &stk, bool deferred = false) {
+#if PTB_QNODE
+    const QNodeData nd = load_qnode(S.qnodes, cur);
+    const uint4 ch = nd.ch;
+    const QNodeRay nr = qnode_ray(nd, pre, no, S.f32_one_bits);
+    float t0 = qslab<0>(nd, nr, t_prune), t1 = qslab<1>(nd, nr, t_prune);
+    float t2 = qslab<2>(nd, nr, t_prune), t3 = qslab<3>(nd, nr, t_prune);
+#else
     const NodeData nd = load_node(S.nodes, cur);
     const uint4 ch = nd.ch;
     float t0 = slab_fma(nd.lo_x.x, nd.lo_y.x, nd.lo_z.x, nd.hi_x.x, nd.hi_y.x, nd.hi_z.x, pre, no, t_prune, ch.x);
     float t1 = slab_fma(nd.lo_x.y, nd.lo_y.y, nd.lo_z.y, nd.hi_x.y, nd.hi_y.y, nd.hi_z.y, pre, no, t_prune, ch.y);
     float t2 = slab_fma(nd.lo_x.z, nd.lo_y.z, nd.lo_z.z, nd.hi_x.z, nd.hi_y.z, nd.hi_z.z, pre, no, t_prune, ch.z);
     float t3 = slab_fma(nd.lo_x.w, nd.lo_y.w, nd.lo_z.w, nd.hi_x.w, nd.hi_y.w, nd.hi_z.w, pre, no, t_prune, ch.w);
+#endif
     uint32_t r0 = ch.x, r1 = ch.y, r2 = ch.z, r3 = ch.w;
+#if PTB_SORT3
+    PTB_CSWAP(t0, r0, t1, r1) PTB_CSWAP(t2, r2, t3, r3) PTB_CSWAP(t0, r0, t2, r2)
+    if (t3 < CUDART_INF_F) push(stk, t3, r3);
+    if (t1 < CUDART_INF_F) push(stk, t1, r1);
+    if (t2 < CUDART_INF_F) push(stk, t2, r2);  // the larger of the two pair-minima: never behind both of the others
+#else
     PTB_CSWAP(t0, r0, t1, r1) PTB_CSWAP(t2, r2, t3, r3) PTB_CSWAP(t0, r0, t2, r2) PTB_CSWAP(t1, r1, t3, r3)
     PTB_CSWAP(t1, r1, t2, r2)
-    if (t3 < CUDART_INF_F) stk.put(sp++, t3, r3);
-    if (t2 < CUDART_INF_F) stk.put(sp++, t2, r2);
-    if (t1 < CUDART_INF_F) stk.put(sp++, t1, r1);
+    if (t3 < CUDART_INF_F) push(stk, t3, r3);
+    if (t2 < CUDART_INF_F) push(stk, t2, r2);
+    if (t1 < CUDART_INF_F) push(stk, t1, r1);
+#endif
     if (t0 < CUDART_INF_F) cur = r0;
     else after(stk, deferred);
   }
@@ -229,6 +271,9 @@ struct ClosestTrav {
 // shadow rays of these scenes are occluded for the extra test (and 22 B more spills) to pay.  Off.
 #define PTB_SHADOW_CACHE 0
 #endif
+#ifndef PTB_SHADOW_STACK_PTR
+#define PTB_SHADOW_STACK_PTR PTB_STACK_PTR
+#endif
 
 struct ShadowTrav {
   Ray r;
@@ -236,13 +281,30 @@ struct ShadowTrav {
   float t_max, limit, pu, pv, tr;
   V3 pos;
   uint32_t cur;
+  static constexpr uint32_t DONE = 0xFFFFFFFFu;
+#if PTB_SHADOW_STACK_PTR
+  uint32_t *top;  // next free stack word
+  __device__ __forceinline__ void stack_reset(uint32_t *stk) {
+    stk[0] = DONE;  // sentinel: popping it ends the walk
+    top = stk + 1;
+  }
+  __device__ __forceinline__ void push(uint32_t *, uint32_t ref) { *top++ = ref; }
+  __device__ __forceinline__ uint32_t take(const uint32_t *) { return *--top; }
+#else
   int sp;
+  __device__ __forceinline__ void stack_reset(uint32_t *stk) {
+    stk[0] = DONE;
+    sp = 1;
+  }
+  __device__ __forceinline__ void push(uint32_t *stk, uint32_t ref) { stk[sp++] = ref; }
+  __device__ __forceinline__ uint32_t take(const uint32_t *stk) { return stk[--sp]; }
+#endif
   uint32_t occluder;  // leaf-order index of the opaque triangle that ended this walk (valid when it did)
 
   // limit < 0: directional light (every hit on the ray, occluder sampled at its own uv, mod.rs:291-297)
   // limit >= 0: point light at distance `limit` from the primary hit `p`; occluders farther than the light are
   // ignored and the occluder's material is sampled with the PRIMARY hit's uv/variant (mod.rs:319-329, u NaN = sphere)
-  __device__ __forceinline__ void begin(const Ray &ray, float lim, V3 p, float u, float v) {
+  __device__ __forceinline__ void begin(const Ray &ray, float lim, V3 p, float u, float v, uint32_t *stk) {
     r = ray;
     pre = precompute(ray);
     limit = lim;
@@ -267,12 +329,11 @@ struct ShadowTrav {
     }
     tr = 1.0f;
     cur = 0;
-    sp = 0;
+    stack_reset(stk);
   }
-  static constexpr uint32_t DONE = 0xFFFFFFFFu;
   __device__ __forceinline__ bool at_inner() const { return !(cur & 0x80000000u); }
   __device__ __forceinline__ bool at_leaf() const { return (cur & 0x80000000u) && cur != DONE; }
-  __device__ __forceinline__ void pop(const uint32_t *stk) { cur = (tr == 0.0f || sp == 0) ? DONE : stk[--sp]; }
+  __device__ __forceinline__ void pop(const uint32_t *stk) { cur = tr == 0.0f ? DONE : take(stk); }
   // After begin(): if the ray hits opaque triangle `tri` (leaf order) within the light's reach, the walk is over.
   __device__ __forceinline__ void try_cached(const DevScene &S, uint32_t tri) {
     const float4 *tp = reinterpret_cast<const float4 *>(S.tris + tri);
@@ -289,9 +350,23 @@ struct ShadowTrav {
   }
 
   __device__ __forceinline__ void node_step(const DevScene &S, const NodeOrder &no, uint32_t *stk) {
+#if PTB_QNODE
+    const QNodeData nd = load_qnode(S.qnodes, cur);
+    const uint4 ch = nd.ch;
+    const QNodeRay nr = qnode_ray(nd, pre, no, S.f32_one_bits);
+    float tn;
+    if (qslab_test<0>(nd, nr, t_max, tn)) push(stk, ch.x);
+    if (qslab_test<1>(nd, nr, t_max, tn)) push(stk, ch.y);
+    if (qslab_test<2>(nd, nr, t_max, tn)) push(stk, ch.z);
+    if (qslab_test<3>(nd, nr, t_max, tn)) push(stk, ch.w);
+    pop(stk);
+    return;
+#else
     const NodeData nd = load_node(S.nodes, cur);
     const uint4 ch = nd.ch;
-#if PTB_SHADOW_ORDERED
+#endif
+#if PTB_QNODE
+#elif PTB_SHADOW_ORDERED
     float t0 = slab_fma(nd.lo_x.x, nd.lo_y.x, nd.lo_z.x, nd.hi_x.x, nd.hi_y.x, nd.hi_z.x, pre, no, t_max, ch.x);
     float t1 = slab_fma(nd.lo_x.y, nd.lo_y.y, nd.lo_z.y, nd.hi_x.y, nd.hi_y.y, nd.hi_z.y, pre, no, t_max, ch.y);
     float t2 = slab_fma(nd.lo_x.z, nd.lo_y.z, nd.lo_z.z, nd.hi_x.z, nd.hi_y.z, nd.hi_z.z, pre, no, t_max, ch.z);
@@ -299,15 +374,15 @@ struct ShadowTrav {
     uint32_t r0 = ch.x, r1 = ch.y, r2 = ch.z, r3 = ch.w;
     PTB_CSWAP(t0, r0, t1, r1) PTB_CSWAP(t2, r2, t3, r3) PTB_CSWAP(t0, r0, t2, r2) PTB_CSWAP(t1, r1, t3, r3)
     PTB_CSWAP(t1, r1, t2, r2)
-    if (t3 < CUDART_INF_F) stk[sp++] = r3;
-    if (t2 < CUDART_INF_F) stk[sp++] = r2;
-    if (t1 < CUDART_INF_F) stk[sp++] = r1;
-    if (t0 < CUDART_INF_F) stk[sp++] = r0;
+    if (t3 < CUDART_INF_F) push(stk, r3);
+    if (t2 < CUDART_INF_F) push(stk, r2);
+    if (t1 < CUDART_INF_F) push(stk, r1);
+    if (t0 < CUDART_INF_F) push(stk, r0);
 #elif !PTB_SHADOW_NOPUSH
-    if (slab_fma(nd.lo_x.x, nd.lo_y.x, nd.lo_z.x, nd.hi_x.x, nd.hi_y.x, nd.hi_z.x, pre, no, t_max, ch.x) < CUDART_INF_F) stk[sp++] = ch.x;
-    if (slab_fma(nd.lo_x.y, nd.lo_y.y, nd.lo_z.y, nd.hi_x.y, nd.hi_y.y, nd.hi_z.y, pre, no, t_max, ch.y) < CUDART_INF_F) stk[sp++] = ch.y;
-    if (slab_fma(nd.lo_x.z, nd.lo_y.z, nd.lo_z.z, nd.hi_x.z, nd.hi_y.z, nd.hi_z.z, pre, no, t_max, ch.z) < CUDART_INF_F) stk[sp++] = ch.z;
-    if (slab_fma(nd.lo_x.w, nd.lo_y.w, nd.lo_z.w, nd.hi_x.w, nd.hi_y.w, nd.hi_z.w, pre, no, t_max, ch.w) < CUDART_INF_F) stk[sp++] = ch.w;
+    if (slab_hit(nd.lo_x.x, nd.lo_y.x, nd.lo_z.x, nd.hi_x.x, nd.hi_y.x, nd.hi_z.x, pre, no, t_max)) push(stk, ch.x);
+    if (slab_hit(nd.lo_x.y, nd.lo_y.y, nd.lo_z.y, nd.hi_x.y, nd.hi_y.y, nd.hi_z.y, pre, no, t_max)) push(stk, ch.y);
+    if (slab_hit(nd.lo_x.z, nd.lo_y.z, nd.lo_z.z, nd.hi_x.z, nd.hi_y.z, nd.hi_z.z, pre, no, t_max)) push(stk, ch.z);
+    if (slab_hit(nd.lo_x.w, nd.lo_y.w, nd.lo_z.w, nd.hi_x.w, nd.hi_y.w, nd.hi_z.w, pre, no, t_max)) push(stk, ch.w);
 #else
     // every child the ray enters is visited (in no particular order): the last one found becomes current directly,
     // only the others go through the local-memory stack (one STL + one LDL fewer per node visit)
@@ -318,15 +393,15 @@ struct ShadowTrav {
     uint32_t nxt = DONE;
     if (h0) nxt = ch.x;
     if (h1) {
-      if (nxt != DONE) stk[sp++] = nxt;
+      if (nxt != DONE) push(stk, nxt);
       nxt = ch.y;
     }
     if (h2) {
-      if (nxt != DONE) stk[sp++] = nxt;
+      if (nxt != DONE) push(stk, nxt);
       nxt = ch.z;
     }
     if (h3) {
-      if (nxt != DONE) stk[sp++] = nxt;
+      if (nxt != DONE) push(stk, nxt);
       nxt = ch.w;
     }
     if (nxt != DONE) {
@@ -404,9 +479,9 @@ __device__ __forceinline__ void trace_closest(const DevScene &S, const Ray &r, b
 
 __device__ __forceinline__ float trace_transmittance(const DevScene &S, const Ray &r, float limit, V3 pos, float pu,
                                                      float pv) {
-  uint32_t stk[PTB_STACK];
+  uint32_t stk[PTB_STACK + 1];
   ShadowTrav tv;
-  tv.begin(r, limit, pos, pu, pv);
+  tv.begin(r, limit, pos, pu, pv, stk);
   const NodeOrder no = node_order(tv.r, tv.pre);
   while (tv.cur != ShadowTrav::DONE) {
     if (tv.at_inner()) tv.node_step(S, no, stk);
