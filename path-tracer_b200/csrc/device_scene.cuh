@@ -72,8 +72,20 @@ struct DevQNode {
 };
 static_assert(sizeof(DevQNode) == 64, "quantised node layout");
 
+// PTB_CNODE 1: the float node stores centre / half-extent per child and axis instead of lo / hi (same 128-byte layout:
+// the "lo" chunks hold the centres, the "hi" chunks the half-extents): the slab parameters of a child are
+// tm -+ |h * inv| with tm = fma(c, inv, -o * inv) - multiply-adds and adds on the FMA pipe in place of the six
+// min / max of the lo / hi form, which run on the half-rate ALU pipe.
+// Measured (profiles/r07/ab_s20_centre_half_extent_shadow_stack.jsonl): k_extend -0.7 % on console, -0.5 % on foliage,
+// +0.4 % on city; k_shadow +1.5 ... +3 %.  The ALU pipe is the busiest unit (60 % of its peak, ncu) but not the limit:
+// the kernels wait for the slowest lane's node line (L2 latency).  Off; the lo / hi node stays.
+#ifndef PTB_CNODE
+#define PTB_CNODE 0
+#endif
+
 struct DevScene {
-  const DevNode *nodes;    // float nodes (PTB_QNODE 0 builds only; null otherwise)
+  const DevNode *nodes;    // float nodes, lo / hi planes (PTB_QNODE 0 && PTB_CNODE 0 builds)
+  const DevNode *cnodes;   // float nodes, centre / half-extent (PTB_CNODE 1)
   const DevQNode *qnodes;  // quantised nodes
   const DevTri *tris;
   const DevTriShade *shade;

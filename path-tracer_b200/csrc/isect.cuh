@@ -152,6 +152,11 @@ __device__ __forceinline__ NodeOrder node_order(const Ray &r, const RayPre &p) {
 #ifndef PTB_SLAB_FOLD
 #define PTB_SLAB_FOLD 1
 #endif
+// The any-hit walk of k_shadow keeps the two comparisons: folded, it measured +4 % on console and +2 % on foliage
+// (profiles/r07/ab_s18_node_step_diet.jsonl, ab_s20_...jsonl); k_extend -2 % folded.
+#ifndef PTB_SHADOW_SLAB_FOLD
+#define PTB_SHADOW_SLAB_FOLD 0
+#endif
 __device__ __forceinline__ float fmin_nan(float a, float b) {
   float r;
   asm("min.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
@@ -160,17 +165,15 @@ __device__ __forceinline__ float fmin_nan(float a, float b) {
 // The slab test on the six plane parameters of a box: entry parameter, or +inf when the ray misses the box within
 // [0, t_max].  Empty child slots of the float node carry NaN planes (bvh_build.cpp, lbvh.cu): every t is NaN, fminf /
 // fmaxf then leave tf = NaN and the comparison is false, so no test of the child reference is needed.
+template <bool FOLD = (PTB_SLAB_FOLD != 0)>
 __device__ __forceinline__ bool slab_test(float t0x, float t1x, float t0y, float t1y, float t0z, float t1z, float t_max,
                                           float &tn) {
   tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.0f));
   const float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
-#if PTB_SLAB_FOLD
-  // one comparison: the widened exit and the pruning bound are merged with a NaN-propagating minimum first (an empty
-  // slot's NaN exit must survive the merge for the comparison to fail)
-  return tn <= fmin_nan(__fmaf_rn(tf, 1.000002f, 1e-7f), t_max);
-#else
+  // FOLD: one comparison - the widened exit and the pruning bound are merged with a NaN-propagating minimum first (an
+  // empty slot's NaN exit must survive the merge for the comparison to fail)
+  if (FOLD) return tn <= fmin_nan(__fmaf_rn(tf, 1.000002f, 1e-7f), t_max);
   return tn <= __fmaf_rn(tf, 1.000002f, 1e-7f) && tn <= t_max;
-#endif
 }
 __device__ __forceinline__ float slab_fma(float lox, float loy, float loz, float hix, float hiy, float hiz, const RayPre &p,
                                           const NodeOrder &n, float t_max, uint32_t child) {
@@ -180,12 +183,32 @@ __device__ __forceinline__ float slab_fma(float lox, float loy, float loz, float
                              __fmaf_rn(hiy, p.iy, n.oiy), __fmaf_rn(loz, p.iz, n.oiz), __fmaf_rn(hiz, p.iz, n.oiz), t_max, tn);
   return hit ? tn : CUDART_INF_F;
 }
+// Centre / half-extent form (PTB_CNODE): per axis tm = fma(c, inv, -o inv), p = h * inv, near = tm - |p|, far = tm + |p|.
+// Two roundings per parameter instead of one (~1.2e-7 relative, against the 2e-6 widening of the exit); the host
+// rounds h up so that [c - h, c + h] contains the builder's box (render.cu).  NaN centres mark empty slots.
+template <bool FOLD = (PTB_SLAB_FOLD != 0)>
+__device__ __forceinline__ bool cslab_test(float cx, float cy, float cz, float hx, float hy, float hz, const RayPre &p,
+                                           const NodeOrder &n, float t_max, float &tn) {
+  const float mx = __fmaf_rn(cx, p.ix, n.oix), my = __fmaf_rn(cy, p.iy, n.oiy), mz = __fmaf_rn(cz, p.iz, n.oiz);
+  const float px = fabsf(hx * p.ix), py = fabsf(hy * p.iy), pz = fabsf(hz * p.iz);
+  tn = fmaxf(fmaxf(mx - px, my - py), fmaxf(mz - pz, 0.0f));
+  const float tf = fminf(fminf(mx + px, my + py), mz + pz);
+  if (FOLD) return tn <= fmin_nan(__fmaf_rn(tf, 1.000002f, 1e-7f), t_max);
+  return tn <= __fmaf_rn(tf, 1.000002f, 1e-7f) && tn <= t_max;
+}
+__device__ __forceinline__ float cslab(float cx, float cy, float cz, float hx, float hy, float hz, const RayPre &p,
+                                       const NodeOrder &n, float t_max) {
+  float tn;
+  return cslab_test(cx, cy, cz, hx, hy, hz, p, n, t_max, tn) ? tn : CUDART_INF_F;
+}
+
 // The same test as a predicate (any-hit walks need no entry distance).  Conservative like slab_fma: a ray with
 // non-finite slab parameters may be let into a box it misses, never kept out of one it hits.
+template <bool FOLD = (PTB_SLAB_FOLD != 0)>
 __device__ __forceinline__ bool slab_hit(float lox, float loy, float loz, float hix, float hiy, float hiz, const RayPre &p,
                                          const NodeOrder &n, float t_max) {
   float tn;
-  return slab_test(__fmaf_rn(lox, p.ix, n.oix), __fmaf_rn(hix, p.ix, n.oix), __fmaf_rn(loy, p.iy, n.oiy),
+  return slab_test<FOLD>(__fmaf_rn(lox, p.ix, n.oix), __fmaf_rn(hix, p.ix, n.oix), __fmaf_rn(loy, p.iy, n.oiy),
                    __fmaf_rn(hiy, p.iy, n.oiy), __fmaf_rn(loz, p.iz, n.oiz), __fmaf_rn(hiz, p.iz, n.oiz), t_max, tn);
 }
 
@@ -268,6 +291,23 @@ template <int K>
 __device__ __forceinline__ float qslab(const QNodeData &n, const QNodeRay &r, float t_max) {
   float tn;
   return qslab_test<K>(n, r, t_max, tn) ? tn : CUDART_INF_F;
+}
+
+// Prefetch of the record behind a child reference into L1 (an inner node's line, or the first line of a leaf's first
+// triangle): issued when the reference is decided, so that the load of the next visit finds the line on its way.
+__device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+__device__ __forceinline__ void prefetch_ref(const DevScene &S, uint32_t ref) {
+  if (!(ref & 0x80000000u)) {
+#if PTB_QNODE
+    prefetch_l1(S.qnodes + ref);
+#elif PTB_CNODE
+    prefetch_l1(S.cnodes + ref);
+#else
+    prefetch_l1(S.nodes + ref);
+#endif
+  } else if (!(ref & 0x40000000u)) {
+    prefetch_l1(S.tris + ((ref & 0x3FFFFFFFu) >> 3));
+  }
 }
 
 #define PTB_STACK 96

@@ -320,7 +320,7 @@ constexpr int LEAF_THRESHOLD = PTB_LEAF_T;      // run the (divergent) primitive
 // launch_extend picks by tree depth.
 template <int POP>
 __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
-                                                WaveState W, uint32_t bounce, uint32_t alpha_on, pt_hit *__restrict__ trace_out) {
+                                                const __grid_constant__ WaveState W, uint32_t bounce, uint32_t alpha_on, pt_hit *__restrict__ trace_out) {
   const uint32_t in = bounce & 1u, outb = in ^ 1u;
   const uint32_t n = W.counters[CTR_QUEUE(in)];
   if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -476,7 +476,7 @@ __device__ __forceinline__ void cta_append2(uint32_t *pair, bool want_path, bool
 // reset by k_extend.
 #if PTB_HIT_LIST
 __global__ void __launch_bounds__(256) k_hit_list(const __grid_constant__ DevScene S, const __grid_constant__ WaveParams P,
-                                                  WaveState W, uint32_t bounce) {
+                                                  const __grid_constant__ WaveState W, uint32_t bounce) {
   const uint32_t in = bounce & 1u;
   const uint32_t n = W.counters[CTR_QUEUE(in)];
   const V3 bgc = mk3(S.background[0], S.background[1], S.background[2]);
@@ -523,7 +523,7 @@ __global__ void __launch_bounds__(256) k_hit_list(const __grid_constant__ DevSce
 // and compaction of the surviving paths into the other queue buffer.  Queue positions are assigned statically
 // (warp-strided): no work-fetch atomic; the last light's shadow entry and the next ray share one reservation atomic.
 __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(const __grid_constant__ DevScene S,
-                                                               const __grid_constant__ WaveParams P, WaveState W,
+                                                               const __grid_constant__ WaveParams P, const __grid_constant__ WaveState W,
                                                                uint32_t bounce) {
   const uint32_t in = bounce & 1u, outb = in ^ 1u;
 #if PTB_HIT_LIST
@@ -759,7 +759,7 @@ __global__ void __launch_bounds__(128) k_debug_aov(const __grid_constant__ DevSc
 
 // shadow: transmittance of every queued shadow ray; adds contribution * transmittance to the path's radiance.
 // Same lane-level ray replacement and node / primitive phases as k_extend.
-__global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_constant__ DevScene S, WaveState W, uint32_t bounce) {
+__global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_constant__ DevScene S, const __grid_constant__ WaveState W, uint32_t bounce) {
   uint32_t n = W.counters[CTR_SHADOW((bounce & 1u) ^ 1u)];
   if (n > W.shadow_capacity) n = W.shadow_capacity;
   if (blockIdx.x == 0 && threadIdx.x == 0) stat_add(W.counters, CTR_STAT_SHADOW, n);

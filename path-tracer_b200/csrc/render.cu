@@ -230,16 +230,38 @@ int build_device_scene(pt_scene *sc) {
   static_assert(sizeof(DevNode) == sizeof(Bvh4Node), "node layout");
   static_assert(sizeof(DevQNode) == sizeof(Bvh4QNode), "quantised node layout");
   D.nodes = nullptr;
+  D.cnodes = nullptr;
   D.qnodes = nullptr;
-#if PTB_QNODE && !defined(PTB_BOTH_NODE_FORMATS)
-  const bool want_float = false, want_q = true;
+#if defined(PTB_BOTH_NODE_FORMATS)
+  const bool want_float = true, want_c = true, want_q = true;  // A/B builds: one host library under kernels of any kind
 #elif PTB_QNODE
-  const bool want_float = true, want_q = true;  // A/B builds: one host library under kernels of either kind
+  const bool want_float = false, want_c = false, want_q = true;
+#elif PTB_CNODE
+  const bool want_float = false, want_c = true, want_q = false;
 #else
-  const bool want_float = true, want_q = false;
+  const bool want_float = true, want_c = false, want_q = false;
 #endif
   if (want_float)
     if ((rc = upload(sc, sc->bvh.nodes, reinterpret_cast<const Bvh4Node **>(&D.nodes)))) return rc;
+  if (want_c) {
+    // centre / half-extent per child and axis, the half-extent rounded up so that [c - h, c + h] contains [lo, hi]
+    std::vector<Bvh4Node> cn(sc->bvh.nodes);
+    for (Bvh4Node &nd : cn) {
+      float *lo[3] = {nd.lo_x, nd.lo_y, nd.lo_z}, *hi[3] = {nd.hi_x, nd.hi_y, nd.hi_z};
+      for (int a = 0; a < 3; ++a)
+        for (int k = 0; k < 4; ++k) {
+          const double l = lo[a][k], h = hi[a][k];
+          if (!(l <= h)) continue;  // empty slot: NaN planes stay NaN
+          const float c = (float)(0.5 * (l + h));
+          const double hd = std::max(h - (double)c, (double)c - l);
+          float he = (float)hd;
+          if ((double)he < hd) he = std::nextafterf(he, INFINITY);
+          lo[a][k] = c;
+          hi[a][k] = he;
+        }
+    }
+    if ((rc = upload(sc, cn, reinterpret_cast<const Bvh4Node **>(&D.cnodes)))) return rc;
+  }
   if (want_q) {
     if (n_leaf_tris >= (1u << 27)) {
       set_error("too many triangles for the leaf reference encoding");

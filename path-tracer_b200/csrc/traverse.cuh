@@ -145,6 +145,13 @@ struct ClosestTrav {
     const QNodeRay nr = qnode_ray(nd, pre, no, S.f32_one_bits);
     float t0 = qslab<0>(nd, nr, t_prune), t1 = qslab<1>(nd, nr, t_prune);
     float t2 = qslab<2>(nd, nr, t_prune), t3 = qslab<3>(nd, nr, t_prune);
+#elif PTB_CNODE
+    const NodeData nd = load_node(S.cnodes, cur);
+    const uint4 ch = nd.ch;
+    float t0 = cslab(nd.lo_x.x, nd.lo_y.x, nd.lo_z.x, nd.hi_x.x, nd.hi_y.x, nd.hi_z.x, pre, no, t_prune);
+    float t1 = cslab(nd.lo_x.y, nd.lo_y.y, nd.lo_z.y, nd.hi_x.y, nd.hi_y.y, nd.hi_z.y, pre, no, t_prune);
+    float t2 = cslab(nd.lo_x.z, nd.lo_y.z, nd.lo_z.z, nd.hi_x.z, nd.hi_y.z, nd.hi_z.z, pre, no, t_prune);
+    float t3 = cslab(nd.lo_x.w, nd.lo_y.w, nd.lo_z.w, nd.hi_x.w, nd.hi_y.w, nd.hi_z.w, pre, no, t_prune);
 #else
     const NodeData nd = load_node(S.nodes, cur);
     const uint4 ch = nd.ch;
@@ -162,6 +169,12 @@ struct ClosestTrav {
 #else
     PTB_CSWAP(t0, r0, t1, r1) PTB_CSWAP(t2, r2, t3, r3) PTB_CSWAP(t0, r0, t2, r2) PTB_CSWAP(t1, r1, t3, r3)
     PTB_CSWAP(t1, r1, t2, r2)
+#if PTB_PREFETCH_CUR
+    if (t0 < CUDART_INF_F) prefetch_ref(S, r0);
+#endif
+#if PTB_PREFETCH_PUSH
+    if (t1 < CUDART_INF_F) prefetch_ref(S, r1);
+#endif
     if (t3 < CUDART_INF_F) push(stk, t3, r3);
     if (t2 < CUDART_INF_F) push(stk, t2, r2);
     if (t1 < CUDART_INF_F) push(stk, t1, r1);
@@ -271,8 +284,26 @@ struct ClosestTrav {
 // shadow rays of these scenes are occluded for the extra test (and 22 B more spills) to pay.  Off.
 #define PTB_SHADOW_CACHE 0
 #endif
+// k_shadow keeps the index: the pointer form costs it 62 bytes of spills at 64 registers and measured +3 ... +4 %
+// (profiles/r07/ab_s20_centre_half_extent_shadow_stack.jsonl).
 #ifndef PTB_SHADOW_STACK_PTR
-#define PTB_SHADOW_STACK_PTR PTB_STACK_PTR
+#define PTB_SHADOW_STACK_PTR 0
+#endif
+// Prefetches (isect.cuh prefetch_ref): PTB_PREFETCH_CUR - the nearest child, as soon as the sort has decided it (its
+// load is some thirty instructions and a warp vote away); PTB_PREFETCH_PUSH - the second nearest child, which goes to
+// the stack; PTB_SHADOW_PREFETCH - every child the shadow walk pushes (all of them are visited unless the ray is
+// occluded first).  Measured (profiles/r07/ab_s21_prefetch_grid_constant_wave.jsonl): k_extend +2 % (CUR), +1 % (PUSH),
+// +4.5 % (both) on console, +2.8 % / +2 % / +4.6 % on foliage, +2.8 % / - / +5.5 % on city; k_shadow +11 % on console,
+// +13 % on foliage, +11 % on city: every extra request through the L1 data pipe costs more than the latency it
+// hides.  All off.
+#ifndef PTB_PREFETCH_CUR
+#define PTB_PREFETCH_CUR 0
+#endif
+#ifndef PTB_PREFETCH_PUSH
+#define PTB_PREFETCH_PUSH 0
+#endif
+#ifndef PTB_SHADOW_PREFETCH
+#define PTB_SHADOW_PREFETCH 0
 #endif
 
 struct ShadowTrav {
@@ -299,6 +330,14 @@ struct ShadowTrav {
   __device__ __forceinline__ void push(uint32_t *stk, uint32_t ref) { stk[sp++] = ref; }
   __device__ __forceinline__ uint32_t take(const uint32_t *stk) { return stk[--sp]; }
 #endif
+  __device__ __forceinline__ void shadow_push(const DevScene &S, uint32_t *stk, uint32_t ref) {
+    push(stk, ref);
+#if PTB_SHADOW_PREFETCH
+    prefetch_ref(S, ref);
+#else
+    (void)S;
+#endif
+  }
   uint32_t occluder;  // leaf-order index of the opaque triangle that ended this walk (valid when it did)
 
   // limit < 0: directional light (every hit on the ray, occluder sampled at its own uv, mod.rs:291-297)
@@ -361,11 +400,21 @@ struct ShadowTrav {
     if (qslab_test<3>(nd, nr, t_max, tn)) push(stk, ch.w);
     pop(stk);
     return;
+#elif PTB_CNODE
+    const NodeData nd = load_node(S.cnodes, cur);
+    const uint4 ch = nd.ch;
+    float tn;
+    if (cslab_test<(PTB_SHADOW_SLAB_FOLD != 0)>(nd.lo_x.x, nd.lo_y.x, nd.lo_z.x, nd.hi_x.x, nd.hi_y.x, nd.hi_z.x, pre, no, t_max, tn)) push(stk, ch.x);
+    if (cslab_test<(PTB_SHADOW_SLAB_FOLD != 0)>(nd.lo_x.y, nd.lo_y.y, nd.lo_z.y, nd.hi_x.y, nd.hi_y.y, nd.hi_z.y, pre, no, t_max, tn)) push(stk, ch.y);
+    if (cslab_test<(PTB_SHADOW_SLAB_FOLD != 0)>(nd.lo_x.z, nd.lo_y.z, nd.lo_z.z, nd.hi_x.z, nd.hi_y.z, nd.hi_z.z, pre, no, t_max, tn)) push(stk, ch.z);
+    if (cslab_test<(PTB_SHADOW_SLAB_FOLD != 0)>(nd.lo_x.w, nd.lo_y.w, nd.lo_z.w, nd.hi_x.w, nd.hi_y.w, nd.hi_z.w, pre, no, t_max, tn)) push(stk, ch.w);
+    pop(stk);
+    return;
 #else
     const NodeData nd = load_node(S.nodes, cur);
     const uint4 ch = nd.ch;
 #endif
-#if PTB_QNODE
+#if PTB_QNODE || PTB_CNODE
 #elif PTB_SHADOW_ORDERED
     float t0 = slab_fma(nd.lo_x.x, nd.lo_y.x, nd.lo_z.x, nd.hi_x.x, nd.hi_y.x, nd.hi_z.x, pre, no, t_max, ch.x);
     float t1 = slab_fma(nd.lo_x.y, nd.lo_y.y, nd.lo_z.y, nd.hi_x.y, nd.hi_y.y, nd.hi_z.y, pre, no, t_max, ch.y);
@@ -379,10 +428,10 @@ struct ShadowTrav {
     if (t1 < CUDART_INF_F) push(stk, r1);
     if (t0 < CUDART_INF_F) push(stk, r0);
 #elif !PTB_SHADOW_NOPUSH
-    if (slab_hit(nd.lo_x.x, nd.lo_y.x, nd.lo_z.x, nd.hi_x.x, nd.hi_y.x, nd.hi_z.x, pre, no, t_max)) push(stk, ch.x);
-    if (slab_hit(nd.lo_x.y, nd.lo_y.y, nd.lo_z.y, nd.hi_x.y, nd.hi_y.y, nd.hi_z.y, pre, no, t_max)) push(stk, ch.y);
-    if (slab_hit(nd.lo_x.z, nd.lo_y.z, nd.lo_z.z, nd.hi_x.z, nd.hi_y.z, nd.hi_z.z, pre, no, t_max)) push(stk, ch.z);
-    if (slab_hit(nd.lo_x.w, nd.lo_y.w, nd.lo_z.w, nd.hi_x.w, nd.hi_y.w, nd.hi_z.w, pre, no, t_max)) push(stk, ch.w);
+    if (slab_hit<(PTB_SHADOW_SLAB_FOLD != 0)>(nd.lo_x.x, nd.lo_y.x, nd.lo_z.x, nd.hi_x.x, nd.hi_y.x, nd.hi_z.x, pre, no, t_max)) shadow_push(S, stk, ch.x);
+    if (slab_hit<(PTB_SHADOW_SLAB_FOLD != 0)>(nd.lo_x.y, nd.lo_y.y, nd.lo_z.y, nd.hi_x.y, nd.hi_y.y, nd.hi_z.y, pre, no, t_max)) shadow_push(S, stk, ch.y);
+    if (slab_hit<(PTB_SHADOW_SLAB_FOLD != 0)>(nd.lo_x.z, nd.lo_y.z, nd.lo_z.z, nd.hi_x.z, nd.hi_y.z, nd.hi_z.z, pre, no, t_max)) shadow_push(S, stk, ch.z);
+    if (slab_hit<(PTB_SHADOW_SLAB_FOLD != 0)>(nd.lo_x.w, nd.lo_y.w, nd.lo_z.w, nd.hi_x.w, nd.hi_y.w, nd.hi_z.w, pre, no, t_max)) shadow_push(S, stk, ch.w);
 #else
     // every child the ray enters is visited (in no particular order): the last one found becomes current directly,
     // only the others go through the local-memory stack (one STL + one LDL fewer per node visit)
