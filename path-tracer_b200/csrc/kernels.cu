@@ -193,6 +193,9 @@ __global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene
 #ifndef PTB_FETCH_AHEAD_EXTEND
 #define PTB_FETCH_AHEAD_EXTEND 0
 #endif
+#ifdef PTB_FETCH_AHEAD_SHADOW
+#define PTB_FETCH_AHEAD_SHADOW_FORCED 1
+#endif
 #ifndef PTB_FETCH_AHEAD_SHADOW
 #define PTB_FETCH_AHEAD_SHADOW 1
 #endif
@@ -759,6 +762,11 @@ __global__ void __launch_bounds__(128) k_debug_aov(const __grid_constant__ DevSc
 
 // shadow: transmittance of every queued shadow ray; adds contribution * transmittance to the path's radiance.
 // Same lane-level ray replacement and node / primitive phases as k_extend.
+// FETCH = the asynchronous work fetch with record prefetch (WorkFetch above): -32 % on the console scene, whose shadow
+// walks are short (5.9 node visits) and whose queue records come from DRAM; +6 % on foliage (20.7 node visits per ray:
+// refills are rare and the chunked reservation only costs balance), profiles/r07/ab_s22_occupancy_fetch_ahead.jsonl.
+// launch_shadow picks by tree depth, like launch_extend; -DPTB_FETCH_AHEAD_SHADOW=<0|1> forces one.
+template <int FETCH>
 __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_constant__ DevScene S, const __grid_constant__ WaveState W, uint32_t bounce) {
   uint32_t n = W.counters[CTR_SHADOW((bounce & 1u) ^ 1u)];
   if (n > W.shadow_capacity) n = W.shadow_capacity;
@@ -776,24 +784,21 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
 #if PTB_COUNT_STEPS
   uint32_t cnt_nodes = 0, cnt_prims = 0;
 #endif
-#if PTB_FETCH_AHEAD_SHADOW
   WorkFetch wf;
-  wf.init(&W.counters[CTR_WORK_SHADOW], n);
-#define drained wf.drained
-#else
-  bool drained = false;
-#endif
+  bool drained_sync = false;
+  if (FETCH) wf.init(&W.counters[CTR_WORK_SHADOW], n);
   for (;;) {
-#if PTB_FETCH_AHEAD_SHADOW
-    uint32_t nq = wf.refill(&W.counters[CTR_WORK_SHADOW], q == NONE, n, [&](uint32_t p) {
-      prefetch_l2(W.sh_o + p);
-      prefetch_l2(W.sh_d + p);
-      prefetch_l2(W.sh_c + p);
-      prefetch_l2(W.sh_p + p);
-    });
-#else
-    uint32_t nq = refill(&W.counters[CTR_WORK_SHADOW], q == NONE, n, drained);
-#endif
+    uint32_t nq;
+    if (FETCH)
+      nq = wf.refill(&W.counters[CTR_WORK_SHADOW], q == NONE, n, [&](uint32_t p) {
+        prefetch_l2(W.sh_o + p);
+        prefetch_l2(W.sh_d + p);
+        prefetch_l2(W.sh_c + p);
+        prefetch_l2(W.sh_p + p);
+      });
+    else
+      nq = refill(&W.counters[CTR_WORK_SHADOW], q == NONE, n, drained_sync);
+    const bool drained = FETCH ? wf.drained : drained_sync;
     if (nq != NONE) {
       q = nq;
       float4 o4 = ld_wave(&W.sh_o[q]), d4 = ld_wave(&W.sh_d[q]), c4 = ld_wave(&W.sh_c[q]), p4 = ld_wave(&W.sh_p[q]);
@@ -848,8 +853,6 @@ __global__ void __launch_bounds__(128, PTB_SHADOW_MINB) k_shadow(const __grid_co
   }
 #endif
 }
-
-#undef drained
 
 // resolve: *pixel += color (mod.rs:130) for the wave's samples of each pixel, in sample order.
 __global__ void __launch_bounds__(256) k_resolve(const __grid_constant__ WaveParams P, WaveState W, float *__restrict__ accum) {
@@ -980,7 +983,13 @@ void launch_hit_list(const DevScene &S, const WaveParams &P, const WaveState &W,
 }
 int shade_launches() { return 1 + PTB_HIT_LIST; }
 void launch_shadow(const DevScene &S, const WaveState &W, uint32_t bounce, cudaStream_t st) {
-  k_shadow<<<sm_count() * PERSIST_CTAS_PER_SM, 128, 0, st>>>(S, W, bounce);
+  const int grid = sm_count() * PERSIST_CTAS_PER_SM;
+#if defined(PTB_FETCH_AHEAD_SHADOW_FORCED)
+  k_shadow<PTB_FETCH_AHEAD_SHADOW><<<grid, 128, 0, st>>>(S, W, bounce);
+#else
+  if (S.tree_depth >= 16) k_shadow<0><<<grid, 128, 0, st>>>(S, W, bounce);  // long walks: plain work fetch
+  else k_shadow<1><<<grid, 128, 0, st>>>(S, W, bounce);
+#endif
 }
 void launch_resolve(const WaveParams &P, const WaveState &W, float *accum, cudaStream_t st) {
   uint32_t npix = P.width * P.height;
