@@ -83,7 +83,7 @@ __device__ __forceinline__ void stat_add(uint32_t *counters, int which, unsigned
 // traversal, not a side kernel.  Queue position q of the chunk holds ray `slot_base + q`; the slot doubles as the
 // "pixel" of the RNG key in alpha mode.
 __global__ void __launch_bounds__(256) k_load_rays(const float *__restrict__ rays, uint32_t n, uint32_t slot_base,
-                                                   WaveState W, uint32_t buf) {
+                                                   const __grid_constant__ WaveState W, uint32_t buf) {
   const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
   if (q == 0) {
     W.counters[CTR_QUEUE(buf)] = n;
