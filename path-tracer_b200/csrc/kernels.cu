@@ -298,8 +298,10 @@ __device__ __forceinline__ void st_wave(float4 *p, float4 v) {
 #endif
 }
 
+// Thresholds re-tuned on the round's last kernels (profiles/r07/ab_s24_thresholds.jsonl): refill at 16 busy lanes
+// instead of 18: k_extend -0.7 % (console), -0.8 % (foliage), k_shadow -1 %; 20 is +2 %; leaf threshold 10 / 14: +-0.5 %.
 #ifndef PTB_REFILL_T
-#define PTB_REFILL_T 18
+#define PTB_REFILL_T 16
 #endif
 #ifndef PTB_LEAF_T
 #define PTB_LEAF_T 12
