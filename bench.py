@@ -74,16 +74,45 @@ class ClockSampler:
 
     def __init__(self, index):
         self.index, self.rows, self.stop, self.th = index, [], threading.Event(), None
+        self.nvml = self.handle = None
+        try:  # the same counters through NVML, in process: an nvidia-smi process per sample (on every rank at once) takes
+            # tens of ms of driver time, which is visible in a timed region of 50 ms (5 frames of 9 ms on 8 GPUs)
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml, self.handle = pynvml, pynvml.nvmlDeviceGetHandleByIndex(self._physical_index(index))
+        except Exception:
+            self.nvml = None
+
+    @staticmethod
+    def _physical_index(index):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            ids = [v.strip() for v in vis.split(",") if v.strip()]
+            if index < len(ids) and ids[index].isdigit():
+                return int(ids[index])
+        return index
+
+    def _sample_nvml(self):
+        n, h = self.nvml, self.handle
+        sm = n.nvmlDeviceGetClockInfo(h, n.NVML_CLOCK_SM)
+        mx = n.nvmlDeviceGetMaxClockInfo(h, n.NVML_CLOCK_SM)
+        r = n.nvmlDeviceGetCurrentClocksEventReasons(h) if hasattr(n, "nvmlDeviceGetCurrentClocksEventReasons") \
+            else n.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+        act = lambda bit: "Active" if r & bit else "Not Active"
+        return [str(sm), str(mx), act(0x8), act(0x40), act(0x20), act(0x4)]  # hw, hw thermal, sw thermal, sw power cap
 
     def _run(self):
         while not self.stop.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                self.rows.append([x.strip() for x in out.strip().split(",")])
+                if self.nvml is not None:
+                    self.rows.append(self._sample_nvml())
+                else:
+                    out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                    self.rows.append([x.strip() for x in out.strip().split(",")])
             except Exception:
                 pass
-            self.stop.wait(0.1)
+            self.stop.wait(0.01 if self.nvml is not None else 0.1)
 
     def __enter__(self):
         self.th = threading.Thread(target=self._run, daemon=True)
@@ -111,7 +140,8 @@ class ClockSampler:
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm),
+                "source": "NVML, in process" if self.nvml is not None else "nvidia-smi"}
 
 
 def load_json(path, key):
@@ -346,7 +376,10 @@ def measure(env, name, wl, steps, warmup, want_weak):
             return nbytes
     else:
         def step_e2e():
-            nbytes = scene.upload(env.stream.cuda_stream)
+            # up to 4 GPUs every rank re-sends the whole scene from its pinned host copy; from 8 up each rank sends 1/N of
+            # every array and an in-place NCCL all-gather replicates it over NVSwitch - eight uploads of the same bytes
+            # exceed what one host delivers (profiles/r07/s26_8gpu_bench.json: 11.1 ms per step against a 9.7 ms frame)
+            nbytes = R.distribute_scene()
             img = R.render(spp)
             if img is not None:
                 rgb_host.copy_(img, non_blocking=True)
@@ -356,6 +389,7 @@ def measure(env, name, wl, steps, warmup, want_weak):
         h2d = step_e2e()
     ms_e2e = env.timed(step_e2e, steps)
     e2e_value = samples_per_step * steps / ms_e2e / 1e3
+    h2d_all = env.sum_over_ranks(h2d)  # host -> device bytes of one step over all ranks
 
     weak = None
     if want_weak and env.world > 1:
@@ -377,10 +411,13 @@ def measure(env, name, wl, steps, warmup, want_weak):
                       "build_s": build_s, "accel": scene.accel_info()},
             "spp_per_gpu": [env.multi.sample_partition(spp, env.world, g)[2] for g in range(env.world)],
             "clocks": clocks,
-            "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(w * h * 3),
+            "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d_all), "d2h_bytes_per_step": int(w * h * 3),
                     "ms_per_step": ms_e2e / steps,
                     "call": "pt_scene_upload + pt_render_async (pinned host image out), pipelined" if env.world == 1 else
-                            "pt_scene_upload + pt_render_accum_device per rank + NCCL reduce + pt_tonemap_device + D2H on rank 0"},
+                            "scene to every rank (DistributedRenderer.distribute_scene: pt_scene_upload per rank below 8 GPUs, "
+                            "pt_scene_upload_part + NCCL all-gather from 8 up) + pt_render_accum_device per rank + NCCL reduce + "
+                            "pt_tonemap_device + D2H on rank 0",
+                    "h2d_bytes_per_step_all_ranks": int(h2d_all)},
             "gpu_launches": int((st["kernel_launches"] + 1) * steps),
             "rays_per_step": {"extend": ext_all, "shadow": sh_all, "alpha_tests": alpha_all,
                               "shadow_dropped": dropped},

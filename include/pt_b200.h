@@ -176,6 +176,26 @@ int pt_scene_accel_info(const pt_scene *scene, int *accel, double *build_ms, int
  * scene waits for them and switches to that set - so the upload for frame k+1 overlaps the rendering of frame k.
  * `stream` is unused (kept for source compatibility).  *bytes_out = bytes copied. */
 int pt_scene_upload(pt_scene *scene, void *stream, uint64_t *bytes_out);
+/* The same refresh for a scene replica whose arrays arrive from somewhere else than this process's host copy - the
+ * multi-GPU form of Scene::load's result reaching every device: ONE rank uploads from host memory (pt_scene_upload),
+ * the others receive the arrays from that GPU over NVLink (an NCCL broadcast, a peer copy), because eight uploads of
+ * the same scene share one host's PCIe / memory bandwidth and NVSwitch does not (path-tracer_b200/multi.py
+ * distribute_scene).
+ * pt_scene_upload_targets: the arrays of the set no kernel is reading (the set a pt_scene_upload just wrote, if one is
+ * pending), as device pointers and sizes in bytes, in the same order on every replica of a scene; at most `capacity`
+ * entries are written, *count = how many there are.  `stream` is made to wait until the set may be written or read
+ * (the kernels of two frames ago, a pending upload): enqueue the transfer on it.
+ * pt_scene_upload_commit: the arrays are complete once the work enqueued on `stream` so far has run; the next render
+ * / trace call on the scene waits for it and switches to that set, exactly as after pt_scene_upload. */
+int pt_scene_upload_targets(pt_scene *scene, void *stream, void **ptrs, uint64_t *bytes, uint32_t capacity,
+                            uint32_t *count);
+int pt_scene_upload_commit(pt_scene *scene, void *stream);
+/* pt_scene_upload of one part of `parts`: of every array, bytes [part * shard, (part + 1) * shard) with
+ * shard = (size / parts) rounded down to a multiple of 256, plus the remainder behind the last shard (sent by every
+ * part).  With one part per rank followed by an in-place all-gather of the first parts * shard bytes of each array
+ * (pt_scene_upload_targets, then pt_scene_upload_commit) the scene crosses the host's PCIe once per frame, not once per
+ * GPU, and NVSwitch replicates it.  *bytes_out = bytes this call copied. */
+int pt_scene_upload_part(pt_scene *scene, uint32_t part, uint32_t parts, uint64_t *bytes_out);
 /* Introspection (host copies; pointers valid until pt_scene_destroy). */
 int pt_scene_get_desc(const pt_scene *scene, pt_scene_desc *out);
 int pt_scene_info(const pt_scene *scene, uint64_t *n_tris, uint64_t *n_prims, uint64_t *n_nodes,

@@ -19,7 +19,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
 EXPORTS = ["pt_last_error", "pt_device_count", "pt_profile_default", "pt_profile_load_yaml", "pt_scene_load_isf",
-           "pt_scene_create", "pt_scene_synthetic", "pt_scene_destroy", "pt_set_accel_builder", "pt_scene_accel_info", "pt_scene_upload", "pt_set_kernel_timing", "pt_scene_get_desc", "pt_scene_info",
+           "pt_scene_create", "pt_scene_synthetic", "pt_scene_destroy", "pt_set_accel_builder", "pt_scene_accel_info", "pt_scene_upload", "pt_scene_upload_targets", "pt_scene_upload_commit", "pt_scene_upload_part", "pt_set_kernel_timing", "pt_scene_get_desc", "pt_scene_info",
            "pt_trace_closest", "pt_trace_closest_device", "pt_trace_closest_device_noalloc", "pt_trace_accepted", "pt_trace_shadow", "pt_trace_transmittance",
            "pt_triangle_intersect", "pt_philox4x32_10",
            "pt_trace_paths", "pt_render_accum_device", "pt_aov_name", "pt_debug_textures", "pt_render_progressive", "pt_convert_gltf", "pt_scene_save_binary",
@@ -56,6 +56,9 @@ def lib():
         L.pt_scene_destroy.argtypes = [vp]
         L.pt_scene_destroy.restype = None
         L.pt_scene_upload.argtypes = [vp, vp, C.POINTER(u64)]
+        L.pt_scene_upload_targets.argtypes = [vp, vp, C.POINTER(vp), C.POINTER(u64), u32, C.POINTER(u32)]
+        L.pt_scene_upload_commit.argtypes = [vp, vp]
+        L.pt_scene_upload_part.argtypes = [vp, u32, u32, C.POINTER(u64)]
         L.pt_set_kernel_timing.argtypes = [C.c_int]
         L.pt_set_kernel_timing.restype = None
         L.pt_scene_get_desc.argtypes = [vp, C.POINTER(pt_scene_desc)]
@@ -191,6 +194,25 @@ class Scene:
         n = C.c_uint64()
         _check(lib().pt_scene_upload(self.h, stream, C.byref(n)))
         return n.value
+
+    def upload_part(self, part, parts):
+        """upload() of one part of `parts` of every array (+ the remainder behind the last shard); returns bytes copied."""
+        n = C.c_uint64()
+        _check(lib().pt_scene_upload_part(self.h, part, parts, C.byref(n)))
+        return n.value
+
+    def upload_targets(self, stream=None):
+        """[(device pointer, bytes)] of the array set no kernel is reading (the one a pending upload() wrote); `stream`
+        is made to wait until it may be written / read.  Same order on every replica of a scene."""
+        n = C.c_uint32()
+        _check(lib().pt_scene_upload_targets(self.h, stream, None, None, 0, C.byref(n)))
+        ptrs, sizes = (C.c_void_p * n.value)(), (C.c_uint64 * n.value)()
+        _check(lib().pt_scene_upload_targets(self.h, stream, ptrs, sizes, n.value, C.byref(n)))
+        return [(int(ptrs[i] or 0), int(sizes[i])) for i in range(n.value)]
+
+    def upload_commit(self, stream=None):
+        """The arrays of upload_targets() are complete once the work enqueued on `stream` so far has run."""
+        _check(lib().pt_scene_upload_commit(self.h, stream))
 
     def info(self):
         a, b, c, d = C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_uint64()

@@ -550,8 +550,48 @@ void pt_scene_destroy(pt_scene *sc) {
   delete sc;
 }
 
-int pt_scene_upload(pt_scene *sc, void *stream, uint64_t *bytes_out) {
-  (void)stream;  // kept for the ABI: the copies run on the scene's own copy stream (see the header)
+// The second array set, its stream and events (first upload of a scene; sc->mu held, current device = the scene's).
+static int ensure_upload_sets(pt_scene *sc) {
+  if (sc->copy_stream) return PT_OK;
+  CUDA_TRY(cudaStreamCreateWithFlags(&sc->copy_stream, cudaStreamNonBlocking));
+  CUDA_TRY(cudaEventCreateWithFlags(&sc->upload_ev, cudaEventDisableTiming));
+  for (int k = 0; k < 2; ++k) CUDA_TRY(cudaEventCreateWithFlags(&sc->use_ev[k], cudaEventDisableTiming));
+  for (auto &e : sc->staged) {
+    CUDA_TRY(cudaMalloc(&e.dev2, e.bytes));
+    sc->allocs.push_back(e.dev2);  // freed with the scene whichever set is current by then
+    sc->device_bytes += e.bytes;
+  }
+  return PT_OK;
+}
+
+int pt_scene_upload_targets(pt_scene *sc, void *stream, void **ptrs, uint64_t *bytes, uint32_t capacity, uint32_t *count) {
+  if (!sc || !count || (capacity && (!ptrs || !bytes))) {
+    set_error("null argument");
+    return PT_ERR_INVALID;
+  }
+  if (sc->device < 0) return no_device();
+  DeviceGuard g(sc->device);
+  std::lock_guard<std::mutex> lock(sc->mu);
+  int rc = ensure_upload_sets(sc);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  // e.dev2 is the set that is not current - also while an upload into it is pending (the switch happens at the next
+  // render): wait for its last readers and for that upload
+  CUDA_TRY(cudaStreamWaitEvent(st, sc->use_ev[sc->cur_set ^ 1], 0));
+  if (sc->upload_pending) CUDA_TRY(cudaStreamWaitEvent(st, sc->upload_ev, 0));
+  uint32_t n = 0;
+  for (auto &e : sc->staged) {
+    if (n < capacity) {
+      ptrs[n] = e.dev2;
+      bytes[n] = e.bytes;
+    }
+    ++n;
+  }
+  *count = n;
+  return PT_OK;
+}
+
+int pt_scene_upload_commit(pt_scene *sc, void *stream) {
   if (!sc) {
     set_error("null argument");
     return PT_ERR_INVALID;
@@ -560,22 +600,58 @@ int pt_scene_upload(pt_scene *sc, void *stream, uint64_t *bytes_out) {
   DeviceGuard g(sc->device);
   std::lock_guard<std::mutex> lock(sc->mu);
   if (!sc->copy_stream) {
-    CUDA_TRY(cudaStreamCreateWithFlags(&sc->copy_stream, cudaStreamNonBlocking));
-    CUDA_TRY(cudaEventCreateWithFlags(&sc->upload_ev, cudaEventDisableTiming));
-    for (int k = 0; k < 2; ++k) CUDA_TRY(cudaEventCreateWithFlags(&sc->use_ev[k], cudaEventDisableTiming));
-    for (auto &e : sc->staged) {
-      CUDA_TRY(cudaMalloc(&e.dev2, e.bytes));
-      sc->allocs.push_back(e.dev2);  // freed with the scene whichever set is current by then
-      sc->device_bytes += e.bytes;
-    }
+    set_error("pt_scene_upload_commit without pt_scene_upload_targets");
+    return PT_ERR_INVALID;
+  }
+  // a pending upload's event is replaced by one that is later on `stream`, which waited for it in _targets
+  CUDA_TRY(cudaEventRecord(sc->upload_ev, (cudaStream_t)stream));
+  sc->upload_pending = true;
+  return PT_OK;
+}
+
+static int upload_impl(pt_scene *sc, uint32_t part, uint32_t parts, uint64_t *bytes_out);
+
+int pt_scene_upload(pt_scene *sc, void *stream, uint64_t *bytes_out) {
+  (void)stream;  // kept for the ABI: the copies run on the scene's own copy stream (see the header)
+  return upload_impl(sc, 0, 1, bytes_out);
+}
+
+int pt_scene_upload_part(pt_scene *sc, uint32_t part, uint32_t parts, uint64_t *bytes_out) {
+  if (parts == 0 || part >= parts) {
+    set_error("pt_scene_upload_part: part %u of %u", part, parts);
+    return PT_ERR_INVALID;
+  }
+  return upload_impl(sc, part, parts, bytes_out);
+}
+
+static int upload_impl(pt_scene *sc, uint32_t part, uint32_t parts, uint64_t *bytes_out) {
+  if (!sc) {
+    set_error("null argument");
+    return PT_ERR_INVALID;
+  }
+  if (sc->device < 0) return no_device();
+  DeviceGuard g(sc->device);
+  std::lock_guard<std::mutex> lock(sc->mu);
+  {
+    int rc = ensure_upload_sets(sc);
+    if (rc) return rc;
   }
   // the set the kernels are not reading; wait for the last kernels that did read it (two frames ago)
   const int target = sc->cur_set ^ 1;
   CUDA_TRY(cudaStreamWaitEvent(sc->copy_stream, sc->use_ev[target], 0));
   uint64_t total = 0;
   for (auto &e : sc->staged) {
-    CUDA_TRY(cudaMemcpyAsync(e.dev2, e.host, e.bytes, cudaMemcpyHostToDevice, sc->copy_stream));
-    total += e.bytes;
+    if (parts == 1) {
+      CUDA_TRY(cudaMemcpyAsync(e.dev2, e.host, e.bytes, cudaMemcpyHostToDevice, sc->copy_stream));
+      total += e.bytes;
+      continue;
+    }
+    const size_t shard = (e.bytes / parts) & ~(size_t)255, tail = (size_t)parts * shard;
+    char *d = static_cast<char *>(e.dev2);
+    const char *h = static_cast<const char *>(e.host);
+    if (shard) CUDA_TRY(cudaMemcpyAsync(d + part * shard, h + part * shard, shard, cudaMemcpyHostToDevice, sc->copy_stream));
+    if (e.bytes > tail) CUDA_TRY(cudaMemcpyAsync(d + tail, h + tail, e.bytes - tail, cudaMemcpyHostToDevice, sc->copy_stream));
+    total += shard + (e.bytes - tail);
   }
   CUDA_TRY(cudaEventRecord(sc->upload_ev, sc->copy_stream));
   sc->upload_pending = true;

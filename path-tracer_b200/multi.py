@@ -9,6 +9,8 @@ the image differs between G only by the f32 summation order.
 
 No collective is issued inside a frame; the reduce is the only exchange step of the path.
 """
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -33,6 +35,39 @@ def reduce_accum(accum, dst=0):
     if size > 1:
         dist.reduce(accum, dst=dst, op=dist.ReduceOp.SUM)
     return accum
+
+
+def broadcast_arrays(tensors, src=0, group=None):
+    """Send every tensor of `tensors` from rank `src` to the same-sized tensor of the other ranks (in place)."""
+    rank, size = world()
+    if size > 1:
+        for t in tensors:
+            dist.broadcast(t, src=src, group=group)
+    return tensors
+
+
+def part_size(nbytes, parts):
+    """Bytes of one part of pt_scene_upload_part: (size / parts) rounded down to a multiple of 256."""
+    return (nbytes // parts) & ~255
+
+
+def allgather_parts(tensors, group=None):
+    """In-place all-gather of byte tensors whose part r (part_size bytes at offset r * part_size) is valid on rank r;
+    the remainder behind the last part is not touched (every rank has it already)."""
+    rank, size = world()
+    if size > 1:
+        for t in tensors:
+            n = part_size(t.numel(), size)
+            if n:
+                dist.all_gather_into_tensor(t[:n * size], t[rank * n:(rank + 1) * n], group=group)
+    return tensors
+
+
+class _DeviceBytes:
+    """A raw device allocation as a __cuda_array_interface__ object (torch.as_tensor wraps it without copying)."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
 
 
 def render_distributed(render_fn, tonemap_fn, total_samples, accum):
@@ -66,6 +101,45 @@ class DistributedRenderer:
         self.accum = torch.zeros(h, w, 3, dtype=torch.float32, device=self.device)
         self.rgb = torch.zeros(h, w, 3, dtype=torch.uint8, device=self.device)
         self.last_stats = None
+        self._dist_tensors = {}
+
+    def distribute_scene(self, mode=None, src=0):
+        """Scene::load's result reaching every GPU, once per frame.  Returns the bytes THIS rank read from its host.
+
+        mode "replicate": every rank re-sends the whole scene from its own pinned host copy (pt_scene_upload) - N
+            uploads of the same bytes; fine while N x bytes per frame stays below what one host's PCIe / memory
+            system delivers (2 GPUs: e2e within 1.2 % of the device-resident figure).
+        mode "allgather": rank r sends part r of N of every array (pt_scene_upload_part) and one in-place NCCL
+            all-gather per array replicates it over NVLink / NVSwitch: the scene crosses the host's PCIe once per
+            frame.  Eight uploads of the console scene are 121 GB/s against the 107 GB/s the 8-GPU box delivered
+            (profiles/r07/s26_8gpu_bench.json: 11.1 ms per step against a 9.7 ms frame).
+        mode "broadcast": rank `src` uploads, one NCCL broadcast per array.
+        Default ($PT_B200_SCENE_DIST): "allgather" from 8 ranks up, "replicate" below.  The host-to-device copies run
+        on the scene's copy stream (they overlap the frame the GPU is still rendering); the collectives are enqueued on
+        the current stream, between two frames - beside a frame they wait for SM slots that the persistent kernels
+        hold (measured at 2 GPUs: +2.1 ms per step on a stream of their own, +1.4 ms in line)."""
+        rank, size = world()
+        if mode is None:
+            mode = os.environ.get("PT_B200_SCENE_DIST") or ("allgather" if size >= 8 else "replicate")
+        if size == 1 or mode == "replicate":
+            return self.scene.upload()
+        assert mode in ("allgather", "broadcast"), mode
+        nbytes = 0
+        if mode == "allgather":
+            nbytes = self.scene.upload_part(rank, size)
+        elif rank == src:
+            nbytes = self.scene.upload()
+        raw = torch.cuda.current_stream(self.device).cuda_stream
+        targets = self.scene.upload_targets(raw)
+        key = tuple(targets)
+        if key not in self._dist_tensors:
+            self._dist_tensors[key] = [torch.as_tensor(_DeviceBytes(p, n), device=self.device) for p, n in targets if n]
+        if mode == "allgather":
+            allgather_parts(self._dist_tensors[key])
+        else:
+            broadcast_arrays(self._dist_tensors[key], src)
+        self.scene.upload_commit(raw)
+        return nbytes
 
     def _render(self, begin, stride, count, accum, want_stats=False):
         stream = torch.cuda.current_stream(self.device).cuda_stream

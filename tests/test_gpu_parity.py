@@ -485,6 +485,50 @@ def test_scene_upload_is_double_buffered_and_takes_effect(loaded):
     sc.close()
 
 
+def test_scene_arrays_delivered_from_another_replica(loaded):
+    """pt_scene_upload_targets / pt_scene_upload_commit: the arrays of a scene filled from somewhere else than its own
+    host copy (under torchrun: an NCCL broadcast from the rank that uploaded; here: device-to-device copies from a
+    second scene with the same geometry but other materials and lights).  After the commit the scene renders the
+    donor's image, and goes back to its own after an ordinary upload."""
+    import copy
+    import torch
+    import path_tracer_b200.multi as M
+    sa = isf_py.load_isf(scene_path("cube"))
+    sb = copy.copy(sa)
+    sb.materials = [dict(m, albedo=(0.9, 0.2, 0.1), roughness=0.35) for m in sa.materials]
+    sb.lights = [dict(l, color=tuple(0.5 * float(c) for c in l["color"])) for l in sa.lights]
+    a, b = pt.Scene.from_arrays(sa), pt.Scene.from_arrays(sb)
+    prof = pt.Profile(width=96, height=64, samples=4, bounces=3)
+
+    def render(sc):
+        buf = torch.zeros(64, 96, 3, device="cuda")
+        pt.render_accum_device(sc, prof, buf.data_ptr())
+        torch.cuda.synchronize()
+        return buf
+
+    img_a, img_b = render(a), render(b)
+    assert not torch.allclose(img_a, img_b, rtol=1e-3, atol=1e-4)
+    st = torch.cuda.Stream()
+    for k in range(3):  # several rounds: both array sets of `a` get written this way
+        b.upload()  # the donor's pending set = its host copy
+        src, dst = b.upload_targets(st.cuda_stream), a.upload_targets(st.cuda_stream)
+        assert [n for _, n in src] == [n for _, n in dst] and len(dst) >= 4
+        with torch.cuda.stream(st):
+            for (ps, n), (pd, _) in zip(src, dst):
+                d = torch.as_tensor(M._DeviceBytes(pd, n), device="cuda")
+                d.copy_(torch.as_tensor(M._DeviceBytes(ps, n), device="cuda"), non_blocking=True)
+        a.upload_commit(st.cuda_stream)
+        assert torch.equal(render(a), img_b), k
+        assert torch.equal(render(b), img_b), k
+        if k == 1:  # its own host copy again, in three parts (pt_scene_upload_part: what three ranks would each send)
+            assert sum(a.upload_part(r, 3) for r in (2, 0, 1)) >= sum(n for _, n in dst)
+        else:
+            a.upload()
+        assert torch.equal(render(a), img_a), k
+    a.close()
+    b.close()
+
+
 def test_render_async_pipelines_frames_and_uploads(loaded):
     """pt_render_async: frames issued back to back on one stream, with a scene upload between them, each deliver the
     image pt_render returns."""

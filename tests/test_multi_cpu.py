@@ -68,6 +68,24 @@ def _worker(rank, world, port, out_path):
         assert (img is None) == (rank != 0)
         if rank == 0:
             np.savez(out_path, img=img, accum=accum.numpy())
+        # the scene-distribution leg (DistributedRenderer.distribute_scene): ragged byte arrays of one rank reach the
+        # same-sized arrays of the others, on a process group of their own
+        grp = dist.new_group(backend="gloo")
+        sizes = [1, 48, 64 * 1000 + 17, 4096]
+        want = [torch.arange(n, dtype=torch.int64).mul(7).add(k).to(torch.uint8) for k, n in enumerate(sizes)]
+        have = [w.clone() if rank == 1 else torch.zeros_like(w) for w in want]
+        multi.broadcast_arrays(have, src=1, group=grp)
+        assert all(torch.equal(h, w) for h, w in zip(have, want))
+        # ... and the all-gather form: part r of every array valid on rank r, the remainder on both
+        have = []
+        for w in want:
+            n = multi.part_size(w.numel(), world)
+            h = torch.zeros_like(w)
+            h[rank * n:(rank + 1) * n] = w[rank * n:(rank + 1) * n]
+            h[world * n:] = w[world * n:]
+            have.append(h)
+        multi.allgather_parts(have, group=grp)
+        assert all(torch.equal(h, w) for h, w in zip(have, want))
         dist.barrier()
     finally:
         dist.destroy_process_group()
