@@ -306,6 +306,15 @@ __device__ __forceinline__ void st_wave(float4 *p, float4 v) {
 #ifndef PTB_LEAF_T
 #define PTB_LEAF_T 12
 #endif
+// PTB_SPECULATE 1: speculative traversal in k_extend (see the kernel).  Not offered for k_shadow: its result is a
+// product over the occluders, so the order in which a lane meets them - which would then depend on the lane's warp
+// mates - shows in the last bit of the transmittance; the closest-hit walk is decided by exact keys and stays
+// reproducible.  Measured (profiles/r07/ab_s32_speculative_traversal.jsonl; all 105 GPU tests green on the variant,
+// identical checksums): k_extend +2.3 % on console, -0.2 % on foliage, +2 % on city - more lanes per node visit do
+// not shorten a walk that waits for its slowest lane's memory, and the parked leaf costs wasted visits.  Off.
+#ifndef PTB_SPECULATE
+#define PTB_SPECULATE 0
+#endif
 #ifndef PTB_REFILL_T_SHADOW
 #define PTB_REFILL_T_SHADOW PTB_REFILL_T
 #endif
@@ -345,6 +354,9 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
   ClosestStack stk;
   uint32_t q = NONE;
   tv.cur = ClosestTrav::DONE;
+#if PTB_SPECULATE
+  uint32_t held = ClosestTrav::NEED_POP;  // the parked leaf (NEED_POP: none); empty again whenever a ray ends
+#endif
 #if PTB_FETCH_AHEAD_EXTEND
   WorkFetch wf;
   wf.init(&W.counters[CTR_WORK_EXTEND], n);
@@ -372,6 +384,56 @@ __global__ void __launch_bounds__(128, PTB_EXTEND_MINB) k_extend(const __grid_co
       no = node_order(tv.r, tv.pre);
     }
     if (__ballot_sync(0xffffffffu, q != NONE) == 0) break;
+#if PTB_SPECULATE
+    // Speculative traversal (Aila & Laine 2009): a lane that arrives at a leaf while the warp is not ready for a
+    // primitive phase parks the leaf in `held` and goes on with its stack instead of idling through the others' node
+    // visits; a primitive phase tests the parked leaf first.  The nodes it visits meanwhile may turn out to lie behind a
+    // hit of the parked leaf (wasted visits, same result: candidate keys decide, not the order).  Pops at one site.
+    for (;;) {
+      const bool has = q != NONE;
+#if PTB_COUNT_STEPS
+      if (has && tv.at_inner()) ++cnt_nodes;
+#endif
+      if (has && tv.at_inner()) tv.node_step(S, no, stk, true);
+      const bool cur_leaf = has && tv.at_leaf(), held_leaf = has && held != ClosestTrav::NEED_POP;
+      const uint32_t m_leaf = __ballot_sync(0xffffffffu, cur_leaf || held_leaf);
+      const uint32_t m_inner = __ballot_sync(0xffffffffu, has && tv.at_inner());
+      if (__popc(m_leaf) >= LEAF_THRESHOLD || m_inner == 0) {
+        if (cur_leaf || held_leaf) {
+#if PTB_COUNT_STEPS
+          ++cnt_prims;
+#endif
+          uint32_t ref = held_leaf ? held : tv.cur;
+          tv.leaf_test(S, stk, ref, alpha, bounce,
+                       [&]() { return make_key(P, (uint32_t)__float_as_int(ld_wave(&W.ray_d[in][q]).w)); }, n_alpha);
+          if (held_leaf) held = ref;
+          else tv.cur = ref;
+        }
+      } else if (cur_leaf && !held_leaf) {
+        held = tv.cur;
+        tv.cur = ClosestTrav::NEED_POP;
+      }
+      if (has && tv.cur == ClosestTrav::NEED_POP) tv.pop(stk);
+      if (has && tv.cur == ClosestTrav::DONE && held == ClosestTrav::NEED_POP) {
+        tv.finish(stk, alpha);
+        const bool hit = tv.st.idx >= 0;
+        st_wave(&W.hit[q], hit ? make_float4(tv.st.best_t, tv.st.u, tv.st.v, __int_as_float(tv.st.idx))
+                               : make_float4(0.f, 0.f, 0.f, __int_as_float(-1)));
+        if (trace_out) {
+          pt_hit h;
+          h.prim_id = hit ? tv.st.best_id : -1;
+          h.t = hit ? tv.st.best_t : 0.f;
+          h.u = hit ? tv.st.u : 0.f;
+          h.v = hit ? tv.st.v : 0.f;
+          trace_out[q] = h;
+        }
+        q = NONE;
+      }
+      const uint32_t busy = __ballot_sync(0xffffffffu, q != NONE);
+      if (busy == 0 || (!drained && __popc(busy) < REFILL_THRESHOLD)) break;
+    }
+    continue;
+#endif
     for (;;) {
       const bool has = q != NONE;
 #if PTB_COUNT_STEPS

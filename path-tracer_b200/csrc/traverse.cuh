@@ -243,6 +243,36 @@ struct ClosestTrav {
     else after(stk, deferred);
   }
 
+  // leaf_step on a leaf reference held outside `cur` (PTB_SPECULATE, k_extend): tests ONE primitive of `ref`; `ref` moves
+  // on to the leaf's next primitive or becomes NEED_POP when the leaf is exhausted.  Does not touch `cur` or the stack
+  // position (consider() only reads / writes the farthest-rejected record).
+  template <typename KeyFn>
+  __device__ __forceinline__ void leaf_test(const DevScene &S, ClosestStack &stk, uint32_t &ref, bool alpha, uint32_t bounce,
+                                            KeyFn key_of, uint32_t &n_alpha) {
+    if (ref & 0x40000000u) {
+      const uint32_t si = ref & 0x3FFFFFFFu;
+      const DevSphere sph = S.spheres[si];
+      float dist[2], tp[2];
+      int exit_only = 0;
+      const int n = sphere_hits(r, sph, dist, tp, exit_only);
+      for (int k = 0; k < n; ++k) {
+        const int is_exit = (n == 1) ? exit_only : k;
+        consider(S, stk, dist[k], sph.prim_id + is_exit, 0.f, 0.f, (int)(S.n_tris + 2u * si + (uint32_t)is_exit), sph.flags,
+                 alpha, bounce, key_of, n_alpha);
+      }
+      ref = NEED_POP;
+      return;
+    }
+    const float4 *tp = reinterpret_cast<const float4 *>(S.tris + ((ref & 0x3FFFFFFFu) >> 3));
+    const float4 A = __ldg(tp), B = __ldg(tp + 1), C = __ldg(tp + 2);
+    float t, u, v, det;
+    if (moller_trumbore(r, mk3(A.x, A.y, A.z), mk3(B.x, B.y, B.z), mk3(C.x, C.y, C.z), t, u, v, det))
+      consider(S, stk, t, __float_as_int(A.w), u, v, __float_as_int(B.w) | (det < 0.0f ? HIT_BACKFACE : 0),
+               __float_as_uint(C.w), alpha, bounce, key_of, n_alpha);
+    if (ref & 7u) ref += 7u;
+    else ref = NEED_POP;
+  }
+
   // After DONE: when nothing was accepted, the farthest rejected hit is the one the reference shades.
   __device__ __forceinline__ void finish(const ClosestStack &stk, bool alpha) {
     if (!alpha || st.idx >= 0) return;
