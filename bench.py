@@ -112,7 +112,7 @@ class ClockSampler:
                     self.rows.append([x.strip() for x in out.strip().split(",")])
             except Exception:
                 pass
-            self.stop.wait(0.01 if self.nvml is not None else 0.1)
+            self.stop.wait(0.02 if self.nvml is not None else 0.1)  # >= 2 samples in the shortest timed region (8 GPUs: 46 ms)
 
     def __enter__(self):
         self.th = threading.Thread(target=self._run, daemon=True)
